@@ -1,0 +1,462 @@
+// bf16 GEMM on 5th-gen tensor cores:  C[M,N] = op(A)[M,K] * op(B)[K,N] (+ R[M,N]),  fp32 accumulation.
+//
+// This is the kernel behind every nn.Linear of the reference hot path (cuBLAS there; SURVEY §2.3 K18:
+// models/llama/llama_model.py:459-462, :421-423, :55) — forward (both operands K-major), dgrad
+// (B MN-major) and wgrad (A and B MN-major), with the residual add / gradient accumulation fused into
+// the epilogue (R == C gives C += A*B).
+//
+// Design (B200, sm_100a):
+//   * persistent, warp-specialised, one CTA per SM:  warp 0 = TMA producer, warp 1 = tcgen05.mma issuer
+//     (one elected lane), warp 2 = TMEM allocator, warps 4..7 = epilogue (TMEM -> regs -> smem -> TMA store)
+//   * operands arrive by TMA (cp.async.bulk.tensor, SWIZZLE_128B) into a multi-stage smem ring guarded by
+//     mbarriers; accumulators live in TMEM (2 x 256 columns, so the epilogue of tile i overlaps the MMAs of
+//     tile i+1)
+//   * kCtaGroup == 2: a CTA pair (cluster of 2, cta_group::2) computes a 256x256 tile; each CTA loads its own
+//     128 rows of A and HALF of the B tile, the MMA reads both halves -> half the L2->smem operand traffic
+//     per flop of the 1-CTA form. Only the leader CTA issues MMAs; commits are multicast to both CTAs.
+//   * BLOCK 128(x2) x 256 x 64, UMMA 128(256) x 256 x 16.
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace llmt {
+namespace gemm {
+
+using namespace sm100;
+
+constexpr int BM = 128;       // rows of C per CTA
+constexpr int BN = 256;       // cols of C per tile (UMMA N)
+constexpr int BK = 64;        // K per pipeline stage (= one 128-byte swizzle row of bf16)
+constexpr int UMMA_K = 16;
+constexpr int kThreads = 256;
+constexpr int kEpiWarp0 = 4;  // warps 4..7
+constexpr int kAccStages = 2;
+constexpr int kTmemCols = 512;
+constexpr int kStagingBytes = 16384;  // 128 rows x 128 B
+constexpr int kNumStaging = 2;
+
+template <int kCtaGroup>
+struct Cfg {
+  static constexpr int kABytes = BM * BK * 2;                  // 16 KB
+  static constexpr int kBRows = BN / kCtaGroup;                // B rows (N) held by one CTA
+  static constexpr int kBBytes = kBRows * BK * 2;              // 32 KB or 16 KB
+  static constexpr int kStageBytes = kABytes + kBBytes;        // 48 KB or 32 KB
+  static constexpr int kStages = (kCtaGroup == 1) ? 4 : 6;     // 192 KB of operand ring either way
+  static constexpr int kRingBytes = kStages * kStageBytes;
+  static constexpr int kBarOffset = kRingBytes + kNumStaging * kStagingBytes;
+  // full[kStages] empty[kStages] tmem_full[2] tmem_empty[2] res[2] + tmem ptr
+  static constexpr int kNumBars = 2 * kStages + 2 * kAccStages + kNumStaging;
+  static constexpr int kSmemBytes = kBarOffset + kNumBars * 8 + 16 + 1024;  // +1024: manual alignment slack
+};
+
+struct Params {
+  int M, N, K;
+  int has_residual;
+};
+
+// grouped rasterisation: consecutive tile ids walk down M inside a band of kGroupM m-tiles so that the
+// ~148 tiles in flight share A and B panels in L2
+__device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int& tm, int& tn) {
+  constexpr int kGroupM = 8;
+  const int per_group = kGroupM * num_n;
+  const int g = tile / per_group;
+  const int first_m = g * kGroupM;
+  const int group_m = min(num_m - first_m, kGroupM);
+  const int r = tile - g * per_group;
+  tm = first_m + (r % group_m);
+  tn = r / group_m;
+}
+
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, Params p) {
+  using C = Cfg<kCtaGroup>;
+  constexpr int kOutChunkCols = 128 / (int)sizeof(OutT);  // columns per 128-byte staging row: 64 bf16 / 32 fp32
+  constexpr int kNumChunks = BN / kOutChunkCols;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B wants 1024-B alignment
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+
+  const uint32_t bars = smem_base + C::kBarOffset;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::kStages + s); };
+  auto tmem_full_bar = [&](int a) { return bars + 8u * (2 * C::kStages + a); };
+  auto tmem_empty_bar = [&](int a) { return bars + 8u * (2 * C::kStages + kAccStages + a); };
+  auto res_bar = [&](int b) { return bars + 8u * (2 * C::kStages + 2 * kAccStages + b); };
+  const uint32_t tmem_ptr_smem = bars + 8u * C::kNumBars;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + C::kBarOffset + 8 * C::kNumBars);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = (kCtaGroup == 2) ? cluster_ctarank() : 0u;
+  const bool is_leader = cta_rank == 0;
+
+  const int num_m = (p.M + BM * kCtaGroup - 1) / (BM * kCtaGroup);
+  const int num_n = (p.N + BN - 1) / BN;
+  const int num_tiles = num_m * num_n;
+  const int num_k = (p.K + BK - 1) / BK;
+  const int worker = blockIdx.x / kCtaGroup;
+  const int num_workers = gridDim.x / kCtaGroup;
+
+  // ---------------------------------------------------------------- one-time setup
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmC);
+    if (p.has_residual) tma_prefetch_desc(&tmR);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < kAccStages; ++a) {
+      mbar_init(tmem_full_bar(a), 1);
+      mbar_init(tmem_empty_bar(a), 4 * kCtaGroup);  // one arrive per epilogue warp of every CTA in the group
+    }
+    for (int b = 0; b < kNumStaging; ++b) mbar_init(res_bar(b), 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<kCtaGroup>(tmem_ptr_smem, kTmemCols);
+    tmem_relinquish<kCtaGroup>();
+  }
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  // ---------------------------------------------------------------- roles
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      // in a CTA pair all operand bytes are accounted on the LEADER's full barrier
+      const uint32_t full0 = (kCtaGroup == 2) ? mapa(full_bar(0), 0) : full_bar(0);
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = worker; tile < num_tiles; tile += num_workers) {
+        int tm, tn;
+        tile_coords(tile, num_m, num_n, tm, tn);
+        const int m0 = (tm * kCtaGroup + (int)cta_rank) * BM;
+        const int n0 = tn * BN + (int)cta_rank * C::kBRows;
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+          const uint32_t fb = full0 + 8u * stage;
+          const int k0 = kb * BK;
+          if (kCtaGroup == 1 || is_leader) mbar_arrive_expect_tx(full_bar(stage), C::kStageBytes * kCtaGroup);
+          if constexpr (kCtaGroup == 1) {
+            if constexpr (!kAMn) tma_load_2d(sa, &tmA, fb, k0, m0);
+            else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tmA, fb, m0 + j * 64, k0);
+            }
+            if constexpr (!kBMn) tma_load_2d(sb, &tmB, fb, k0, n0);
+            else {
+#pragma unroll
+              for (int j = 0; j < C::kBRows / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tmB, fb, n0 + j * 64, k0);
+            }
+          } else {
+            if constexpr (!kAMn) tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
+            else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j) tma_load_2d_cg2(sa + j * (BK * 128), &tmA, fb, m0 + j * 64, k0);
+            }
+            if constexpr (!kBMn) tma_load_2d_cg2(sb, &tmB, fb, k0, n0);
+            else {
+#pragma unroll
+              for (int j = 0; j < C::kBRows / 64; ++j)
+                tma_load_2d_cg2(sb + j * (BK * 128), &tmB, fb, n0 + j * 64, k0);
+            }
+          }
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer (leader CTA only) =====
+    if (is_leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * kCtaGroup, BN, kAMn, kBMn);
+      constexpr uint32_t kALbo = kAMn ? BK * 128 : 0, kBLbo = kBMn ? BK * 128 : 0;
+      constexpr uint32_t kAKStep = kAMn ? UMMA_K * 128 : UMMA_K * 2;  // bytes to advance 16 along K
+      constexpr uint32_t kBKStep = kBMn ? UMMA_K * 128 : UMMA_K * 2;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = worker; tile < num_tiles; tile += num_workers) {
+        mbar_wait_cluster(tmem_empty_bar(acc), acc_phase ^ 1);  // epilogue(s) drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_k; ++kb) {
+          mbar_wait_cluster(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t sa = smem_base + stage * C::kStageBytes;
+          const uint32_t sb = sa + C::kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t ad = make_smem_desc(sa + k * kAKStep, kALbo, 1024);
+            const uint64_t bd = make_smem_desc(sb + k * kBKStep, kBLbo, 1024);
+            umma_f16<kCtaGroup>(d_tmem, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          // frees this smem stage (in both CTAs of a pair) once the MMAs above have read it
+          if constexpr (kCtaGroup == 1) umma_commit(empty_bar(stage));
+          else umma_commit_cg2_mcast(empty_bar(stage), 0b11);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        if constexpr (kCtaGroup == 1) umma_commit(tmem_full_bar(acc));
+        else umma_commit_cg2_mcast(tmem_full_bar(acc), 0b11);
+        if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= kEpiWarp0) {
+    // ===== epilogue: TMEM -> registers -> (+R) -> swizzled smem -> TMA store =====
+    const int ew = warp - kEpiWarp0;       // == warp % 4 -> TMEM lanes [32*ew, 32*ew+32)
+    const int row = ew * 32 + lane;        // row of the 128-row CTA tile owned by this thread
+    const bool store_leader = (warp == kEpiWarp0 && lane == 0);
+    const uint32_t staging0 = smem_base + C::kRingBytes;
+    uint8_t* staging_gen = smem_gen + C::kRingBytes;
+    const uint32_t tmem_empty_target = (kCtaGroup == 2) ? mapa(tmem_empty_bar(0), 0) : tmem_empty_bar(0);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t res_phase_bits = 0;
+    int chunk_counter = 0;
+    for (int tile = worker; tile < num_tiles; tile += num_workers) {
+      int tm, tn;
+      tile_coords(tile, num_m, num_n, tm, tn);
+      const int m0 = (tm * kCtaGroup + (int)cta_rank) * BM;
+      const int n0 = tn * BN;
+      mbar_wait_cluster(tmem_full_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + ((uint32_t)(ew * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int ch = 0; ch < kNumChunks; ++ch, ++chunk_counter) {
+        const int buf = chunk_counter & 1;
+        const uint32_t sbuf = staging0 + buf * kStagingBytes;
+        uint8_t* gbuf = staging_gen + buf * kStagingBytes;
+        const int c0 = n0 + ch * kOutChunkCols;
+        // (1) the TMA store that last used this staging buffer must have finished reading it
+        if (store_leader) tma_store_wait_read<kNumStaging - 1>();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // (2) optional residual / accumulate source: TMA load of the R chunk into the staging buffer
+        if (p.has_residual) {
+          if (store_leader) {
+            mbar_arrive_expect_tx(res_bar(buf), kStagingBytes);
+            tma_load_2d(sbuf, &tmR, res_bar(buf), c0, m0);
+          }
+        }
+        // (3) accumulator chunk -> registers (kept as raw fp32 bits)
+        uint32_t v[32 * (kOutChunkCols / 32)];
+#pragma unroll
+        for (int q = 0; q < kOutChunkCols / 32; ++q) {
+          uint32_t (&vq)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[q * 32]);
+          tmem_ld_32x32b_x32(t_row + (uint32_t)(ch * kOutChunkCols + q * 32), vq);
+        }
+        tmem_ld_wait();
+        if (ch == kNumChunks - 1) {
+          // whole accumulator is in registers: hand the TMEM stage back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (kCtaGroup == 2) mbar_arrive_cluster(tmem_empty_target + 8u * acc);
+            else mbar_arrive(tmem_empty_target + 8u * acc);
+          }
+        }
+        if (p.has_residual) {
+          mbar_wait(res_bar(buf), (res_phase_bits >> buf) & 1u);
+          res_phase_bits ^= 1u << buf;
+        }
+        // (4) convert (+ residual) and write this thread's 128-byte row in the SWIZZLE_128B pattern
+        uint8_t* grow = gbuf + row * 128;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {  // 16-byte pieces of the row
+          uint8_t* dst = grow + ((j ^ (row & 7)) << 4);
+          if constexpr (sizeof(OutT) == 2) {
+            float f[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(v[j * 8 + e]);
+            if (p.has_residual) {
+              float r[8];
+              unpack8(*reinterpret_cast<const bf16x8*>(dst), r);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) f[e] += r[e];
+            }
+            *reinterpret_cast<bf16x8*>(dst) = pack8(f);
+          } else {
+            float4 o = make_float4(__uint_as_float(v[j * 4 + 0]), __uint_as_float(v[j * 4 + 1]),
+                                   __uint_as_float(v[j * 4 + 2]), __uint_as_float(v[j * 4 + 3]));
+            if (p.has_residual) {
+              const float4 r = *reinterpret_cast<const float4*>(dst);
+              o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w;
+            }
+            *reinterpret_cast<float4*>(dst) = o;
+          }
+        }
+        // (5) publish to the async proxy, then one thread stores the 128 x chunk box
+        fence_proxy_async_smem();
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+        if (store_leader) {
+          tma_store_2d(&tmC, sbuf, c0, m0);
+          tma_store_commit();
+        }
+      }
+      if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+    }
+    if (store_leader) tma_store_wait<0>();
+  }
+
+  // ---------------------------------------------------------------- teardown
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<kCtaGroup>(tmem_base, kTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// 2-D row-major tensor [rows, cols] with leading dimension ld (elements); box = {box_cols, box_rows}.
+int make_tmap_2d(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows, int64_t cols, int64_t ld,
+                 int box_cols, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return 3;
+  }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * elem_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                  const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): ptr=%p rows=%lld cols=%lld ld=%lld box=%dx%d", (int)r, ptr,
+              (long long)rows, (long long)cols, (long long)ld, box_cols, box_rows);
+    return 3;
+  }
+  return 0;
+}
+
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT>
+int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const CUtensorMap& r, Params p,
+           int max_ctas, cudaStream_t stream) {
+  using C = Cfg<kCtaGroup>;
+  auto kern = gemm_bf16_kernel<kCtaGroup, kAMn, kBMn, OutT>;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
+    if (e != cudaSuccess) {
+      set_error("gemm: cannot set %d B dynamic smem: %s", C::kSmemBytes, cudaGetErrorString(e));
+      return 2;
+    }
+    configured = true;
+  }
+  const int num_m = (p.M + BM * kCtaGroup - 1) / (BM * kCtaGroup);
+  const int num_n = (p.N + BN - 1) / BN;
+  int workers = num_m * num_n;
+  const int cap = max_ctas / kCtaGroup;
+  if (workers > cap) workers = cap;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(workers * kCtaGroup);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCtaGroup;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p);
+  if (e != cudaSuccess) {
+    set_error("gemm launch: %s", cudaGetErrorString(e));
+    return 2;
+  }
+  return 0;
+}
+
+}  // namespace gemm
+}  // namespace llmt
+
+using namespace llmt;
+using namespace llmt::gemm;
+
+// C[M,N] = op(A) * op(B) (+ R).  All matrices row-major with leading dimensions in elements.
+//   a_mn_major = 0: A stored [M, K] (lda >= K)      1: A stored [K, M] (lda >= M)
+//   b_mn_major = 0: B stored [N, K] (ldb >= K)      1: B stored [K, N] (ldb >= N)
+//   out_fp32: C (and R) are fp32, else bf16.  R may be null; R == C accumulates in place.
+//   cta_group: 1 or 2 (CTA pairs, 256x256 tiles).  max_ctas <= 0 -> all SMs.
+extern "C" int llmt_gemm_bf16(const void* A, const void* B, void* Cout, const void* R, int M, int N, int K,
+                              int64_t lda, int64_t ldb, int64_t ldc, int64_t ldr, int a_mn_major, int b_mn_major,
+                              int out_fp32, int cta_group, int max_ctas, cudaStream_t stream) {
+  LLMT_REQUIRE(M > 0 && N > 0 && K > 0, "gemm: empty problem %dx%dx%d", M, N, K);
+  LLMT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "gemm: lda/ldb must be multiples of 8 elements (16-byte rows)");
+  LLMT_REQUIRE((ldc * (out_fp32 ? 4 : 2)) % 16 == 0, "gemm: ldc must give 16-byte aligned rows");
+  LLMT_REQUIRE(((uintptr_t)A % 16 == 0) && ((uintptr_t)B % 16 == 0) && ((uintptr_t)Cout % 16 == 0) &&
+                   ((uintptr_t)R % 16 == 0),
+               "gemm: operands must be 16-byte aligned");
+  LLMT_REQUIRE(cta_group == 1 || cta_group == 2, "gemm: cta_group must be 1 or 2");
+  if (max_ctas <= 0) max_ctas = num_sms();
+  if (max_ctas < cta_group) max_ctas = cta_group;
+
+  CUtensorMap ta, tb, tc, tr;
+  int rc;
+  if (!a_mn_major) rc = make_tmap_2d(&ta, A, 2, M, K, lda, BK, BM);
+  else             rc = make_tmap_2d(&ta, A, 2, K, M, lda, 64, BK);
+  if (rc) return rc;
+  const int b_rows = BN / cta_group;
+  if (!b_mn_major) rc = make_tmap_2d(&tb, B, 2, N, K, ldb, BK, b_rows);
+  else             rc = make_tmap_2d(&tb, B, 2, K, N, ldb, 64, BK);
+  if (rc) return rc;
+  const int esz = out_fp32 ? 4 : 2;
+  rc = make_tmap_2d(&tc, Cout, esz, M, N, ldc, 128 / esz, BM);
+  if (rc) return rc;
+  if (R) {
+    rc = make_tmap_2d(&tr, R, esz, M, N, ldr, 128 / esz, BM);
+    if (rc) return rc;
+  } else {
+    tr = tc;
+  }
+  Params p{M, N, K, R ? 1 : 0};
+
+#define LLMT_GEMM_DISPATCH(CG, AMN, BMN)                                                        \
+  return out_fp32 ? launch<CG, AMN, BMN, float>(ta, tb, tc, tr, p, max_ctas, stream)            \
+                  : launch<CG, AMN, BMN, __nv_bfloat16>(ta, tb, tc, tr, p, max_ctas, stream)
+  if (cta_group == 1) {
+    if (!a_mn_major && !b_mn_major) { LLMT_GEMM_DISPATCH(1, false, false); }
+    if (!a_mn_major && b_mn_major) { LLMT_GEMM_DISPATCH(1, false, true); }
+    if (a_mn_major && b_mn_major) { LLMT_GEMM_DISPATCH(1, true, true); }
+    LLMT_GEMM_DISPATCH(1, true, false);
+  } else {
+    if (!a_mn_major && !b_mn_major) { LLMT_GEMM_DISPATCH(2, false, false); }
+    if (!a_mn_major && b_mn_major) { LLMT_GEMM_DISPATCH(2, false, true); }
+    if (a_mn_major && b_mn_major) { LLMT_GEMM_DISPATCH(2, true, true); }
+    LLMT_GEMM_DISPATCH(2, true, false);
+  }
+#undef LLMT_GEMM_DISPATCH
+}

@@ -1,0 +1,198 @@
+// RMSNorm forward / backward for bf16 activations (fp32 math), rows x cols with cols % 8 == 0.
+//
+//   y = x * rsqrt(mean(x^2) + eps) * w
+//
+// Replaces Liger's Triton RMSNorm on the reference hot path
+// (reference: src/llm_training/ops/liger_kernel/rms_norm_op.py:15-19, called from
+// models/llama/llama_model.py:283).  Memory-bound: one pass over x, row kept in registers,
+// 16-byte vector accesses, one CTA per row in a grid-stride loop.
+//
+// Backward:  dx = rstd * (g - xhat * mean(g * xhat)),  g = dy * w,  xhat = x * rstd
+//            dw = sum_rows dy * xhat
+// dw is produced in two stages: every CTA accumulates its rows into registers and writes one fp32
+// partial row into caller-provided scratch [grid, cols]; a second kernel sums the partials.
+#include "common.cuh"
+
+namespace llmt {
+
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxVec = 8;  // cols <= 256 * 8 * 8 = 16384
+
+template <int MAXV>
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w,
+                   __nv_bfloat16* __restrict__ y, float* __restrict__ rstd_out, int rows, int cols,
+                   float eps) {
+  __shared__ float red[32];
+  const int nvec = cols >> 3;
+  float wreg[MAXV][8];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) unpack8(ld_bf16x8(w + (size_t)v * 8), wreg[i]);
+  }
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const __nv_bfloat16* xr = x + (size_t)row * cols;
+    float xv[MAXV][8];
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) {
+        unpack8(ld_bf16x8_stream(xr + (size_t)v * 8), xv[i]);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) ss += xv[i][j] * xv[i][j];
+      }
+    }
+    ss = block_sum(ss, red);
+    const float rstd = rsqrtf(ss / (float)cols + eps);
+    if (threadIdx.x == 0 && rstd_out != nullptr) rstd_out[row] = rstd;
+    __nv_bfloat16* yr = y + (size_t)row * cols;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = xv[i][j] * rstd * wreg[i][j];
+        st_bf16x8(yr + (size_t)v * 8, pack8(o));
+      }
+    }
+  }
+}
+
+template <int MAXV>
+__global__ void __launch_bounds__(kNormThreads)
+rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                   const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd_in,
+                   __nv_bfloat16* __restrict__ dx, float* __restrict__ dw_partial, int rows, int cols) {
+  __shared__ float red[32];
+  const int nvec = cols >> 3;
+  float wreg[MAXV][8];
+  float dwacc[MAXV][8];
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) unpack8(ld_bf16x8(w + (size_t)v * 8), wreg[i]);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
+  }
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+    const size_t off = (size_t)row * cols;
+    const float rstd = rstd_in[row];
+    float xh[MAXV][8], g[MAXV][8];
+    float dot = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) {
+        float dyv[8];
+        unpack8(ld_bf16x8_stream(x + off + (size_t)v * 8), xh[i]);
+        unpack8(ld_bf16x8_stream(dy + off + (size_t)v * 8), dyv);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          xh[i][j] *= rstd;
+          g[i][j] = dyv[j] * wreg[i][j];
+          dot += g[i][j] * xh[i][j];
+          dwacc[i][j] += dyv[j] * xh[i][j];
+        }
+      }
+    }
+    dot = block_sum(dot, red) / (float)cols;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) {
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+        st_bf16x8(dx + off + (size_t)v * 8, pack8(o));
+      }
+    }
+  }
+  float* part = dw_partial + (size_t)blockIdx.x * cols;
+#pragma unroll
+  for (int i = 0; i < MAXV; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      *reinterpret_cast<float4*>(part + (size_t)v * 8) =
+          make_float4(dwacc[i][0], dwacc[i][1], dwacc[i][2], dwacc[i][3]);
+      *reinterpret_cast<float4*>(part + (size_t)v * 8 + 4) =
+          make_float4(dwacc[i][4], dwacc[i][5], dwacc[i][6], dwacc[i][7]);
+    }
+  }
+}
+
+// dw[c] (+)= sum_p partial[p, c]; output bf16 or fp32
+template <typename OutT>
+__global__ void colsum_partials_kernel(const float* __restrict__ partial, OutT* __restrict__ out,
+                                       int nparts, int cols, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float s = 0.f;
+  for (int p = 0; p < nparts; ++p) s += partial[(size_t)p * cols + c];
+  if (accumulate) s += (float)out[c];
+  out[c] = (OutT)s;
+}
+
+int norm_grid(int rows) {
+  const int g = num_sms() * 4;
+  return rows < g ? rows : g;
+}
+
+}  // namespace llmt
+
+using namespace llmt;
+
+extern "C" int llmt_rmsnorm_bwd_num_partials(int rows) { return norm_grid(rows); }
+
+extern "C" int llmt_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int rows, int cols,
+                                float eps, cudaStream_t stream) {
+  LLMT_REQUIRE(cols % 8 == 0 && cols <= kNormThreads * 8 * kNormMaxVec,
+               "rmsnorm: cols=%d must be a multiple of 8 and <= %d", cols, kNormThreads * 8 * kNormMaxVec);
+  if (rows == 0) return 0;
+  const int grid = norm_grid(rows);
+  auto X = (const __nv_bfloat16*)x;
+  auto W = (const __nv_bfloat16*)w;
+  auto Y = (__nv_bfloat16*)y;
+  const int nvec = cols / 8;
+  if (nvec <= kNormThreads * 2)
+    rmsnorm_fwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(X, W, Y, rstd, rows, cols, eps);
+  else if (nvec <= kNormThreads * 4)
+    rmsnorm_fwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(X, W, Y, rstd, rows, cols, eps);
+  else
+    rmsnorm_fwd_kernel<8><<<grid, kNormThreads, 0, stream>>>(X, W, Y, rstd, rows, cols, eps);
+  return check_launch("rmsnorm_fwd");
+}
+
+// dw_partial: fp32 scratch [llmt_rmsnorm_bwd_num_partials(rows), cols]. dw_is_fp32 selects the output
+// type of dw; accumulate_dw adds into the existing dw (gradient accumulation).
+extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx,
+                                void* dw, float* dw_partial, int rows, int cols, int dw_is_fp32,
+                                int accumulate_dw, cudaStream_t stream) {
+  LLMT_REQUIRE(cols % 8 == 0 && cols <= kNormThreads * 8 * kNormMaxVec,
+               "rmsnorm_bwd: cols=%d must be a multiple of 8 and <= %d", cols, kNormThreads * 8 * kNormMaxVec);
+  if (rows == 0) return 0;
+  const int grid = norm_grid(rows);
+  auto DY = (const __nv_bfloat16*)dy;
+  auto X = (const __nv_bfloat16*)x;
+  auto W = (const __nv_bfloat16*)w;
+  auto DX = (__nv_bfloat16*)dx;
+  const int nvec = cols / 8;
+  if (nvec <= kNormThreads * 2)
+    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+  else if (nvec <= kNormThreads * 4)
+    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+  else
+    rmsnorm_bwd_kernel<8><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+  int rc = check_launch("rmsnorm_bwd");
+  if (rc) return rc;
+  const int tb = 128;
+  if (dw_is_fp32)
+    colsum_partials_kernel<float><<<(cols + tb - 1) / tb, tb, 0, stream>>>(dw_partial, (float*)dw, grid, cols,
+                                                                          accumulate_dw);
+  else
+    colsum_partials_kernel<__nv_bfloat16>
+        <<<(cols + tb - 1) / tb, tb, 0, stream>>>(dw_partial, (__nv_bfloat16*)dw, grid, cols, accumulate_dw);
+  return check_launch("rmsnorm_bwd_colsum");
+}

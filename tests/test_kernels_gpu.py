@@ -1,0 +1,224 @@
+"""sm_100a kernels vs plain PyTorch fp32 restatements of the same op (SURVEY §4 'kernel oracle tests')."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from llm_training_b200.ops import reference as ref
+from llm_training_b200.ops.adamw_op import adamw_step, sumsq
+from llm_training_b200.ops.cross_entropy_op import (cross_entropy, fused_linear_cross_entropy,
+                                                    fused_linear_logprob)
+from llm_training_b200.ops.embedding_op import embedding
+from llm_training_b200.ops.gemm_op import gemm
+from llm_training_b200.ops.linear_op import linear
+from llm_training_b200.ops.rms_norm_op import rms_norm
+from llm_training_b200.ops.rope_op import rope_qk_packed
+from llm_training_b200.ops.swiglu_op import silu_mul_fused
+
+DEV = 'cuda'
+
+
+def _close(a, b, rtol=2e-2, atol=2e-2):
+    a, b = a.float(), b.float()
+    err = (a - b).abs().max().item()
+    bound = atol + rtol * b.abs().max().item()
+    assert err <= bound, f'max abs err {err} > {bound}'
+
+
+def test_kernel_library_is_loaded():
+    from llm_training_b200.ops import _lib
+    assert _lib.lib().llmt_abi_version() == 1
+
+
+@pytest.mark.parametrize('rows,cols', [(64, 4096), (333, 1024), (17, 8192), (5, 3072)])
+def test_rmsnorm(rows, cols):
+    torch.manual_seed(0)
+    x = torch.randn(rows, cols, device=DEV).bfloat16().requires_grad_()
+    w = (1 + 0.1 * torch.randn(cols, device=DEV)).bfloat16().requires_grad_()
+    dy = torch.randn(rows, cols, device=DEV).bfloat16()
+    y = rms_norm(x, w, 1e-5)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    wr = w.detach().float().requires_grad_()
+    yr = ref.rms_norm_ref(xr, wr, 1e-5)
+    yr.backward(dy.float())
+    _close(y, yr)
+    _close(x.grad, xr.grad)
+    _close(w.grad, wr.grad, rtol=3e-2, atol=0.15)
+
+
+def test_silu_mul():
+    torch.manual_seed(0)
+    gu = torch.randn(300, 2 * 1024, device=DEV).bfloat16().requires_grad_()
+    d = torch.randn(300, 1024, device=DEV).bfloat16()
+    out = silu_mul_fused(gu)
+    out.backward(d)
+    gr = gu.detach().float().requires_grad_()
+    g, u = gr.chunk(2, -1)
+    outr = torch.nn.functional.silu(g) * u
+    outr.backward(d.float())
+    _close(out, outr)
+    _close(gu.grad, gr.grad)
+
+
+@pytest.mark.parametrize('head_dim', [128, 96, 64])
+def test_rope(head_dim):
+    torch.manual_seed(0)
+    t, hq, hkv = 200, 4, 2
+    qkv = torch.randn(t, (hq + 2 * hkv) * head_dim, device=DEV).bfloat16()
+    pos = torch.randint(0, 512, (t,), device=DEV, dtype=torch.int32)
+    inv = 1.0 / (10000 ** (torch.arange(0, head_dim, 2, device=DEV).float() / head_dim))
+    fr = torch.outer(torch.arange(512, device=DEV).float(), inv)
+    cos_t, sin_t = fr.cos().contiguous(), fr.sin().contiguous()
+    expect = rope_qk_packed(qkv.float().cpu(), pos.cpu(), cos_t.cpu(), sin_t.cpu(), hq + hkv, head_dim)
+    x = qkv.clone().requires_grad_()
+    y = rope_qk_packed(x * 1.0, pos, cos_t, sin_t, hq + hkv, head_dim)
+    _close(y.cpu(), expect)
+    # backward = inverse rotation: rope(bwd(rope(x))) round trip via autograd
+    g = torch.randn_like(qkv)
+    y.backward(g)
+    xr = qkv.float().cpu().requires_grad_()
+    yr = rope_qk_packed(xr, pos.cpu(), cos_t.cpu(), sin_t.cpu(), hq + hkv, head_dim)
+    yr.backward(g.float().cpu())
+    _close(x.grad.cpu(), xr.grad)
+
+
+@pytest.mark.parametrize('cg', [1, 2])
+@pytest.mark.parametrize('amn,bmn', [(0, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize('m,n,k', [(256, 256, 128), (392, 712, 328), (1024, 1536, 512)])
+def test_gemm(cg, amn, bmn, m, n, k):
+    torch.manual_seed(0)
+    a = (torch.randn((k, m) if amn else (m, k), device=DEV) * 0.5).bfloat16()
+    b = (torch.randn((k, n) if bmn else (n, k), device=DEV) * 0.5).bfloat16()
+    A = a.float().t() if amn else a.float()
+    B = b.float() if bmn else b.float().t()
+    c = gemm(a, b, a_mn_major=bool(amn), b_mn_major=bool(bmn), cta_group=cg)
+    _close(c, A @ B, rtol=1e-2, atol=1e-2)
+
+
+@pytest.mark.parametrize('cg', [1, 2])
+def test_gemm_residual_and_fp32_accumulate(cg):
+    torch.manual_seed(0)
+    m, n, k = 520, 776, 264
+    a = torch.randn(m, k, device=DEV).bfloat16()
+    b = torch.randn(n, k, device=DEV).bfloat16()
+    r = torch.randn(m, n, device=DEV).bfloat16()
+    c = gemm(a, b, residual=r, cta_group=cg)
+    _close(c, a.float() @ b.float().t() + r.float(), rtol=1e-2)
+    acc = torch.randn(m, n, device=DEV)
+    expect = acc + a.float() @ b.float().t()
+    gemm(a, b, out=acc, residual=acc, cta_group=cg)
+    _close(acc, expect, rtol=1e-2)
+
+
+def test_linear_autograd():
+    torch.manual_seed(0)
+    x = torch.randn(4, 100, 256, device=DEV).bfloat16().requires_grad_()
+    w = (torch.randn(384, 256, device=DEV) * 0.05).bfloat16().requires_grad_()
+    r = torch.randn(4, 100, 384, device=DEV).bfloat16().requires_grad_()
+    dy = torch.randn(4, 100, 384, device=DEV).bfloat16()
+    y = linear(x, w, residual=r)
+    y.backward(dy)
+    xr, wr, rr = (t.detach().float().requires_grad_() for t in (x, w, r))
+    yr = torch.nn.functional.linear(xr, wr) + rr
+    yr.backward(dy.float())
+    _close(y, yr)
+    _close(x.grad, xr.grad)
+    _close(w.grad, wr.grad, rtol=2e-2, atol=0.1)
+    _close(r.grad, rr.grad)
+
+
+def test_cross_entropy_plain():
+    torch.manual_seed(0)
+    logits = (torch.randn(300, 4104, device=DEV) * 2).bfloat16().requires_grad_()
+    labels = torch.randint(0, 4104, (300,), device=DEV)
+    labels[::7] = -100
+    loss = cross_entropy(logits, labels)
+    loss.backward()
+    lr = logits.detach().float().requires_grad_()
+    lossr = ref.cross_entropy_ref(lr, labels)
+    lossr.backward()
+    assert abs(loss.item() - lossr.item()) < 2e-3 * max(1.0, abs(lossr.item()))
+    _close(logits.grad, lr.grad, rtol=2e-2, atol=1e-5)
+
+
+@pytest.mark.parametrize('rows,vocab', [(300, 1000), (5000, 2048)])
+def test_fused_linear_cross_entropy(rows, vocab):
+    torch.manual_seed(0)
+    dim = 256
+    h = torch.randn(rows, dim, device=DEV).bfloat16().requires_grad_()
+    w = (torch.randn(vocab, dim, device=DEV) * 0.05).bfloat16().requires_grad_()
+    labels = torch.randint(0, vocab, (rows,), device=DEV)
+    labels[::5] = -100
+    loss = fused_linear_cross_entropy(h, w, labels)
+    (loss * 2.0).backward()
+    hr, wr = h.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    lossr = ref.linear_cross_entropy_ref(hr, wr, labels)
+    (lossr * 2.0).backward()
+    assert abs(loss.item() - lossr.item()) < 5e-3 * max(1.0, abs(lossr.item()))
+    _close(h.grad, hr.grad, rtol=3e-2, atol=1e-5)
+    _close(w.grad, wr.grad, rtol=3e-2, atol=1e-5)
+
+
+def test_fused_linear_logprob():
+    torch.manual_seed(0)
+    rows, vocab, dim = 400, 1536, 128
+    h = torch.randn(rows, dim, device=DEV).bfloat16().requires_grad_()
+    w = (torch.randn(vocab, dim, device=DEV) * 0.05).bfloat16().requires_grad_()
+    labels = torch.randint(0, vocab, (rows,), device=DEV)
+    labels[::3] = -100
+    up = torch.randn(rows, device=DEV)
+    lp = fused_linear_logprob(h, w, labels)
+    (lp * up).sum().backward()
+    hr, wr = h.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    lpr = ref.token_logprob_ref(hr, wr, labels)
+    (lpr * up).sum().backward()
+    _close(lp, lpr, rtol=1e-2, atol=2e-2)
+    _close(h.grad, hr.grad, rtol=3e-2, atol=1e-3)
+    _close(w.grad, wr.grad, rtol=3e-2, atol=1e-2)
+
+
+def test_embedding_and_neftune():
+    torch.manual_seed(0)
+    vocab, dim = 1000, 256
+    w = torch.randn(vocab, dim, device=DEV).bfloat16().requires_grad_()
+    ids = torch.randint(0, vocab, (3, 50), device=DEV)
+    out = embedding(ids, w)
+    assert torch.equal(out, w.detach()[ids])
+    dy = torch.randn(3, 50, dim, device=DEV).bfloat16()
+    out.backward(dy)
+    expect = torch.zeros(vocab, dim, device=DEV)
+    expect.index_add_(0, ids.reshape(-1), dy.reshape(-1, dim).float())
+    _close(w.grad, expect, rtol=1e-2, atol=1e-2)
+    scale = torch.full((150,), 0.5, device=DEV)
+    scale[:10] = 0
+    noisy = embedding(ids, w.detach(), noise_scale=scale, seed=123)
+    delta = (noisy.float() - w.detach()[ids].float()).reshape(150, dim)
+    assert delta[:10].abs().max().item() == 0
+    assert 0 < delta[10:].abs().max().item() <= 0.5 + 0.02
+    assert abs(delta[10:].mean().item()) < 0.01
+    assert abs(delta[10:].std().item() - 0.5 / math.sqrt(3)) < 0.02
+
+
+def test_adamw_and_sumsq():
+    torch.manual_seed(0)
+    n = 100003
+    master = torch.randn(n + 1, device=DEV)[:n - 3].contiguous()
+    n = master.numel()
+    g = torch.randn(n, device=DEV).bfloat16()
+    m, v = torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)
+    p = master.bfloat16()
+    mr, m_r, v_r = master.clone().cpu(), m.clone().cpu(), v.clone().cpu()
+    norm_sq = torch.zeros(1, device=DEV)
+    sumsq(g, norm_sq)
+    assert abs(norm_sq.item() - g.float().pow(2).sum().item()) < 1e-3 * norm_sq.item()
+    for step in (1, 2, 3):
+        adamw_step(master, m, v, g, p, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, step=step,
+                   max_norm=1.0, norm_sq=norm_sq)
+        coef = min(1.0, 1.0 / (math.sqrt(norm_sq.item()) + 1e-6))
+        ref.adamw_ref(mr, g.float().cpu(), m_r, v_r, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1,
+                      step=step, grad_scale=coef)
+    _close(master.cpu(), mr, rtol=1e-4, atol=1e-5)
+    _close(p.cpu(), mr, rtol=1e-2, atol=1e-2)
