@@ -1,0 +1,2 @@
+from .modeling_outputs import CausalLMOutput
+from .utils import init_empty_weights, init_on_device

@@ -1,0 +1,128 @@
+"""Attention: packed varlen causal attention (the hot path) plus the 4-D-mask utilities of the
+reference for the ``eager`` / ``sdpa`` implementations.
+
+Reference: src/llm_training/ops/attention_op.py — ``prepare_4d_causal_attention_mask`` (:317-372),
+packed-sequence mask (:286-314), segment ids -> cu_seqlens (:375-412), ``flash_attention_forward``
+(:538-654).  The flash-attn 2.8 CUDA kernels it calls are replaced by ``csrc/kernels/attention.cu``.
+"""
+import math
+
+import torch
+
+from . import _lib
+from .reference import attention_mask_from_bounds, attention_ref
+from .segments import segment_bounds
+
+
+class _PackedAttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.Tensor, hq: int, hkv: int,
+                head_dim: int, scale: float, window: int) -> torch.Tensor:
+        L = _lib.lib()
+        tokens = qkv.shape[0]
+        out = torch.empty((tokens, hq * head_dim), dtype=qkv.dtype, device=qkv.device)
+        lse = torch.empty((hq, tokens), dtype=torch.float32, device=qkv.device)
+        _lib.check(L.llmt_attn_fwd(_lib.ptr(qkv), _lib.ptr(out), _lib.ptr(lse), _lib.ptr(seg_start),
+                                   _lib.c_int(tokens), _lib.c_int(hq), _lib.c_int(hkv), _lib.c_int(head_dim),
+                                   _lib.c_i64(qkv.stride(0)), _lib.c_f32(scale), _lib.c_int(window), _lib.stream()),
+                   'attn_fwd')
+        ctx.save_for_backward(qkv, out, lse, seg_start, seg_end)
+        ctx.meta = (hq, hkv, head_dim, scale, window)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout: torch.Tensor):
+        qkv, out, lse, seg_start, seg_end = ctx.saved_tensors
+        hq, hkv, head_dim, scale, window = ctx.meta
+        L = _lib.lib()
+        tokens = qkv.shape[0]
+        dout = dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        delta = torch.empty((hq, tokens), dtype=torch.float32, device=qkv.device)
+        # fp32 dQ accumulator [T, Hq*D] (scratch), converted into dqkv by the kernel's final pass
+        dq_acc = torch.zeros((tokens, hq * head_dim), dtype=torch.float32, device=qkv.device)
+        _lib.check(L.llmt_attn_bwd(_lib.ptr(qkv), _lib.ptr(out), _lib.ptr(dout), _lib.ptr(lse), _lib.ptr(delta),
+                                   _lib.ptr(dq_acc), _lib.ptr(dqkv), _lib.ptr(seg_start), _lib.ptr(seg_end),
+                                   _lib.c_int(tokens), _lib.c_int(hq), _lib.c_int(hkv), _lib.c_int(head_dim),
+                                   _lib.c_i64(qkv.stride(0)), _lib.c_f32(scale), _lib.c_int(window), _lib.stream()),
+                   'attn_bwd')
+        return dqkv, None, None, None, None, None, None, None
+
+
+def packed_attention(qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.Tensor, num_heads: int,
+                     num_kv_heads: int, head_dim: int, scale: float | None = None,
+                     window: int | None = None) -> torch.Tensor:
+    """Causal attention over a packed token stream.
+
+    ``qkv`` is ``[T, (Hq + 2*Hkv) * D]`` laid out ``q heads | k heads | v heads`` per row (the output
+    of the fused QKV projection, RoPE already applied).  Token ``t`` attends keys ``j`` with
+    ``seg_start[t] <= j <= t`` (and ``j > t - window`` if a sliding window is set).  Returns ``[T, Hq*D]``.
+    """
+    scale = (1.0 / math.sqrt(head_dim)) if scale is None else scale
+    w = int(window) if window else 0
+    if _lib.use_kernels(qkv):
+        return _PackedAttentionFn.apply(qkv.contiguous(), seg_start, seg_end, num_heads, num_kv_heads, head_dim,
+                                        scale, w)
+    t = qkv.shape[0]
+    q, k, v = qkv.split([num_heads * head_dim, num_kv_heads * head_dim, num_kv_heads * head_dim], dim=-1)
+    o = attention_ref(q.reshape(t, num_heads, head_dim), k.reshape(t, num_kv_heads, head_dim),
+                      v.reshape(t, num_kv_heads, head_dim), seg_start, scale, w or None)
+    return o.reshape(t, num_heads * head_dim)
+
+
+# ---------------------------------------------------------------------------------------------------
+# 4-D additive masks (eager / sdpa implementations, and the reference's public helper)
+# ---------------------------------------------------------------------------------------------------
+def prepare_4d_causal_attention_mask(attention_mask: torch.Tensor | None, input_shape: tuple[int, int],
+                                     inputs_embeds: torch.Tensor, past_key_values_length: int = 0,
+                                     sliding_window: int | None = None) -> torch.Tensor:
+    """Additive ``[B, 1, S, S]`` mask (0 = attend, dtype-min = blocked): causal, block-diagonal over the
+    documents of a pack (segment ids), pad keys blocked.  Vectorised: no Python loop over tokens
+    (reference loops over every token, attention_op.py:286-301)."""
+    assert past_key_values_length == 0, 'training-only framework: no KV cache'
+    bsz, seq = input_shape
+    device, dtype = inputs_embeds.device, inputs_embeds.dtype
+    start, _ = segment_bounds(attention_mask, bsz, seq, device)
+    start = start.view(bsz, seq) - (torch.arange(bsz, device=device, dtype=torch.int32) * seq)[:, None]
+    idx = torch.arange(seq, device=device)
+    allowed = (idx[None, None, :] <= idx[None, :, None]) & (idx[None, None, :] >= start[:, :, None])
+    if sliding_window:
+        allowed &= idx[None, None, :] > (idx[None, :, None] - sliding_window)
+    if attention_mask is not None:
+        allowed &= attention_mask.to(device).bool()[:, None, :]
+        # fully masked (pad) query rows attend to themselves so softmax stays finite
+        allowed |= torch.eye(seq, dtype=torch.bool, device=device)[None] & ~attention_mask.to(device).bool()[:, :, None]
+    mask = torch.zeros((bsz, 1, seq, seq), dtype=dtype, device=device)
+    return mask.masked_fill(~allowed[:, None], torch.finfo(dtype).min)
+
+
+def get_unpad_data(attention_mask: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor, int]:
+    """(indices of non-pad tokens, cu_seqlens int32 over documents, max document length).
+    API parity with the reference's ``_get_unpad_data`` (attention_op.py:388-412); the training path
+    does not use it (it would force a host sync)."""
+    bsz, seq = attention_mask.shape
+    start, end = segment_bounds(attention_mask, bsz, seq, attention_mask.device)
+    flat = attention_mask.reshape(-1)
+    keep = flat != 0
+    indices = torch.nonzero(keep, as_tuple=False).flatten()
+    idx = torch.arange(bsz * seq, device=attention_mask.device, dtype=torch.int32)
+    is_doc_start = (start == idx) & keep
+    lengths = (end - start)[is_doc_start]
+    cu = torch.nn.functional.pad(torch.cumsum(lengths, 0, dtype=torch.int32), (1, 0))
+    return indices, cu, int(lengths.max().item()) if lengths.numel() else 0
+
+
+def flash_attention_forward(query_states: torch.Tensor, key_states: torch.Tensor, value_states: torch.Tensor,
+                            attention_mask: torch.Tensor | None, query_length: int, is_causal: bool = True,
+                            dropout: float = 0.0, softmax_scale: float | None = None,
+                            sliding_window: int | None = None, **_) -> torch.Tensor:
+    """Reference-compatible entry point: q/k/v ``[B, S, H, D]``, ``attention_mask [B, S]`` of segment ids.
+    Routes to the packed kernel; segment ids are always honoured (fixes SURVEY Appendix B2)."""
+    assert is_causal and dropout == 0.0, 'only causal, dropout-free attention is implemented'
+    bsz, seq, hq, d = query_states.shape
+    hkv = key_states.shape[2]
+    start, end = segment_bounds(attention_mask, bsz, seq, query_states.device)
+    qkv = torch.cat((query_states.reshape(bsz * seq, hq * d), key_states.reshape(bsz * seq, hkv * d),
+                     value_states.reshape(bsz * seq, hkv * d)), dim=-1)
+    out = packed_attention(qkv, start, end, hq, hkv, d, softmax_scale, sliding_window)
+    return out.view(bsz, seq, hq, d)

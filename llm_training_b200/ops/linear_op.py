@@ -53,3 +53,61 @@ def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = No
         return y
     y = F.linear(x, weight, bias)
     return y if residual is None else y + residual
+
+
+# ---------------------------------------------------------------------------------------------------
+# several projections of the same input as ONE GEMM (q|k|v, gate|up)
+# ---------------------------------------------------------------------------------------------------
+def _adjacent_rows_view(weights: tuple[torch.Tensor, ...]) -> torch.Tensor | None:
+    """If the weights are consecutive row blocks of one buffer (the flat parameter layout built by
+    ``parallel.ParamStore``), return the fused ``[sum(out_i), in]`` view without copying."""
+    first = weights[0]
+    if not all(w.is_contiguous() and w.dim() == 2 and w.shape[1] == first.shape[1] and w.dtype == first.dtype
+               for w in weights):
+        return None
+    expected = first.data_ptr()
+    for w in weights:
+        if w.data_ptr() != expected or w.untyped_storage().data_ptr() != first.untyped_storage().data_ptr():
+            return None
+        expected += w.numel() * w.element_size()
+    rows = sum(w.shape[0] for w in weights)
+    return torch.as_strided(first.detach(), (rows, first.shape[1]), (first.shape[1], 1))
+
+
+class _MultiLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, *weights: torch.Tensor) -> torch.Tensor:
+        fused = _adjacent_rows_view(weights)
+        if fused is None:
+            fused = torch.cat([w.detach() for w in weights], dim=0)
+        x2 = _as_2d(x)
+        y = gemm(x2, fused)
+        ctx.save_for_backward(x2, fused)
+        ctx.x_shape = x.shape
+        ctx.splits = [w.shape[0] for w in weights]
+        return y.view(*x.shape[:-1], fused.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x2, fused = ctx.saved_tensors
+        dy2 = _as_2d(dy)
+        dx = gemm(dy2, fused, b_mn_major=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
+        dws: list = [None] * len(ctx.splits)
+        if any(ctx.needs_input_grad[1:]):
+            dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+            dws = list(dw.split(ctx.splits, dim=0))
+        return (dx, *dws)
+
+
+def multi_linear(x: torch.Tensor, weights: list[torch.Tensor], biases: list[torch.Tensor | None] | None = None
+                 ) -> torch.Tensor:
+    """``concat_i(x @ W_i^T (+ b_i))`` along the last dim, computed as a single GEMM on CUDA."""
+    if _lib.use_kernels(x) and all(w.dtype == torch.bfloat16 for w in weights) and x.shape[-1] % 8 == 0:
+        y = _MultiLinearFn.apply(x, *weights)
+    else:
+        y = F.linear(x, torch.cat(list(weights), dim=0))
+    if biases is not None and any(b is not None for b in biases):
+        full = torch.cat([b if b is not None else torch.zeros(w.shape[0], dtype=y.dtype, device=y.device)
+                          for w, b in zip(weights, biases)])
+        y = y + full
+    return y

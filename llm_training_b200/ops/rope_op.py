@@ -31,7 +31,7 @@ class _RopeQKFn(torch.autograd.Function):
     def backward(ctx, d: torch.Tensor):
         pos, cos_t, sin_t = ctx.saved_tensors
         n_rot_heads, head_dim = ctx.meta
-        d = d.contiguous()
+        d = d.clone(memory_format=torch.contiguous_format)   # never rotate the caller's gradient in place
         tokens = d.shape[0]
         _lib.check(_lib.lib().llmt_rope_inplace(_lib.ptr(d), _lib.ptr(pos), _lib.ptr(cos_t), _lib.ptr(sin_t),
                                                 _lib.c_int(tokens), _lib.c_int(n_rot_heads), _lib.c_int(head_dim),
