@@ -1,0 +1,459 @@
+// Packed causal attention, backward, on tcgen05 tensor cores.
+//
+// Replaces flash-attn's varlen backward (reference path: src/llm_training/ops/attention_op.py:606-618 under
+// autograd).  One CTA owns 128 KV rows of one KV head and walks over every (query head of the group, 64-row
+// query block) that can see them; dK / dV accumulate in TMEM across the whole walk (no atomics), dQ is
+// reduced into an fp32 [T, Hq*D] accumulator with coalesced red.global.add.
+//
+// Everything is computed TRANSPOSED so that "thread r <-> TMEM lane r <-> KV row r":
+//   S^T  = K Q^T            (M=128 kv, N=64 q,  K=D)    A=K  K-major, B=Q  K-major
+//   dP^T = V dO^T           (M=128 kv, N=64 q,  K=D)    A=V  K-major, B=dO K-major
+//   P^T  = exp2(S^T*c - L[q]) masked;  dS^T = P^T o (dP^T - delta[q]) * scale        (threads, bf16 -> smem)
+//   dV  += P^T  dO          (M=128 kv, N=D,     K=64 q) A=P^T  K-major, B=dO MN-major
+//   dK  += dS^T Q           (M=128 kv, N=D,     K=64 q) A=dS^T K-major, B=Q  MN-major
+//   dQ^T = K^T dS^T         (M=D,      N=64 q,  K=128)  A=K  MN-major,  B=dS^T MN-major   -> red.add to dq_acc
+// TMEM: S^T @0 (64) | dP^T @64 (64) | dQ^T @128 (64) | dK @256 (128) | dV @384 (128)  = 512 columns, 1 CTA / SM.
+// The head dimension is always padded to 128 here (TMA zero-fills the out-of-range columns).
+#include <cuda.h>
+
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace llmt {
+namespace attn {
+
+using namespace sm100;
+
+int make_tmap_thd(CUtensorMap* out, const void* ptr, int64_t tokens, int heads, int head_dim, int64_t row_stride,
+                  int box_rows);
+
+constexpr int kBwdKV = 128;   // kv rows per CTA
+constexpr int kBwdQ = 64;     // q rows per step
+constexpr int kBwdD = 128;    // padded head dim
+constexpr int kBwdThreads = 192;
+
+struct BwdCfg {
+  static constexpr int kKBytes = kBwdKV * kBwdD * 2;        // 32 KB : 2 boxes [128][64]
+  static constexpr int kQBytes = kBwdQ * kBwdD * 2;         // 16 KB : 2 boxes [64][64]
+  static constexpr int kPBytes = kBwdKV * kBwdQ * 2;        // 16 KB : 1 box  [128][64]
+  static constexpr int kKOff = 0;
+  static constexpr int kVOff = kKOff + kKBytes;
+  static constexpr int kQOff = kVOff + kKBytes;             // 2 stages
+  static constexpr int kDOOff = kQOff + 2 * kQBytes;        // 2 stages
+  static constexpr int kPOff = kDOOff + 2 * kQBytes;
+  static constexpr int kDSOff = kPOff + kPBytes;
+  static constexpr int kMetaOff = kDSOff + kPBytes;         // 2 x {L[64], delta[64], seg_start[64]}
+  static constexpr int kMetaBytes = 2 * 3 * 64 * 4;
+  static constexpr int kBarOff = kMetaOff + kMetaBytes;
+  // kv_full, qdo_full[2], qdo_empty[2], st_full, st_empty, pds_full, pds_empty, dq_full, dq_empty, acc_done
+  static constexpr int kNumBars = 12;
+  static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
+  static constexpr int kColST = 0, kColDPT = 64, kColDQT = 128, kColDK = 256, kColDV = 384;
+};
+
+struct BwdParams {
+  const int* seg_start;
+  const int* seg_end;
+  const float* lse;     // [Hq, T] log2 units
+  const float* delta;   // [Hq, T]
+  float* dq_acc;        // [T, Hq*D] fp32, zero-initialised
+  int tokens, hq, hkv, head_dim;
+  float scale, scale_log2;
+  int window;
+};
+
+__device__ __forceinline__ float bwd_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+// delta[h, t] = sum_d O[t, h, d] * dO[t, h, d]   (one warp per (t, h))
+__global__ void __launch_bounds__(256)
+attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                  float* __restrict__ delta, int tokens, int hq, int head_dim) {
+  const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (w >= (int64_t)tokens * hq) return;
+  const int64_t t = w / hq;
+  const int h = (int)(w - t * hq);
+  const __nv_bfloat16* po = o + (t * hq + h) * head_dim;
+  const __nv_bfloat16* pd = d_o + (t * hq + h) * head_dim;
+  float s = 0.f;
+  for (int c = lane * 8; c < head_dim; c += 256) {
+    float a[8], b[8];
+    unpack8(ld_bf16x8(po + c), a);
+    unpack8(ld_bf16x8(pd + c), b);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += a[j] * b[j];
+  }
+  s = warp_sum(s);
+  if (lane == 0) delta[(size_t)h * tokens + t] = s;
+}
+
+// dqkv[t, 0 : Hq*D] = bf16(dq_acc[t, :])
+__global__ void __launch_bounds__(256)
+attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int tokens, int width,
+                       int64_t out_stride) {
+  const int vec_per_row = width >> 3;
+  const int64_t total = (int64_t)tokens * vec_per_row;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / vec_per_row;
+    const int c = (int)(i - t * vec_per_row) << 3;
+    const float4 a = *reinterpret_cast<const float4*>(dq_acc + t * width + c);
+    const float4 b = *reinterpret_cast<const float4*>(dq_acc + t * width + c + 4);
+    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    st_bf16x8(dqkv + t * out_stride + c, pack8(f));
+  }
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,128}
+                const __grid_constant__ CUtensorMap tmQ,     // qkv, box {64,1,64}
+                const __grid_constant__ CUtensorMap tmDO,    // dO [T][Hq][D], box {64,1,64}
+                const __grid_constant__ CUtensorMap tmDKV,   // dqkv, box {64,1,128} (store)
+                BwdParams p) {
+  using C = BwdCfg;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0) __trap();
+
+  const uint32_t bars = sbase + C::kBarOff;
+  const uint32_t kv_full = bars;
+  auto qdo_full = [&](int s) { return bars + 8u * (1 + s); };
+  auto qdo_empty = [&](int s) { return bars + 8u * (3 + s); };
+  const uint32_t st_full = bars + 8u * 5, st_empty = bars + 8u * 6;
+  const uint32_t pds_full = bars + 8u * 7, pds_empty = bars + 8u * 8;
+  const uint32_t dq_full = bars + 8u * 9, dq_empty = bars + 8u * 10;
+  const uint32_t acc_done = bars + 8u * 11;
+  const uint32_t tmem_ptr_smem = bars + 8u * 12;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 12);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.y;                       // kv head
+  const int G = p.hq / p.hkv;
+  const int k0 = (int)blockIdx.x * kBwdKV;        // early kv tiles see the most queries: launched first
+  const int k_last = min(k0 + kBwdKV, p.tokens) - 1;
+  // query blocks that can see this kv tile: q >= k0, q < seg_end[k_last] (bounds are non-decreasing)
+  int q_hi = p.seg_end[k_last] - 1;
+  if (p.window > 0) q_hi = min(q_hi, k_last + p.window - 1);
+  q_hi = min(q_hi, p.tokens - 1);
+  const int i_lo = k0 / kBwdQ;
+  const int nq = q_hi / kBwdQ - i_lo + 1;
+  const int n_total = G * nq;
+
+  if (warp == 4 && lane == 0) {
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(qdo_full(s), 1);
+      mbar_init(qdo_empty(s), 1);
+    }
+    mbar_init(st_full, 1);
+    mbar_init(st_empty, 128);
+    mbar_init(pds_full, 128);
+    mbar_init(pds_empty, 1);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_empty, 128);
+    mbar_init(acc_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 5) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmKV);
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmDO);
+      tma_prefetch_desc(&tmDKV);
+    }
+    tmem_alloc<1>(tmem_ptr_smem, 512);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  if (warp == 5) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      mbar_arrive_expect_tx(kv_full, 2 * C::kKBytes);
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        tma_load_3d(sbase + C::kKOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + g, k0);
+        tma_load_3d(sbase + C::kVOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + p.hkv + g, k0);
+      }
+      for (int it = 0; it < n_total; ++it) {
+        const int st = it & 1;
+        const int h = g * G + it / nq;
+        const int q0 = (i_lo + it % nq) * kBwdQ;
+        mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(qdo_full(st), 2 * C::kQBytes);
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          tma_load_3d(sbase + C::kQOff + st * C::kQBytes + b * (kBwdQ * 128), &tmQ, qdo_full(st), b * 64, h, q0);
+          tma_load_3d(sbase + C::kDOOff + st * C::kQBytes + b * (kBwdQ * 128), &tmDO, qdo_full(st), b * 64, h, q0);
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_st = make_idesc_bf16(kBwdKV, kBwdQ, false, false);   // S^T, dP^T
+      constexpr uint32_t idesc_dkv = make_idesc_bf16(kBwdKV, kBwdD, false, true);   // dV, dK
+      constexpr uint32_t idesc_dq = make_idesc_bf16(kBwdD, kBwdQ, true, true);      // dQ^T
+      const uint32_t ka = sbase + C::kKOff, va = sbase + C::kVOff;
+      const uint32_t pa = sbase + C::kPOff, dsa = sbase + C::kDSOff;
+      auto issue_st = [&](int it) {
+        const int st = it & 1;
+        const uint32_t qa = sbase + C::kQOff + st * C::kQBytes, doa = sbase + C::kDOOff + st * C::kQBytes;
+#pragma unroll
+        for (int kk = 0; kk < kBwdD / 16; ++kk) {
+          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
+          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
+          umma_f16<1>(tmem_base + C::kColST, make_smem_desc(ka + aoff, 0, 1024), make_smem_desc(qa + boff, 0, 1024),
+                      idesc_st, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < kBwdD / 16; ++kk) {
+          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
+          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
+          umma_f16<1>(tmem_base + C::kColDPT, make_smem_desc(va + aoff, 0, 1024),
+                      make_smem_desc(doa + boff, 0, 1024), idesc_st, kk != 0);
+        }
+        umma_commit(st_full);
+      };
+      mbar_wait(kv_full, 0);
+      mbar_wait(qdo_full(0), 0);
+      tc_fence_after();
+      issue_st(0);
+      for (int it = 0; it < n_total; ++it) {
+        if (it + 1 < n_total) {
+          mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+          mbar_wait(st_empty, it & 1);           // threads hold S^T / dP^T (it) in registers
+          tc_fence_after();
+          issue_st(it + 1);
+        }
+        mbar_wait(pds_full, it & 1);
+        mbar_wait(dq_empty, (it & 1) ^ 1);
+        tc_fence_after();
+        const int st = it & 1;
+        const uint32_t qa = sbase + C::kQOff + st * C::kQBytes, doa = sbase + C::kDOOff + st * C::kQBytes;
+#pragma unroll
+        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dV += P^T dO
+          umma_f16<1>(tmem_base + C::kColDV, make_smem_desc(pa + kk * 32, 0, 1024),
+                      make_smem_desc(doa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dK += dS^T Q
+          umma_f16<1>(tmem_base + C::kColDK, make_smem_desc(dsa + kk * 32, 0, 1024),
+                      make_smem_desc(qa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < kBwdKV / 16; ++kk) {  // dQ^T = K^T dS^T
+          umma_f16<1>(tmem_base + C::kColDQT, make_smem_desc(ka + kk * 2048, kBwdKV * 128, 1024),
+                      make_smem_desc(dsa + kk * 2048, kBwdKV * 128, 1024), idesc_dq, kk != 0);
+        }
+        umma_commit(qdo_empty(st));
+        umma_commit(pds_empty);
+        umma_commit(dq_full);
+      }
+      umma_commit(acc_done);
+    }
+  } else {
+    // ===== compute warps: thread <-> kv row =====
+    const int r = warp * 32 + lane;
+    const int kvi = k0 + r;
+    const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
+    uint8_t* p_row = smem + C::kPOff + r * 128;
+    uint8_t* ds_row = smem + C::kDSOff + r * 128;
+    const int ldq = p.hq * p.head_dim;
+
+    for (int it = 0; it < n_total; ++it) {
+      const int h = g * G + it / nq;
+      const int q0 = (i_lo + it % nq) * kBwdQ;
+      float* mL = reinterpret_cast<float*>(smem + C::kMetaOff) + (it & 1) * 192;
+      float* mD = mL + 64;
+      int* mS = reinterpret_cast<int*>(mL + 128);
+      if (r < 64) {
+        const int q = q0 + r;
+        const bool ok = q < p.tokens;
+        mL[r] = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
+        mD[r] = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
+      } else {
+        const int q = q0 + r - 64;
+        mS[r - 64] = q < p.tokens ? p.seg_start[q] : 0x7fffffff;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      const bool need_mask = (q0 < k0 + kBwdKV - 1) || (mS[63] > k0) || (p.window > 0);
+
+      mbar_wait(st_full, it & 1);
+      tc_fence_after();
+      uint32_t sv[64];
+      {
+        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[0]);
+        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[32]);
+        tmem_ld_32x32b_x32(t_lane + C::kColST, a);
+        tmem_ld_32x32b_x32(t_lane + C::kColST + 32, b);
+      }
+      tmem_ld_wait();
+      // P^T (fp32, kept in sv)
+#pragma unroll
+      for (int c = 0; c < 64; ++c) {
+        float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c]));
+        if (need_mask) {
+          const int q = q0 + c;
+          const bool valid = (mS[c] <= kvi) && (kvi <= q) && (p.window == 0 || q - kvi < p.window);
+          pv = valid ? pv : 0.f;
+        }
+        sv[c] = __float_as_uint(pv);
+      }
+      mbar_wait(pds_empty, (it & 1) ^ 1);       // dV/dK/dQ MMAs of the previous step have read P^T / dS^T
+#pragma unroll
+      for (int ch = 0; ch < 8; ++ch) {
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(sv[ch * 8 + e]);
+        *reinterpret_cast<bf16x8*>(p_row + ((ch ^ (r & 7)) << 4)) = pack8(f);
+      }
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t dp[32];
+        tmem_ld_32x32b_x32(t_lane + C::kColDPT + half * 32, dp);
+        tmem_ld_wait();
+        if (half == 1) {
+          tc_fence_before();
+          mbar_arrive(st_empty);                // S^T and dP^T are fully in registers
+        }
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int c = half * 32 + ch * 8 + e;
+            f[e] = __uint_as_float(sv[c]) * (__uint_as_float(dp[ch * 8 + e]) - mD[c]) * p.scale;
+          }
+          *reinterpret_cast<bf16x8*>(ds_row + (((half * 4 + ch) ^ (r & 7)) << 4)) = pack8(f);
+        }
+      }
+      fence_proxy_async_smem();
+      mbar_arrive(pds_full);
+
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      {
+        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[0]);
+        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[32]);
+        tmem_ld_32x32b_x32(t_lane + C::kColDQT, a);
+        tmem_ld_32x32b_x32(t_lane + C::kColDQT + 32, b);
+      }
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(dq_empty);
+      if (r < p.head_dim) {                     // lane r of dQ^T is head-dim index r
+        float* dst = p.dq_acc + (size_t)q0 * ldq + (size_t)h * p.head_dim + r;
+        const int nvalid = min(kBwdQ, p.tokens - q0);
+#pragma unroll
+        for (int c = 0; c < 64; ++c)
+          if (c < nvalid) atomicAdd(dst + (size_t)c * ldq, __uint_as_float(sv[c]));
+      }
+    }
+
+    // ---- dK / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
+    mbar_wait(acc_done, 0);
+    tc_fence_after();
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
+      const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
+#pragma unroll
+      for (int c0 = 0; c0 < kBwdD; c0 += 32) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(t_lane + col + c0, o);
+        tmem_ld_wait();
+        uint8_t* box_row = stage + (c0 / 64) * (kBwdKV * 128) + r * 128;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(o[ch * 8 + e]);
+          const int chunk = ((c0 % 64) / 8) + ch;
+          *reinterpret_cast<bf16x8*>(box_row + ((chunk ^ (r & 7)) << 4)) = pack8(f);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        tma_store_3d(&tmDKV, sbase + C::kKOff + b * (kBwdKV * 128), b * 64, p.hq + g, k0);
+        tma_store_3d(&tmDKV, sbase + C::kVOff + b * (kBwdKV * 128), b * 64, p.hq + p.hkv + g, k0);
+      }
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) tmem_dealloc<1>(tmem_base, 512);
+}
+
+}  // namespace attn
+}  // namespace llmt
+
+using namespace llmt;
+using namespace llmt::attn;
+
+// Backward of llmt_attn_fwd.  delta: fp32 [Hq, T] scratch; dq_acc: fp32 [T, Hq*D] scratch, must be ZERO on
+// entry; dqkv: bf16 [T, (Hq+2Hkv)*D] (same row stride as qkv), fully overwritten.
+extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                             float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
+                             int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
+                             cudaStream_t stream) {
+  LLMT_REQUIRE(tokens > 0 && hq > 0 && hkv > 0 && hq % hkv == 0, "attn_bwd: bad head counts %d/%d", hq, hkv);
+  LLMT_REQUIRE(head_dim % 16 == 0 && head_dim <= 128, "attn_bwd: head_dim %d unsupported", head_dim);
+  LLMT_REQUIRE(qkv_stride % 8 == 0, "attn_bwd: qkv stride must be a multiple of 8");
+  {
+    const int64_t warps = (int64_t)tokens * hq;
+    const int64_t blocks = (warps * 32 + 255) / 256;
+    attn_delta_kernel<<<(unsigned)blocks, 256, 0, stream>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
+                                                            delta, tokens, hq, head_dim);
+    int rc = check_launch("attn_delta");
+    if (rc) return rc;
+  }
+  CUtensorMap tkv, tq, tdo, tdkv;
+  int rc = make_tmap_thd(&tkv, qkv, tokens, hq + 2 * hkv, head_dim, qkv_stride, kBwdKV);
+  if (rc) return rc;
+  rc = make_tmap_thd(&tq, qkv, tokens, hq + 2 * hkv, head_dim, qkv_stride, kBwdQ);
+  if (rc) return rc;
+  rc = make_tmap_thd(&tdo, dout, tokens, hq, head_dim, (int64_t)hq * head_dim, kBwdQ);
+  if (rc) return rc;
+  rc = make_tmap_thd(&tdkv, dqkv, tokens, hq + 2 * hkv, head_dim, qkv_stride, kBwdKV);
+  if (rc) return rc;
+  BwdParams p;
+  p.seg_start = seg_start; p.seg_end = seg_end; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
+  p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
+  p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f; p.window = window;
+  static bool configured = false;
+  if (!configured) {
+    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         BwdCfg::kSmemBytes);
+    if (e != cudaSuccess) {
+      set_error("attn_bwd: cannot set %d B dynamic smem: %s", BwdCfg::kSmemBytes, cudaGetErrorString(e));
+      return 2;
+    }
+    configured = true;
+  }
+  dim3 grid((tokens + kBwdKV - 1) / kBwdKV, hkv);
+  attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, p);
+  rc = check_launch("attn_bwd");
+  if (rc) return rc;
+  const int width = hq * head_dim;
+  int64_t blocks = ((int64_t)tokens * width / 8 + 255) / 256;
+  const int64_t cap = (int64_t)num_sms() * 8;
+  if (blocks > cap) blocks = cap;
+  attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, (__nv_bfloat16*)dqkv, tokens, width,
+                                                               qkv_stride);
+  return check_launch("attn_dq_convert");
+}

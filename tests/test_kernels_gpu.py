@@ -222,3 +222,50 @@ def test_adamw_and_sumsq():
                       step=step, grad_scale=coef)
     _close(master.cpu(), mr, rtol=1e-4, atol=1e-5)
     _close(p.cpu(), mr, rtol=1e-2, atol=1e-2)
+
+
+def _attn_case(tokens, hq, hkv, d, doc_lens=None, window=None, batch_rows=None):
+    from llm_training_b200.ops.attention_op import packed_attention
+    torch.manual_seed(0)
+    width = (hq + 2 * hkv) * d
+    qkv = (torch.randn(tokens, width, device=DEV) * 0.7).bfloat16().requires_grad_()
+    if doc_lens is None:
+        start = torch.zeros(tokens, dtype=torch.int32, device=DEV)
+        end = torch.full((tokens,), tokens, dtype=torch.int32, device=DEV)
+    else:
+        assert sum(doc_lens) == tokens
+        s, e, pos = [], [], 0
+        for n in doc_lens:
+            s += [pos] * n
+            e += [pos + n] * n
+            pos += n
+        start = torch.tensor(s, dtype=torch.int32, device=DEV)
+        end = torch.tensor(e, dtype=torch.int32, device=DEV)
+    dout = torch.randn(tokens, hq * d, device=DEV).bfloat16()
+    out = packed_attention(qkv, start, end, hq, hkv, d, None, window)
+    out.backward(dout)
+    ref_in = qkv.detach().float().cpu().requires_grad_()
+    q, k, v = ref_in.split([hq * d, hkv * d, hkv * d], dim=-1)
+    o_ref = ref.attention_ref(q.reshape(tokens, hq, d), k.reshape(tokens, hkv, d), v.reshape(tokens, hkv, d),
+                              start.cpu(), None, window).reshape(tokens, hq * d)
+    o_ref.backward(dout.float().cpu())
+    _close(out.cpu(), o_ref, rtol=2e-2, atol=2e-2)
+    g, gr = qkv.grad.cpu().float(), ref_in.grad
+    for name, sl in (('dq', slice(0, hq * d)), ('dk', slice(hq * d, (hq + hkv) * d)),
+                     ('dv', slice((hq + hkv) * d, width))):
+        err = (g[:, sl] - gr[:, sl]).abs().max().item()
+        bound = 3e-2 * gr[:, sl].abs().max().item() + 2e-2
+        assert err <= bound, f'{name}: max abs err {err} > {bound}'
+
+
+@pytest.mark.parametrize('tokens,hq,hkv,d', [(256, 2, 1, 128), (512, 4, 2, 128), (300, 2, 2, 64), (384, 4, 1, 96)])
+def test_attention_causal(tokens, hq, hkv, d):
+    _attn_case(tokens, hq, hkv, d)
+
+
+def test_attention_packed_documents():
+    _attn_case(640, 4, 2, 128, doc_lens=[100, 28, 200, 56, 256])
+
+
+def test_attention_sliding_window():
+    _attn_case(512, 2, 1, 128, doc_lens=[300, 212], window=96)
