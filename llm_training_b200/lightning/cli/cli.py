@@ -1,0 +1,77 @@
+"""``llm-training fit --config cfg.yaml [--trainer.num_nodes 2] [--ckpt_path ...]``.
+
+Own implementation of the reference's ``LightningCLI`` subclass (src/llm_training/lightning/cli/cli.py:17-83):
+top-level ``seed_everything``, ``float32_matmul_precision``, ``logging_level``, ``trainer``, ``model``, ``data``,
+``output_redirection``, ``tqdm_progress``, ``ckpt_path``; ``ExtraConfig`` is callback 0; the resolved config
+is saved and embedded in checkpoints by ``SaveConfigCallback``; ``SLURM_JOB_ID``/``SLURM_NTASKS`` are dropped
+when ``SLURM_NTASKS == 1`` so an interactive allocation launches its own local ranks (cli.py:76-83).
+"""
+import logging
+import os
+import sys
+from typing import Any
+
+from ..callbacks import ExtraConfig, OutputRedirection, SaveConfigCallback, TQDMProgressBar
+from ..trainer import Trainer, seed_everything
+from .config import instantiate, instantiate_nested, load_config, parse_overrides, set_by_path
+
+logger = logging.getLogger(__name__)
+
+SUBCOMMANDS = ('fit', 'validate')
+
+
+class LightningCLI:
+    def __init__(self, args: list[str] | None = None, run: bool = True, trainer_class: type[Trainer] = Trainer,
+                 save_config_callback: type[SaveConfigCallback] | None = SaveConfigCallback,
+                 trainer_defaults: dict[str, Any] | None = None) -> None:
+        argv = list(sys.argv[1:] if args is None else args)
+        configs, overrides, positional = parse_overrides(argv)
+        self.subcommand = positional[0] if positional and positional[0] in SUBCOMMANDS else None
+        if run and self.subcommand is None:
+            raise SystemExit(f'usage: llm-training {{{",".join(SUBCOMMANDS)}}} --config CONFIG [--key.subkey VALUE ...]')
+        if not configs:
+            raise SystemExit('at least one --config file is required')
+        self.config = load_config(configs)
+        for key, value in overrides.items():
+            set_by_path(self.config, key, value)
+        self.trainer_class = trainer_class
+        self.save_config_callback = save_config_callback
+        self.trainer_defaults = trainer_defaults or {}
+
+        self.seed = None
+        if self.config.get('seed_everything') not in (None, False):
+            seed = self.config['seed_everything']
+            self.seed = seed_everything(None if seed is True else int(seed))
+        self.model = instantiate(self.config['model'])
+        self.datamodule = instantiate(self.config['data']) if self.config.get('data') else None
+        self.trainer = self._instantiate_trainer()
+        if run:
+            self.run()
+
+    def _instantiate_trainer(self) -> Trainer:
+        cfg = dict(self.trainer_defaults)
+        cfg.update(self.config.get('trainer') or {})
+        if os.environ.get('SLURM_NTASKS') == '1':
+            os.environ.pop('SLURM_NTASKS', None)
+            os.environ.pop('SLURM_JOB_ID', None)
+        kwargs = instantiate_nested(cfg)
+        callbacks = list(kwargs.pop('callbacks', None) or [])
+        extra = ExtraConfig(float32_matmul_precision=self.config.get('float32_matmul_precision'),
+                            logging_level=self.config.get('logging_level', logging.INFO))
+        callbacks.insert(0, extra)
+        redirect = self.config.get('output_redirection')
+        callbacks.append(OutputRedirection(**(redirect or {})) if not isinstance(redirect, OutputRedirection)
+                         else redirect)
+        progress = self.config.get('tqdm_progress')
+        if progress is not None or kwargs.get('enable_progress_bar', True):
+            callbacks.append(TQDMProgressBar(**(progress or {})))
+        if self.save_config_callback is not None:
+            callbacks.append(self.save_config_callback(config=self.config))
+        return self.trainer_class(callbacks=callbacks, **kwargs)
+
+    def run(self) -> None:
+        ckpt_path = self.config.get('ckpt_path')
+        if self.subcommand == 'validate':
+            self.trainer.validate(self.model, self.datamodule)
+        else:
+            self.trainer.fit(self.model, self.datamodule, ckpt_path=ckpt_path)

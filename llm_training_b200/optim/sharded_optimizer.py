@@ -1,0 +1,179 @@
+"""Optimizer over the flat shards of :class:`parallel.FlatParamEngine`.
+
+One fused kernel launch per sharding unit does: gradient clip scaling (from the device-side global
+norm), AdamW on the fp32 master slice, and the bf16 write-back — followed by one in-place all-gather per
+unit.  This replaces the reference's per-parameter ``MasterWeightsOptimizer.step`` (bf16->fp32 grad copy,
+AdamW, fp32->bf16 copy; src/llm_training/optim/master_weight_wrapper.py:63-80), ``clip_grad_norm_``
+(fsdp2_precision.py:165-169) and DeepSpeed's FusedAdam + ZeRO partitioned step.
+
+AdamW-family user optimizers (torch.optim.AdamW/Adam, FusedAdamW, the DeepSpeed FusedAdam alias) run on
+the fused kernel; any other optimizer class is instantiated over the fp32 master slices and stepped by
+PyTorch (generic path).  The user's optimizer object stays the owner of ``param_groups`` so LR schedulers
+and LearningRateMonitor keep working unchanged.
+"""
+from typing import Any
+
+import torch
+from torch.optim import Optimizer
+
+from ..ops.adamw_op import adamw_step
+from ..parallel.comm import Comm
+from ..parallel.fsdp import FlatParamEngine
+
+_ADAMW_LIKE = ('AdamW', 'FusedAdamW', 'FusedAdam', 'Adam', 'DeepSpeedCPUAdam')
+
+
+class ShardedOptimizer(Optimizer):
+    def __init__(self, optimizer: Optimizer, engines: list[FlatParamEngine], max_grad_norm: float | None = None,
+                 norm_extra_axes: list[Comm] | None = None) -> None:   # noqa: no super().__init__
+        self._optimizer = optimizer
+        self.engines = engines
+        self.max_grad_norm = max_grad_norm
+        self.norm_extra_axes = norm_extra_axes or []
+        self.fused = type(optimizer).__name__ in _ADAMW_LIKE and len(optimizer.param_groups) == 1
+        if type(optimizer).__name__ == 'Adam' and optimizer.param_groups[0].get('weight_decay', 0) != 0:
+            self.fused = False     # Adam's L2 penalty is not decoupled decay
+        self.step_count = 0
+        self.unit_state: list[dict[str, torch.Tensor]] = []
+        for e in engines:
+            for u in e.units:
+                shard = u.param_shard
+                st: dict[str, torch.Tensor] = {}
+                if shard.dtype != torch.float32:
+                    st['master'] = shard.detach().float().clone()
+                st['exp_avg'] = torch.zeros(u.shard_numel, dtype=torch.float32, device=shard.device)
+                st['exp_avg_sq'] = torch.zeros(u.shard_numel, dtype=torch.float32, device=shard.device)
+                self.unit_state.append(st)
+        self._generic: Optimizer | None = None
+        if not self.fused:
+            self._build_generic()
+        self.last_grad_norm: torch.Tensor | None = None
+
+    # -- the user's optimizer stays the source of truth for hyper-parameters ---------------------------
+    @property
+    def param_groups(self):
+        return self._optimizer.param_groups
+
+    @param_groups.setter
+    def param_groups(self, v):
+        self._optimizer.param_groups = v
+
+    @property
+    def state(self):
+        return self._optimizer.state
+
+    @property
+    def defaults(self):
+        return self._optimizer.defaults
+
+    def __getattr__(self, name: str) -> Any:
+        if name.startswith('_'):
+            raise AttributeError(name)
+        return getattr(self._optimizer, name)
+
+    def __repr__(self) -> str:
+        return f'ShardedOptimizer({type(self._optimizer).__name__}, fused={self.fused})'
+
+    @property
+    def inner_class_name(self) -> str:
+        return type(self._optimizer).__name__
+
+    def _units(self):
+        i = 0
+        for e in self.engines:
+            for u in e.units:
+                yield e, u, self.unit_state[i]
+                i += 1
+
+    def _build_generic(self) -> None:
+        masters = []
+        for _, u, st in self._units():
+            m = st.get('master')
+            if m is None:
+                m = u.param_shard      # fp32 training: step the slice itself
+            st['master_param'] = torch.nn.Parameter(m, requires_grad=True)
+            masters.append(st['master_param'])
+        group = {k: v for k, v in self._optimizer.param_groups[0].items() if k != 'params'}
+        self._generic = type(self._optimizer)(masters, **{k: v for k, v in group.items()
+                                                          if k in self._optimizer.defaults})
+
+    # -- step ------------------------------------------------------------------------------------------
+    def sync_master_from_params(self) -> None:
+        """Call after weights were loaded into the flat buffers (pre-trained weights / checkpoint)."""
+        for _, u, st in self._units():
+            if 'master' in st:
+                st['master'].copy_(u.param_shard)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for e in self.engines:
+            e.finish_backward()
+        norm_sq = None
+        for e in self.engines:
+            ns = e.grad_norm_sq(self.norm_extra_axes)
+            norm_sq = ns if norm_sq is None else norm_sq.add_(ns)
+        self.last_grad_norm = norm_sq.sqrt() if norm_sq is not None else None
+        self.step_count += 1
+        max_norm = float(self.max_grad_norm) if self.max_grad_norm else 0.0
+        if self.fused:
+            g = self._optimizer.param_groups[0]
+            beta1, beta2 = g.get('betas', (0.9, 0.999))
+            for _, u, st in self._units():
+                shard = u.param_shard
+                low = 'master' in st
+                adamw_step(st['master'] if low else shard, st['exp_avg'], st['exp_avg_sq'], u.local_grad(),
+                           shard if (low and shard.dtype == torch.bfloat16) else None, lr=g['lr'], beta1=beta1,
+                           beta2=beta2, eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0),
+                           step=self.step_count, max_norm=max_norm, norm_sq=norm_sq)
+                if low and shard.dtype != torch.bfloat16:
+                    shard.copy_(st['master'])
+        else:
+            clip = 1.0
+            if max_norm > 0 and norm_sq is not None:
+                clip = torch.clamp(max_norm / (norm_sq.sqrt() + 1e-6), max=1.0)
+            for group, src in zip(self._generic.param_groups, self._optimizer.param_groups):
+                for k, v in src.items():
+                    if k != 'params':
+                        group[k] = v
+            for _, u, st in self._units():
+                st['master_param'].grad = u.local_grad().float() * clip
+            self._generic.step()
+            for _, u, st in self._units():
+                if 'master' in st:
+                    u.param_shard.copy_(st['master_param'].data)
+        for e in self.engines:
+            e.gather_params()
+        return loss
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        for e in self.engines:
+            e.zero_grad()
+
+    # -- checkpointing: per-unit shards, keyed by unit name ---------------------------------------------
+    def state_dict(self) -> dict:
+        units = {}
+        for _, u, st in self._units():
+            units[u.name] = {k: v for k, v in st.items() if k in ('master', 'exp_avg', 'exp_avg_sq')}
+        sd = {'step': self.step_count, 'units': units,
+              'param_groups': [{k: v for k, v in g.items() if k != 'params'} for g in self.param_groups]}
+        if self._generic is not None:
+            sd['generic'] = self._generic.state_dict()
+        return sd
+
+    def load_state_dict(self, state_dict: dict) -> None:
+        self.step_count = int(state_dict.get('step', 0))
+        for _, u, st in self._units():
+            saved = state_dict['units'].get(u.name, {})
+            for k, v in saved.items():
+                if k in st:
+                    st[k].copy_(v)
+            if 'master' in st and 'master' not in saved:
+                st['master'].copy_(u.param_shard)
+        for g, saved in zip(self.param_groups, state_dict.get('param_groups', [])):
+            g.update(saved)
+        if self._generic is not None and 'generic' in state_dict:
+            self._generic.load_state_dict(state_dict['generic'])
