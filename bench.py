@@ -1,0 +1,296 @@
+#!/usr/bin/env python
+"""Headline benchmark: LLaMA-3-8B pre-training throughput (tokens/s, whole job) with FSDP-style sharding,
+bf16, 8192-token packed sequences, synthetic data, random-init weights (BASELINE.json config 2).
+
+    python bench.py --gpus 1 --steps 5 --warmup 3
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 5 --warmup 3
+    python bench.py --impl reference ...      # the reference arm (unavailable on this image)
+
+Two numbers are measured on the same live model:
+  * ``e2e``   : through the public API — ``Trainer.fit`` on ``CLM`` + ``DummyDataModule``; every timed step
+                copies its batch from pinned host memory to the device and reads the loss back to the host.
+  * ``value`` : the same training step driven directly, inputs already resident on the device, no host read.
+Both are timed with CUDA events on the launching stream between barrier + synchronize, max over ranks.
+The step's working set (16 GB of bf16 weights alone) is far larger than the 126 MB L2, so no explicit flush
+is needed between iterations (stated in ``config.l2``).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MODELS = {
+    'llama-3-8b': dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=32,
+                       num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=8192,
+                       rope_theta=500000.0, rms_norm_eps=1e-5, bos_token_id=128000, eos_token_id=128001),
+    # for smoke runs on small memory / CPU
+    'llama-tiny': dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                       num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=8192),
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons while the timed region runs (B200_PROFILING.md recipe)."""
+    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, gpu_index: int) -> None:
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self) -> None:
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.QUERY}', '--format=csv,noheader,nounits',
+                                          '-lms', '200', '-i', str(self.gpu_index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self) -> None:
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.proc.terminate()
+        sm, smax, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(',')]
+            if len(parts) < 9:
+                continue
+            try:
+                sm.append(float(parts[1]))
+                smax.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, flag in zip(names, parts[5:9]):
+                if flag.lower().startswith('active'):
+                    reasons.add(name)
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': max(smax) if smax else None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def reference_arm(args) -> None:
+    """Run the UNMODIFIED reference from baseline/_ref through its own entry point.  Its stack (Lightning,
+    jsonargparse, DeepSpeed, torchmetrics ...) is not on this image and cannot be installed offline, so the
+    import fails and the arm reports itself unavailable (recorded in DESIGN.md)."""
+    ref = os.path.join(ROOT, 'baseline', '_ref')
+    out = {'impl': 'reference'}
+    if not os.path.isdir(os.path.join(ref, 'llm_training')):
+        out['unavailable'] = 'baseline/_ref not installed (pip install --no-index of /root/reference; see DESIGN.md)'
+        print(json.dumps(out))
+        return
+    probe = subprocess.run([sys.executable, '-c', 'import llm_training.cli.main'], cwd='/tmp',
+                           env=dict(os.environ, PYTHONPATH=ref), capture_output=True, text=True)
+    if probe.returncode != 0:
+        last = [l for l in probe.stderr.strip().splitlines() if l.strip()][-1:] or ['import failed']
+        out['unavailable'] = f'reference entry point does not import on this image: {last[0][:160]}'
+        print(json.dumps(out))
+        return
+    out['unavailable'] = 'reference imports but its Lightning/DeepSpeed runtime cannot train on sm_100 here'
+    print(json.dumps(out))
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--model', default='llama-3-8b', choices=sorted(MODELS))
+    ap.add_argument('--seq-len', type=int, default=8192)
+    ap.add_argument('--micro-batch', type=int, default=1)
+    ap.add_argument('--recompute', default='auto', choices=['auto', 'none', 'full', 'selective'])
+    ap.add_argument('--tp', type=int, default=1)
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        reference_arm(args)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    from llm_training_b200.data import DummyDataModule, DummyDataModuleConfig
+    from llm_training_b200.lightning import Callback, FSDP2Strategy, Trainer, seed_everything
+    from llm_training_b200.lms import CLM, CLMConfig
+    from llm_training_b200.ops import _lib
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit('launch multi-GPU runs with torch.distributed.run (see module docstring)')
+    cuda = torch.cuda.is_available()
+    seed_everything(1234)
+
+    recompute = args.recompute
+    if recompute == 'auto':
+        # 8B on one GPU: 128 GB of weights+grads+Adam state leave no room for 35 GB of saved activations
+        recompute = 'full' if (args.model == 'llama-3-8b' and world // args.tp < 2) else 'none'
+    model_cfg = dict(MODELS[args.model], enable_gradient_checkpointing=recompute != 'none',
+                     recompute_granularity='selective' if recompute == 'selective' else 'full',
+                     attn_implementation='flash_attention_2' if cuda else 'sdpa')
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama', model_config=model_cfg),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=1e-5, weight_decay=0.1),
+                   lr_scheduler_class='llm_training.lr_schedulers.CosineAnnealingWarmupLR',
+                   lr_scheduler_kwargs=dict(num_warmup_steps=2, min_lr=1e-6)))))
+    total_steps = args.warmup + args.steps
+    dp = world // args.tp
+    dm = DummyDataModule(DummyDataModuleConfig(batch_size=args.micro_batch, vocab_size=model_cfg['vocab_size'],
+                                               max_length=args.seq_len,
+                                               num_samples=(total_steps + 2) * args.micro_batch * dp, base_seed=11,
+                                               pin_memory=True, num_workers=0))
+
+    tokens_per_step = args.micro_batch * args.seq_len * dp
+
+    class E2ETimer(Callback):
+        """Times optimizer steps [warmup, warmup+steps) of Trainer.fit, reading the loss on the host each step."""
+
+        def __init__(self) -> None:
+            self.ms = None
+            self.h2d = self.d2h = 0
+            self.launch0 = 0
+
+        def on_train_batch_start(self, trainer, module, batch, batch_idx) -> None:
+            if batch_idx == 0:
+                self.h2d = sum(v.numel() * v.element_size() for v in batch.values() if torch.is_tensor(v))
+
+        def on_train_batch_end(self, trainer, module, outputs, batch, batch_idx) -> None:
+            loss_host = float(outputs)          # device -> host read of the step's loss, every step
+            self.d2h = outputs.element_size()
+            self.last_loss = loss_host
+            if batch_idx == args.warmup - 1:    # timed region starts BEFORE the next batch is fetched / copied
+                trainer.strategy.barrier()
+                if cuda:
+                    torch.cuda.synchronize()
+                    self.start = torch.cuda.Event(enable_timing=True)
+                    self.start.record()
+                self.t0 = time.perf_counter()
+            if batch_idx == args.warmup + args.steps - 1:
+                if cuda:
+                    end = torch.cuda.Event(enable_timing=True)
+                    end.record()
+                trainer.strategy.barrier()
+                if cuda:
+                    torch.cuda.synchronize()
+                    self.ms = self.start.elapsed_time(end)
+                else:
+                    self.ms = (time.perf_counter() - self.t0) * 1e3
+                trainer.should_stop = True
+
+    timer = E2ETimer()
+    strategy = FSDP2Strategy(data_parallel_size=dp, tensor_parallel_size=args.tp)
+    trainer = Trainer(strategy=strategy, precision='bf16-true' if cuda else '32-true', logger=False,
+                      callbacks=[timer], max_steps=total_steps, gradient_clip_val=1.0, enable_progress_bar=False,
+                      enable_checkpointing=False, accelerator='auto')
+    trainer.fit(lm, dm)                         # ---- e2e arm: the user's call
+    device = trainer.strategy.root_device
+
+    def reduce_max(x: float) -> float:
+        if dist.is_initialized() and world > 1:
+            t = torch.tensor([x], dtype=torch.float64, device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return x
+
+    e2e_ms = reduce_max(timer.ms) / args.steps
+
+    # ---- device-timed arm: same step, inputs resident on the device, no host read
+    lm.train()
+    g = torch.Generator().manual_seed(99 + rank)
+    ids = torch.randint(0, model_cfg['vocab_size'], (args.micro_batch, args.seq_len), generator=g)
+    batch = {'input_ids': ids.to(device), 'attention_mask': torch.ones_like(ids).to(device),
+             'position_ids': torch.arange(args.seq_len).unsqueeze(0).to(device), 'labels': ids.to(device)}
+    optimizer = trainer.optimizers[0]
+
+    def step() -> None:
+        loss = trainer.strategy.training_step(batch, 0)
+        trainer.strategy.backward(loss)
+        trainer.strategy.optimizer_step(optimizer)
+        optimizer.zero_grad()
+
+    for _ in range(args.warmup):
+        step()
+    sampler = ClockSampler(local_rank)
+    have_lib = cuda and _lib.kernels_available()
+    if have_lib:
+        _lib.lib().llmt_launch_count.restype = __import__('ctypes').c_ulonglong
+    trainer.strategy.barrier()
+    if cuda:
+        torch.cuda.synchronize()
+    if rank == 0 and cuda:
+        sampler.start()
+    launches0 = _lib.lib().llmt_launch_count() if have_lib else 0
+    if cuda:
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        start.record()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    if cuda:
+        end.record()
+    trainer.strategy.barrier()
+    if cuda:
+        torch.cuda.synchronize()
+        ms_total = start.elapsed_time(end)
+    else:
+        ms_total = (time.perf_counter() - t0) * 1e3
+    launches = (_lib.lib().llmt_launch_count() - launches0) if have_lib else 0
+    clocks = sampler.stop() if (rank == 0 and cuda) else {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': []}
+    ms = reduce_max(ms_total) / args.steps
+
+    # model FLOPs per token: 6*N_layer_params + 6*d*V + 6*L*d*T (causal attention, fwd+bwd)
+    c = model_cfg
+    hd = c['hidden_size'] // c['num_attention_heads']
+    layer_params = c['hidden_size'] * (c['num_attention_heads'] + 2 * c['num_key_value_heads']) * hd \
+        + c['hidden_size'] * c['hidden_size'] + 3 * c['hidden_size'] * c['intermediate_size']
+    flops_per_token = 6 * layer_params * c['num_hidden_layers'] + 6 * c['hidden_size'] * c['vocab_size'] \
+        + 6 * c['num_hidden_layers'] * c['hidden_size'] * args.seq_len
+    peak = None
+    try:
+        peak = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['bf16_tflops_sustained']
+    except Exception:
+        pass
+    value = tokens_per_step / (ms / 1e3)
+    e2e_value = tokens_per_step / (e2e_ms / 1e3)
+    if rank == 0:
+        mfu = (value * flops_per_token / 1e12 / (peak * world)) if peak else None
+        print(json.dumps({
+            'metric': 'tokens_per_sec', 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
+            'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'bf16' if cuda else 'fp32', 'data': 'synthetic', 'impl': 'ours',
+            'config': {'model': args.model, 'global_batch': args.micro_batch * dp, 'seq_len': args.seq_len,
+                       'parallelism': f'dp{dp}' + (f'xtp{args.tp}' if args.tp > 1 else ''),
+                       'sharding': 'flat-param ZeRO (optimizer+grad sharded, params resident)',
+                       'optimizer': 'AdamW fp32 master, grad clip 1.0', 'recompute': recompute,
+                       'l2': 'working set (16 GB bf16 weights) >> 126 MB L2, no flush needed'},
+            'mfu_of_measured_sustained_peak': mfu, 'model_tflops_per_gpu': value * flops_per_token / 1e12 / world,
+            'clocks': clocks,
+            'e2e': {'value': e2e_value, 'unit': 'tokens/s', 'ms_per_step': e2e_ms,
+                    'h2d_bytes_per_step': timer.h2d, 'd2h_bytes_per_step': timer.d2h,
+                    'api': 'Trainer.fit(CLM, DummyDataModule)'},
+            'gpu_launches': int(launches), 'last_loss': getattr(timer, 'last_loss', None),
+        }))
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

@@ -6,6 +6,7 @@
 namespace llmt {
 
 static thread_local char g_error[512] = {0};
+static unsigned long long g_launches = 0;  // kernels launched by this library (all threads)
 
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -15,6 +16,7 @@ void set_error(const char* fmt, ...) {
 }
 
 int check_launch(const char* what) {
+  __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED);
   cudaError_t e = cudaPeekAtLastError();
   if (e != cudaSuccess) {
     cudaGetLastError();  // clear
@@ -29,3 +31,7 @@ int check_launch(const char* what) {
 extern "C" const char* llmt_last_error() { return llmt::g_error; }
 
 extern "C" int llmt_abi_version() { return 1; }
+
+// Number of kernels this library has launched since load (bench.py reports the delta as `gpu_launches`).
+extern "C" unsigned long long llmt_launch_count() { return llmt::g_launches; }
+namespace llmt { void count_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); } }

@@ -10,6 +10,7 @@ namespace llmt {
 // ---- error plumbing (C-ABI: functions return 0 on success, message via llmt_last_error) ----------
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+void count_launch();
 
 #define LLMT_REQUIRE(cond, ...)            \
   do {                                     \

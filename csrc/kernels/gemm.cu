@@ -397,6 +397,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
     set_error("gemm launch: %s", cudaGetErrorString(e));
     return 2;
   }
+  count_launch();
   return 0;
 }
 
