@@ -1,0 +1,82 @@
+/* C ABI of the sm_100a kernel library (llm_training_b200/_C/libllmt_kernels.so).
+ *
+ * Conventions
+ *   - every function returns 0 on success; on failure llmt_last_error() describes the problem
+ *   - pointers are device pointers unless stated otherwise; bf16 tensors are passed as void*
+ *   - the caller owns all memory, including scratch buffers (sizes are documented per function)
+ *   - work is enqueued on `stream`; nothing synchronises the device
+ * Citations name the reference code path each kernel replaces (paths relative to the reference repo).
+ */
+#ifndef LLMT_KERNELS_H_
+#define LLMT_KERNELS_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* llmt_last_error(void);
+int llmt_abi_version(void);
+unsigned long long llmt_launch_count(void); /* kernels launched by this library since load */
+
+/* ---- GEMM: C[M,N] = op(A)[M,K] * op(B)[K,N] (+ R), bf16 in, fp32 accumulate, tcgen05/TMEM/TMA ----------
+ * replaces cuBLAS behind nn.Linear (src/llm_training/models/llama/llama_model.py:459-462,421-423,55).
+ * a_mn_major=0: A is [M,K]; 1: A is [K,M].  b_mn_major=0: B is [N,K]; 1: B is [K,N].  out_fp32: C/R fp32.
+ * R may be NULL; R == C accumulates in place.  cta_group 1|2, max_ctas<=0 -> all SMs. */
+int llmt_gemm_bf16(const void* A, const void* B, void* C, const void* R, int M, int N, int K, int64_t lda,
+                   int64_t ldb, int64_t ldc, int64_t ldr, int a_mn_major, int b_mn_major, int out_fp32,
+                   int cta_group, int max_ctas, cudaStream_t stream);
+
+/* ---- packed causal attention (src/llm_training/ops/attention_op.py:538-654, flash-attn varlen) -----------
+ * qkv: bf16 [T, (Hq+2Hkv)*D]; out: bf16 [T, Hq*D]; lse: fp32 [Hq, T] (log2 units); seg_start/seg_end int32 [T].
+ * bwd scratch: delta fp32 [Hq, T]; dq_acc fp32 [T, Hq*D], must be zero on entry. */
+int llmt_attn_fwd(const void* qkv, void* out, float* lse, const int* seg_start, int tokens, int hq, int hkv,
+                  int head_dim, int64_t qkv_stride, float scale, int window, cudaStream_t stream);
+int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc,
+                  void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq, int hkv, int head_dim,
+                  int64_t qkv_stride, float scale, int window, cudaStream_t stream);
+
+/* ---- RMSNorm (src/llm_training/ops/liger_kernel/rms_norm_op.py:15-19) -------------------------------------
+ * bwd scratch: dw_partial fp32 [llmt_rmsnorm_bwd_num_partials(rows), cols]. */
+int llmt_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int rows, int cols, float eps,
+                     cudaStream_t stream);
+int llmt_rmsnorm_bwd_num_partials(int rows);
+int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx, void* dw,
+                     float* dw_partial, int rows, int cols, int dw_is_fp32, int accumulate_dw, cudaStream_t stream);
+
+/* ---- SiLU*mul, RoPE, embedding (+NEFTune) (ops/liger_kernel/swiglu_op.py:36-39, ops/rope_op.py:10-20,
+ *      lms/clm/clm.py:45-78) ---------------------------------------------------------------------------- */
+int llmt_silu_mul_fwd(const void* gate, const void* up, void* out, int rows, int cols, int64_t in_stride,
+                      int64_t out_stride, cudaStream_t stream);
+int llmt_silu_mul_bwd(const void* dout, const void* gate, const void* up, void* dgate, void* dup, int rows, int cols,
+                      int64_t in_stride, int64_t dout_stride, int64_t dgu_stride, cudaStream_t stream);
+int llmt_rope_inplace(void* x, const int* pos, const float* cos_t, const float* sin_t, int tokens, int heads,
+                      int head_dim, int64_t row_stride, int backward, cudaStream_t stream);
+int llmt_embedding_fwd(const int64_t* ids, const void* weight, void* out, const float* noise_scale, int tokens,
+                       int dim, int vocab, uint64_t seed, cudaStream_t stream);
+int llmt_embedding_bwd(const int64_t* ids, const void* dout, void* dweight, int tokens, int dim, int vocab,
+                       int64_t padding_idx, int grad_is_fp32, cudaStream_t stream);
+
+/* ---- cross-entropy / token log-prob on bf16 logits (ops/liger_kernel/cross_entropy_op.py:29-33,
+ *      lms/dpo/dpo.py:110-114) ---------------------------------------------------------------------------- */
+int llmt_ce_fwd(const void* logits, const int64_t* labels, float* lse, float* tgt, int rows, int vocab,
+                int64_t row_stride, int64_t ignore_index, float softcap, cudaStream_t stream);
+int llmt_ce_bwd_inplace(void* logits, const int64_t* labels, const float* lse, const float* row_scale, int rows,
+                        int vocab, int64_t row_stride, int64_t ignore_index, float softcap, cudaStream_t stream);
+int llmt_ce_reduce(const float* lse, const float* tgt, const int64_t* labels, float* out2, int rows,
+                   int64_t ignore_index, cudaStream_t stream);
+
+/* ---- optimizer (optim/master_weight_wrapper.py:63-80, fsdp2_precision.py:165-169) ------------------------
+ * sumsq scratch: partial fp32 [llmt_sumsq_num_partials()]. */
+int llmt_sumsq_num_partials(void);
+int llmt_sumsq(const void* x, int64_t n, int is_fp32, float* partial, float* out, int accumulate, cudaStream_t stream);
+int llmt_adamw(float* master, float* m, float* v, const void* grad, void* param_bf16, int64_t n, int grad_is_fp32,
+               float lr, float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale,
+               float max_norm, const float* norm_sq, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMT_KERNELS_H_ */

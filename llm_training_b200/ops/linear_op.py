@@ -29,7 +29,7 @@ class _LinearFn(torch.autograd.Function):
         ctx.save_for_backward(x2, w)
         ctx.x_shape = x.shape
         ctx.has_residual = residual is not None
-        return y.view(*x.shape[:-1], weight.shape[0])
+        return y if x.dim() == 2 else y.view(*x.shape[:-1], weight.shape[0])
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor):
@@ -85,7 +85,8 @@ class _MultiLinearFn(torch.autograd.Function):
         ctx.save_for_backward(x2, fused)
         ctx.x_shape = x.shape
         ctx.splits = [w.shape[0] for w in weights]
-        return y.view(*x.shape[:-1], fused.shape[0])
+        # no view for the (usual) 2-D packed case: RoPE rotates this tensor in place
+        return y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor):
