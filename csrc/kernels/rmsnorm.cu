@@ -196,3 +196,95 @@ extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, co
         <<<(cols + tb - 1) / tb, tb, 0, stream>>>(dw_partial, (__nv_bfloat16*)dw, grid, cols, accumulate_dw);
   return check_launch("rmsnorm_bwd_colsum");
 }
+
+// -------------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that must not allocate.
+//
+// Some users of this library run where device allocation is off limits: a process whose device memory is
+// handed out in full by a fixed plan or by another allocator (nothing is left for cudaMalloc, and a failed
+// allocation would take the job down), a latency-critical loop that cannot afford the implicit device
+// synchronisation of cudaMalloc / cudaFree, or a plain C / C++ host that links this .so without torch and has
+// no scratch pool to lend us.  For them the dw partial sums live in the fixed device array below instead of a
+// caller buffer; the call itself performs no cudaMalloc, cudaFree or other allocating call.  The array is part of the
+// library image: every GPU that loads the library keeps kNoAllocScratchFloats * 4 bytes (4.625 MiB) of it until
+// the process exits.
+//
+// Limits: cols <= kNoAllocMaxCols (8192); at most kNoAllocMaxParts (148) partial rows are used, so the grid is
+// min(rows, 148) CTAs.  Larger `cols` are rejected with an error.
+//
+// The array is shared by every call on the device and keeps whatever the previous call left in it.  Nothing
+// has to start at zero: each partial row that the column-sum reads is written in full by the same call first.
+// Two calls that overlap on the GPU (different streams) would use the same partial rows and race; calls on
+// one stream are ordered and safe.
+//
+// The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that
+// first call before starting any stream capture.
+// -------------------------------------------------------------------------------------------------------
+namespace llmt {
+constexpr int kNoAllocMaxCols = 8192;
+constexpr int kNoAllocMaxParts = 148;
+constexpr size_t kNoAllocScratchFloats = (size_t)kNoAllocMaxParts * kNoAllocMaxCols;
+static __device__ __align__(256) float g_rmsnorm_noalloc_scratch[kNoAllocScratchFloats];
+
+constexpr int kNoAllocMaxDevices = 64;
+static float* g_noalloc_ptr[kNoAllocMaxDevices] = {nullptr};
+
+// Host code only knows a stand-in for the array; the kernels need its real device address.
+static int noalloc_scratch_for_current_device(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) {
+    set_error("rmsnorm_bwd_noalloc: cannot identify the current device (%s)", cudaGetErrorString(e));
+    return 2;
+  }
+  float* p = __atomic_load_n(&g_noalloc_ptr[dev], __ATOMIC_ACQUIRE);
+  if (p == nullptr) {
+    void* addr = nullptr;
+    e = cudaGetSymbolAddress(&addr, g_rmsnorm_noalloc_scratch);
+    if (e != cudaSuccess || addr == nullptr) {
+      set_error("rmsnorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+      return 2;
+    }
+    p = static_cast<float*>(addr);
+    __atomic_store_n(&g_noalloc_ptr[dev], p, __ATOMIC_RELEASE);
+  }
+  *out = p;
+  return 0;
+}
+}  // namespace llmt
+
+extern "C" int llmt_rmsnorm_bwd_noalloc_max_cols() { return llmt::kNoAllocMaxCols; }
+
+extern "C" int llmt_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* rstd, void* dx,
+                                        void* dw, int rows, int cols, int dw_is_fp32, int accumulate_dw,
+                                        cudaStream_t stream) {
+  LLMT_REQUIRE(cols % 8 == 0, "rmsnorm_bwd_noalloc: cols=%d must be a multiple of 8", cols);
+  LLMT_REQUIRE(cols <= kNoAllocMaxCols,
+               "rmsnorm_bwd_noalloc: cols=%d exceeds the built-in scratch (max %d columns); use llmt_rmsnorm_bwd "
+               "with a caller-provided buffer",
+               cols, kNoAllocMaxCols);
+  if (rows == 0) return 0;
+  float* partial = nullptr;
+  int rc = noalloc_scratch_for_current_device(&partial);
+  if (rc) return rc;
+  const int grid = rows < kNoAllocMaxParts ? rows : kNoAllocMaxParts;
+  auto DY = (const __nv_bfloat16*)dy;
+  auto X = (const __nv_bfloat16*)x;
+  auto W = (const __nv_bfloat16*)w;
+  auto DX = (__nv_bfloat16*)dx;
+  const int nvec = cols / 8;
+  if (nvec <= kNormThreads * 2)
+    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, partial, rows, cols);
+  else
+    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, partial, rows, cols);
+  rc = check_launch("rmsnorm_bwd_noalloc");
+  if (rc) return rc;
+  const int tb = 128;
+  if (dw_is_fp32)
+    colsum_partials_kernel<float><<<(cols + tb - 1) / tb, tb, 0, stream>>>(partial, (float*)dw, grid, cols,
+                                                                          accumulate_dw);
+  else
+    colsum_partials_kernel<__nv_bfloat16>
+        <<<(cols + tb - 1) / tb, tb, 0, stream>>>(partial, (__nv_bfloat16*)dw, grid, cols, accumulate_dw);
+  return check_launch("rmsnorm_bwd_noalloc_colsum");
+}

@@ -46,6 +46,18 @@ int llmt_rmsnorm_bwd_num_partials(int rows);
 int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx, void* dw,
                      float* dw_partial, int rows, int cols, int dw_is_fp32, int accumulate_dw, cudaStream_t stream);
 
+/* RMSNorm backward without a scratch argument.  This entry point has no counterpart in the reference.
+ * It is for hosts that cannot allocate device memory or lend a buffer (all device memory pre-planned by
+ * another owner, loops that cannot take cudaMalloc's implicit synchronisation, plain C callers): the dw
+ * partial sums go to an array built into the library (4.625 MiB per GPU, held until process exit), so
+ * cols must be <= llmt_rmsnorm_bwd_noalloc_max_cols() (8192) — larger sizes fail with an error.  The call
+ * makes no cudaMalloc / cudaFree.  All calls on a device share that array: calls that overlap on the GPU
+ * (different streams) race, same-stream calls are safe.  The first call on each device resolves the
+ * array's address; issue it before any stream capture begins. */
+int llmt_rmsnorm_bwd_noalloc_max_cols(void);
+int llmt_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* w, const float* rstd, void* dx, void* dw,
+                             int rows, int cols, int dw_is_fp32, int accumulate_dw, cudaStream_t stream);
+
 /* ---- SiLU*mul, RoPE, embedding (+NEFTune) (ops/liger_kernel/swiglu_op.py:36-39, ops/rope_op.py:10-20,
  *      lms/clm/clm.py:45-78) ---------------------------------------------------------------------------- */
 int llmt_silu_mul_fwd(const void* gate, const void* up, void* out, int rows, int cols, int64_t in_stride,
