@@ -26,6 +26,7 @@ using namespace sm100;
 
 int make_tmap_thd(CUtensorMap* out, const void* ptr, int64_t tokens, int heads, int head_dim, int64_t row_stride,
                   int box_rows);
+int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, int64_t rows, int64_t cols, int box_cols, int box_rows);
 
 constexpr int kBwdKV = 128;   // kv rows per CTA
 constexpr int kBwdQ = 64;     // q rows per step
@@ -42,7 +43,9 @@ struct BwdCfg {
   static constexpr int kDOOff = kQOff + 2 * kQBytes;        // 2 stages
   static constexpr int kPOff = kDOOff + 2 * kQBytes;
   static constexpr int kDSOff = kPOff + kPBytes;
-  static constexpr int kMetaOff = kDSOff + kPBytes;         // 2 x {L[64], delta[64], seg_start[64]}
+  static constexpr int kDQOff = kDSOff + kPBytes;           // fp32 [64 q][128 d] staging for the TMA reduce-add
+  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB
+  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 2 x {L[64], delta[64], seg_start[64]}
   static constexpr int kMetaBytes = 2 * 3 * 64 * 4;
   static constexpr int kBarOff = kMetaOff + kMetaBytes;
   // kv_full, qdo_full[2], qdo_empty[2], st_full, st_empty, pds_full, pds_empty, dq_full, dq_empty, acc_done
@@ -113,6 +116,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
                 const __grid_constant__ CUtensorMap tmQ,     // qkv, box {64,1,64}
                 const __grid_constant__ CUtensorMap tmDO,    // dO [T][Hq][D], box {64,1,64}
                 const __grid_constant__ CUtensorMap tmDKV,   // dqkv, box {64,1,128} (store)
+                const __grid_constant__ CUtensorMap tmDQ,    // dq_acc fp32 [T][Hq*D], box {128, 64}, no swizzle
                 BwdParams p) {
   using C = BwdCfg;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -131,9 +135,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 12);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = blockIdx.y;                       // kv head
+  // launch order = longest job first: blockIdx.x (fast axis) walks the kv heads, blockIdx.y the kv tiles, so the
+  // early tiles (which see the most queries) of EVERY head start before any light tile
+  const int g = blockIdx.x;                       // kv head
   const int G = p.hq / p.hkv;
-  const int k0 = (int)blockIdx.x * kBwdKV;        // early kv tiles see the most queries: launched first
+  const int k0 = (int)blockIdx.y * kBwdKV;
   const int k_last = min(k0 + kBwdKV, p.tokens) - 1;
   // query blocks that can see this kv tile: q >= k0, q < seg_end[k_last] (bounds are non-decreasing)
   int q_hi = p.seg_end[k_last] - 1;
@@ -164,6 +170,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       tma_prefetch_desc(&tmQ);
       tma_prefetch_desc(&tmDO);
       tma_prefetch_desc(&tmDKV);
+      tma_prefetch_desc(&tmDQ);
     }
     tmem_alloc<1>(tmem_ptr_smem, 512);
     tmem_relinquish<1>();
@@ -266,7 +273,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
     const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
     uint8_t* p_row = smem + C::kPOff + r * 128;
     uint8_t* ds_row = smem + C::kDSOff + r * 128;
-    const int ldq = p.hq * p.head_dim;
 
     for (int it = 0; it < n_total; ++it) {
       const int h = g * G + it / nq;
@@ -349,14 +355,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(dq_empty);
-      if (r < p.head_dim) {                     // lane r of dQ^T is head-dim index r
-        float* dst = p.dq_acc + (size_t)q0 * ldq + (size_t)h * p.head_dim + r;
-        const int nvalid = min(kBwdQ, p.tokens - q0);
+      // dQ^T tile [lane = d][col = q] -> smem [q][d] fp32 (lanes are consecutive d: conflict-free), then ONE
+      // TMA reduce-add of the 64 x 128 tile into dq_acc (replaces 8192 scalar atomics per step)
+      if (threadIdx.x == 0) tma_store_wait_read<0>();     // previous reduce has finished reading the staging tile
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      {
+        float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
 #pragma unroll
-        for (int c = 0; c < 64; ++c)
-          if (c < nvalid) atomicAdd(dst + (size_t)c * ldq, __uint_as_float(sv[c]));
+        for (int c = 0; c < 64; ++c) stage[c * kBwdD + r] = __uint_as_float(sv[c]);
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (threadIdx.x == 0) {
+        tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, h * p.head_dim, q0);
+        tma_store_commit();
       }
     }
+    if (threadIdx.x == 0) tma_store_wait<0>();
 
     // ---- dK / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
     mbar_wait(acc_done, 0);
@@ -431,6 +446,9 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   if (rc) return rc;
   rc = make_tmap_thd(&tdkv, dqkv, tokens, hq + 2 * hkv, head_dim, qkv_stride, kBwdKV);
   if (rc) return rc;
+  CUtensorMap tdq;
+  rc = make_tmap_f32_2d(&tdq, dq_acc, tokens, (int64_t)hq * head_dim, kBwdD, kBwdQ);
+  if (rc) return rc;
   BwdParams p;
   p.seg_start = seg_start; p.seg_end = seg_end; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
@@ -445,8 +463,8 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
     }
     configured = true;
   }
-  dim3 grid((tokens + kBwdKV - 1) / kBwdKV, hkv);
-  attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, p);
+  dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
+  attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
   rc = check_launch("attn_bwd");
   if (rc) return rc;
   const int width = hq * head_dim;

@@ -365,6 +365,34 @@ int make_tmap_thd(CUtensorMap* out, const void* ptr, int64_t tokens, int heads, 
   return 0;
 }
 
+
+// fp32 row-major [rows][cols] tensor map without swizzle (used for the dQ reduce-add tile)
+int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, int64_t rows, int64_t cols, int box_cols, int box_rows) {
+  CUtensorMap probe;
+  (void)probe;
+  void* sym = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &q) != cudaSuccess ||
+      q != cudaDriverEntryPointSuccess) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return 3;
+  }
+  EncodeTiledFn fn = reinterpret_cast<EncodeTiledFn>(sym);
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 4};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("fp32 tensor map encode failed (%d): rows=%lld cols=%lld box=%dx%d", (int)r, (long long)rows,
+              (long long)cols, box_cols, box_rows);
+    return 3;
+  }
+  return 0;
+}
+
 template <int DPAD>
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to, const FwdParams& p,
                cudaStream_t stream) {

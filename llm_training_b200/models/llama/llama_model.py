@@ -19,7 +19,8 @@ import torch
 import torch.utils.checkpoint
 from torch import nn
 
-from ...ops import embedding, linear, multi_linear, neftune_noise_scale, silu_mul_fused
+from ...ops import (embedding, linear, multi_linear, neftune_noise_scale, norm_multi_linear, silu_mul_fused,
+                    swiglu_down_linear)
 from ..decoder import PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
@@ -48,9 +49,18 @@ class LlamaMLP(nn.Module):
         self.up_proj = nn.Linear(self.hidden_size, self.intermediate_size, bias=config.mlp_bias)
         self.down_proj = nn.Linear(self.intermediate_size, self.hidden_size, bias=config.mlp_bias)
 
-    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None, tp: Any = None) -> torch.Tensor:
-        gate_up = multi_linear(x, [self.gate_proj.weight, self.up_proj.weight],
-                               [self.gate_proj.bias, self.up_proj.bias])
+    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None, tp: Any = None,
+                pre_norm: nn.Module | None = None) -> torch.Tensor:
+        """``pre_norm``: the RMSNorm to apply to ``x`` first, fused with the gate|up projection."""
+        no_bias = self.gate_proj.bias is None and self.down_proj.bias is None
+        if pre_norm is not None:
+            gate_up = norm_multi_linear(x, pre_norm.weight, pre_norm.variance_epsilon,
+                                        [self.gate_proj.weight, self.up_proj.weight])
+        else:
+            gate_up = multi_linear(x, [self.gate_proj.weight, self.up_proj.weight],
+                                   [self.gate_proj.bias, self.up_proj.bias])
+        if tp is None and no_bias:
+            return swiglu_down_linear(gate_up, self.down_proj.weight, residual)
         act = silu_mul_fused(gate_up)
         if tp is not None:
             return tp.row_linear(act, self.down_proj.weight, self.down_proj.bias, residual)
@@ -77,12 +87,16 @@ class LlamaAttention(nn.Module):
         self.v_proj = nn.Linear(self.hidden_size, self.num_key_value_heads * self.head_dim, bias=bias)
         self.o_proj = nn.Linear(self.num_heads * self.head_dim, self.hidden_size, bias=bias)
 
-    def forward(self, hidden_states: torch.Tensor, ctx: PackedContext, residual: torch.Tensor | None = None
-                ) -> torch.Tensor:
+    def forward(self, hidden_states: torch.Tensor, ctx: PackedContext, residual: torch.Tensor | None = None,
+                pre_norm: nn.Module | None = None) -> torch.Tensor:
         tp = ctx.tp
         shards = 1 if tp is None else tp.size
-        qkv = multi_linear(hidden_states, [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
-                           [self.q_proj.bias, self.k_proj.bias, self.v_proj.bias])
+        if pre_norm is not None:
+            qkv = norm_multi_linear(hidden_states, pre_norm.weight, pre_norm.variance_epsilon,
+                                    [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight])
+        else:
+            qkv = multi_linear(hidden_states, [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
+                               [self.q_proj.bias, self.k_proj.bias, self.v_proj.bias])
         attn = attention_core(
             qkv, ctx, num_heads=self.num_heads // shards, num_kv_heads=self.num_key_value_heads // shards,
             head_dim=self.head_dim, impl=self.config._attn_implementation, window=self.sliding_window,
@@ -111,6 +125,10 @@ class LlamaDecoderLayer(nn.Module):
 
     def forward(self, hidden_states: torch.Tensor, ctx: PackedContext) -> torch.Tensor:
         tp = ctx.tp
+        if tp is None and not self.config.attention_bias and not self.config.mlp_bias:
+            # norm + projection fused (normalised activations are recomputed in backward, not stored)
+            hidden_states = self.self_attn(hidden_states, ctx, residual=hidden_states, pre_norm=self.input_layernorm)
+            return self.mlp(hidden_states, residual=hidden_states, pre_norm=self.post_attention_layernorm)
         normed = self.input_layernorm(hidden_states)
         if tp is not None:
             normed = tp.gather_sequence(normed)          # SP: [T/tp, d] -> [T, d]

@@ -9,6 +9,7 @@ from .attention_op import (flash_attention_forward, get_unpad_data, packed_atten
 from .cross_entropy_op import (cross_entropy, fused_linear_cross_entropy,
                                fused_linear_logprob, shift_labels)
 from .embedding_op import embedding, neftune_noise_scale
+from .fused_blocks import norm_multi_linear, swiglu_down_linear
 from .linear_op import linear, multi_linear
 from .rms_norm_op import rms_norm
 from .rope_op import apply_rope, rope_qk_packed, rotate_half

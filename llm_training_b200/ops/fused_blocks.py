@@ -1,0 +1,99 @@
+"""Block-level fusions that trade a cheap elementwise recompute for activation memory.
+
+``norm_multi_linear``   RMSNorm followed by one or several projections of the same input (q|k|v, gate|up)
+``swiglu_down_linear``  SiLU(gate)*up followed by the down projection (+ residual)
+
+The reference saves the normalised activations and the SwiGLU product for backward (Liger ops feeding
+``nn.Linear``; models/llama/llama_model.py:283,427).  Here only the GEMM *inputs that cannot be rebuilt cheaply*
+are saved — the layer input ``x`` + ``rstd`` and the ``gate|up`` GEMM output — and the bandwidth-bound
+RMSNorm / SiLU·mul forward kernels are re-run in backward.  Per LLaMA-3-8B layer at 8192 tokens this drops
+352 MB of saved activations (2 x 64 MB normed inputs + 224 MB SwiGLU output) for ~0.1 ms of recompute, which is
+what lets the 8B model train on ONE 180 GB GPU without layer-level activation checkpointing.
+"""
+import torch
+
+from . import _lib
+from .gemm_op import gemm
+from .linear_op import _adjacent_rows_view, _as_2d, linear, multi_linear
+from .rms_norm_op import rms_norm, rmsnorm_bwd_raw, rmsnorm_fwd_raw
+from .swiglu_op import silu_mul_bwd_raw, silu_mul_fused, silu_mul_fwd_raw
+
+
+class _NormMultiLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, norm_weight: torch.Tensor, eps: float, *weights: torch.Tensor):
+        x2 = _as_2d(x)
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        nw = norm_weight if norm_weight.dtype == torch.bfloat16 else norm_weight.to(torch.bfloat16)
+        xn, rstd = rmsnorm_fwd_raw(x2, nw, eps)
+        fused = _adjacent_rows_view(weights)
+        if fused is None:
+            fused = torch.cat([w.detach() for w in weights], dim=0)
+        y = gemm(xn, fused)
+        ctx.save_for_backward(x2, nw, rstd, fused)
+        ctx.eps = eps
+        ctx.x_shape = x.shape
+        ctx.splits = [w.shape[0] for w in weights]
+        ctx.norm_dtype = norm_weight.dtype
+        return y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x2, nw, rstd, fused = ctx.saved_tensors
+        dy2 = _as_2d(dy)
+        xn, _ = rmsnorm_fwd_raw(x2, nw, ctx.eps, want_rstd=False)          # recompute (bandwidth-bound, cheap)
+        dws: list = [None] * len(ctx.splits)
+        if any(ctx.needs_input_grad[3:]):
+            dws = list(gemm(dy2, xn, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0))
+        del xn
+        dxn = gemm(dy2, fused, b_mn_major=True)
+        dx, dnw = rmsnorm_bwd_raw(dxn, x2, nw, rstd)
+        return (dx.view(ctx.x_shape), dnw.to(ctx.norm_dtype), None, *dws)
+
+
+def norm_multi_linear(x: torch.Tensor, norm_weight: torch.Tensor, eps: float, weights: list[torch.Tensor]
+                      ) -> torch.Tensor:
+    """``concat_i(rms_norm(x) @ W_i^T)``; the normalised activations are not kept for backward."""
+    if (_lib.use_kernels(x) and all(w.dtype == torch.bfloat16 for w in weights) and x.shape[-1] % 8 == 0
+            and x.shape[-1] <= 16384):
+        return _NormMultiLinearFn.apply(x, norm_weight, eps, *weights)
+    return multi_linear(rms_norm(x, norm_weight, eps), weights)
+
+
+class _SwiGLUDownFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, gate_up: torch.Tensor, w_down: torch.Tensor, residual: torch.Tensor | None):
+        gu = _as_2d(gate_up)
+        if not gu.is_contiguous():
+            gu = gu.contiguous()
+        act = silu_mul_fwd_raw(gu)
+        w = _as_2d(w_down)
+        r2 = _as_2d(residual) if residual is not None else None
+        y = gemm(act, w, residual=r2)
+        ctx.save_for_backward(gu, w)
+        ctx.shape = gate_up.shape
+        ctx.has_residual = residual is not None
+        return y if gate_up.dim() == 2 else y.view(*gate_up.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        gu, w = ctx.saved_tensors
+        dy2 = _as_2d(dy)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            act = silu_mul_fwd_raw(gu)                                       # recompute
+            dw = gemm(dy2, act, a_mn_major=True, b_mn_major=True)
+            del act
+        dact = gemm(dy2, w, b_mn_major=True)
+        dgu = silu_mul_bwd_raw(dact, gu)
+        return dgu.view(ctx.shape), dw, (dy if ctx.has_residual else None)
+
+
+def swiglu_down_linear(gate_up: torch.Tensor, w_down: torch.Tensor, residual: torch.Tensor | None = None
+                       ) -> torch.Tensor:
+    """``(silu(gate) * up) @ W_down^T (+ residual)`` with ``gate_up[..., :F] | gate_up[..., F:]``."""
+    f = gate_up.shape[-1] // 2
+    if _lib.use_kernels(gate_up) and w_down.dtype == torch.bfloat16 and f % 8 == 0:
+        return _SwiGLUDownFn.apply(gate_up, w_down, residual)
+    return linear(silu_mul_fused(gate_up), w_down, residual=residual)

@@ -6,6 +6,32 @@ from . import _lib
 from .reference import rms_norm_ref
 
 
+def rmsnorm_fwd_raw(x2: torch.Tensor, w: torch.Tensor, eps: float, want_rstd: bool = True
+                    ) -> tuple[torch.Tensor, torch.Tensor | None]:
+    """Kernel launch only (no autograd): x2 is contiguous bf16 [rows, cols], w bf16 [cols]."""
+    rows, cols = x2.shape
+    y = torch.empty_like(x2)
+    rstd = torch.empty(rows, dtype=torch.float32, device=x2.device) if want_rstd else None
+    _lib.check(_lib.lib().llmt_rmsnorm_fwd(_lib.ptr(x2), _lib.ptr(w), _lib.ptr(y), _lib.ptr(rstd), _lib.c_int(rows),
+                                           _lib.c_int(cols), _lib.c_f32(eps), _lib.stream()), 'rmsnorm_fwd')
+    return y, rstd
+
+
+def rmsnorm_bwd_raw(dy2: torch.Tensor, x2: torch.Tensor, w: torch.Tensor, rstd: torch.Tensor
+                    ) -> tuple[torch.Tensor, torch.Tensor]:
+    """-> (dx bf16 [rows, cols], dw fp32 [cols])."""
+    rows, cols = x2.shape
+    L = _lib.lib()
+    dx = torch.empty_like(x2)
+    nparts = L.llmt_rmsnorm_bwd_num_partials(_lib.c_int(rows))
+    partial = torch.empty((nparts, cols), dtype=torch.float32, device=x2.device)
+    dw = torch.empty(cols, dtype=torch.float32, device=x2.device)
+    _lib.check(L.llmt_rmsnorm_bwd(_lib.ptr(dy2), _lib.ptr(x2), _lib.ptr(w), _lib.ptr(rstd), _lib.ptr(dx), _lib.ptr(dw),
+                                  _lib.ptr(partial), _lib.c_int(rows), _lib.c_int(cols), _lib.c_int(1), _lib.c_int(0),
+                                  _lib.stream()), 'rmsnorm_bwd')
+    return dx, dw
+
+
 class _RMSNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:

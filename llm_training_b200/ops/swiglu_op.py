@@ -7,6 +7,30 @@ from . import _lib
 from .reference import silu_mul_ref
 
 
+def silu_mul_fwd_raw(gu: torch.Tensor) -> torch.Tensor:
+    """Kernel launch only: gu contiguous bf16 [rows, 2F] (gate | up) -> [rows, F]."""
+    rows, f2 = gu.shape
+    f = f2 // 2
+    out = torch.empty((rows, f), dtype=gu.dtype, device=gu.device)
+    _lib.check(_lib.lib().llmt_silu_mul_fwd(_lib.ptr(gu), _lib.ctypes.c_void_p(gu.data_ptr() + 2 * f), _lib.ptr(out),
+                                            _lib.c_int(rows), _lib.c_int(f), _lib.c_i64(f2), _lib.c_i64(f),
+                                            _lib.stream()), 'silu_mul_fwd')
+    return out
+
+
+def silu_mul_bwd_raw(d: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
+    """d contiguous bf16 [rows, F], gu [rows, 2F] -> d(gate | up) [rows, 2F]."""
+    rows, f2 = gu.shape
+    f = f2 // 2
+    dgu = torch.empty_like(gu)
+    c = _lib.ctypes.c_void_p
+    _lib.check(_lib.lib().llmt_silu_mul_bwd(_lib.ptr(d), _lib.ptr(gu), c(gu.data_ptr() + 2 * f), _lib.ptr(dgu),
+                                            c(dgu.data_ptr() + 2 * f), _lib.c_int(rows), _lib.c_int(f),
+                                            _lib.c_i64(f2), _lib.c_i64(f), _lib.c_i64(f2), _lib.stream()),
+               'silu_mul_bwd')
+    return dgu
+
+
 class _SiluMulFn(torch.autograd.Function):
     """Operates on a fused ``[rows, 2F]`` tensor (gate | up) so the GEMM before it is one launch and
     the gradient comes back as one ``[rows, 2F]`` tensor for one dgrad GEMM."""

@@ -269,3 +269,61 @@ def test_attention_packed_documents():
 
 def test_attention_sliding_window():
     _attn_case(512, 2, 1, 128, doc_lens=[300, 212], window=96)
+
+
+def test_fused_norm_multi_linear_and_swiglu_down():
+    from llm_training_b200.ops import norm_multi_linear, swiglu_down_linear
+    torch.manual_seed(0)
+    t, d, f = 300, 256, 512
+    x = torch.randn(t, d, device=DEV).bfloat16().requires_grad_()
+    nw = (1 + 0.1 * torch.randn(d, device=DEV)).bfloat16().requires_grad_()
+    w1 = (torch.randn(f, d, device=DEV) * 0.05).bfloat16().requires_grad_()
+    w2 = (torch.randn(f, d, device=DEV) * 0.05).bfloat16().requires_grad_()
+    wd = (torch.randn(d, f, device=DEV) * 0.05).bfloat16().requires_grad_()
+    dy = torch.randn(t, d, device=DEV).bfloat16()
+    gu = norm_multi_linear(x, nw, 1e-5, [w1, w2])
+    y = swiglu_down_linear(gu, wd, x)
+    y.backward(dy)
+    xr, nwr, w1r, w2r, wdr = (v.detach().float().requires_grad_() for v in (x, nw, w1, w2, wd))
+    xn = ref.rms_norm_ref(xr, nwr, 1e-5)
+    yr = (torch.nn.functional.silu(xn @ w1r.t()) * (xn @ w2r.t())) @ wdr.t() + xr
+    yr.backward(dy.float())
+    _close(y, yr)
+    _close(x.grad, xr.grad, rtol=3e-2, atol=3e-2)
+    _close(nw.grad, nwr.grad, rtol=3e-2, atol=0.2)
+    _close(w1.grad, w1r.grad, rtol=3e-2, atol=0.1)
+    _close(w2.grad, w2r.grad, rtol=3e-2, atol=0.1)
+    _close(wd.grad, wdr.grad, rtol=3e-2, atol=0.1)
+
+
+def test_llama_gpu_matches_cpu_fp32():
+    """Whole model on the sm_100a kernels (bf16) vs the same weights through the fp32 PyTorch path on CPU."""
+    import copy
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, attn_implementation='sdpa')
+    cpu = Llama(cfg)
+    gpu = copy.deepcopy(cpu)
+    gpu.config = cfg.model_copy(update={'attn_implementation': 'flash_attention_2'})
+    for m in gpu.modules():
+        if hasattr(m, 'config') and m is not gpu:
+            m.config = gpu.config
+    gpu = gpu.to(DEV, torch.bfloat16)
+    ids = torch.randint(0, 512, (2, 160))
+    mask = torch.ones_like(ids)
+    mask[0, 100:] = 2
+    mask[1, 150:] = 0
+    labels = shift_labels(ids.masked_fill(mask == 0, -100))
+    out_c = cpu(input_ids=ids, attention_mask=mask)
+    loss_c = torch.nn.functional.cross_entropy(out_c.logits.flatten(0, 1).float(), labels.flatten(), ignore_index=-100)
+    loss_c.backward()
+    out_g = gpu(input_ids=ids.to(DEV), attention_mask=mask.to(DEV), skip_logits=True)
+    loss_g = fused_linear_cross_entropy(out_g.normed_hidden_states, gpu.lm_head.weight, labels.flatten().to(DEV))
+    loss_g.backward()
+    assert abs(loss_g.item() - loss_c.item()) < 3e-2, (loss_g.item(), loss_c.item())
+    for (n, pc), (_, pg) in zip(cpu.named_parameters(), gpu.named_parameters()):
+        g, r = pg.grad.float().cpu(), pc.grad
+        err, scale = (g - r).abs().max().item(), r.abs().max().item()
+        assert err <= 0.08 * scale + 2e-3, f'{n}: grad err {err} vs scale {scale}'
