@@ -1,0 +1,113 @@
+"""Multi-process plumbing on CPU/gloo (BASELINE config 1): sharded-vs-single-process parity of the
+flat-parameter engine, gradient accumulation without sync, checkpoint save -> resume."""
+import copy
+
+import pytest
+import torch
+
+from tests.dist_utils import run_distributed
+
+TINY = dict(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+            num_key_value_heads=2, attn_implementation='sdpa')
+
+
+def _make_model(seed: int = 0):
+    from llm_training_b200.models import Llama, LlamaConfig
+    torch.manual_seed(seed)
+    return Llama(LlamaConfig(**TINY))
+
+
+def _batch(seed: int, rows: int = 4, seq: int = 24):
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(0, TINY['vocab_size'], (rows, seq), generator=g)
+    return ids
+
+
+def _loss(model, ids):
+    logits = model(input_ids=ids).logits.float()
+    return torch.nn.functional.cross_entropy(logits[:, :-1].flatten(0, 1), ids[:, 1:].flatten())
+
+
+def _dp_worker(rank: int, world: int, steps: int, accum: int):
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded, init_mesh
+    mesh = init_mesh(world, 1)
+    model = _make_model()
+    engine = apply_fully_sharded(model, mesh.dp)
+    opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1), [engine],
+                           max_grad_norm=1.0)
+    losses = []
+    for step in range(steps):
+        opt.zero_grad()
+        for micro in range(accum):
+            ids = _batch(100 * step + micro)             # global batch of 4 rows
+            local = ids[rank::world]                     # this rank's rows
+            engine.set_requires_gradient_sync(micro == accum - 1)
+            loss = _loss(model, local) / accum
+            loss.backward()
+            if micro != accum - 1:
+                engine._rearm()
+            losses.append(loss.item())
+        opt.step()
+    return {n: p.detach().clone() for n, p in model.named_parameters()}, losses, float(opt.last_grad_norm)
+
+
+@pytest.mark.parametrize('accum', [1, 2])
+def test_sharded_data_parallel_matches_single_process(accum):
+    steps = 3
+    results = run_distributed(_dp_worker, world=2, args=(steps, accum))
+    ref = _make_model()
+    ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.1)
+    for step in range(steps):
+        ropt.zero_grad()
+        for micro in range(accum):
+            ids = _batch(100 * step + micro)
+            # mean over ranks of per-rank means == what the reduce-scatter(avg) produces
+            loss = sum(_loss(ref, ids[r::2]) for r in range(2)) / 2 / accum
+            loss.backward()
+        norm = torch.nn.utils.clip_grad_norm_(ref.parameters(), 1.0)
+        ropt.step()
+    for rank in range(2):
+        params, _, gnorm = results[rank]
+        assert abs(gnorm - float(norm)) < 1e-4 * max(1.0, float(norm))
+        for n, p in ref.named_parameters():
+            assert torch.allclose(params[n], p.detach(), atol=2e-5, rtol=1e-4), n
+    # both ranks hold identical full parameters after the in-place all-gather
+    for n in results[0][0]:
+        assert torch.equal(results[0][0][n], results[1][0][n]), n
+
+
+def _fit_worker(rank: int, world: int, tmpdir: str, ckpt_path, max_steps: int):
+    from llm_training_b200.data import DummyDataModule, DummyDataModuleConfig
+    from llm_training_b200.lightning import FSDP2Strategy, ModelCheckpoint, Trainer, seed_everything
+    from llm_training_b200.lms import CLM, CLMConfig
+    seed_everything(42)
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama', model_config=TINY),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=5e-3),
+                   lr_scheduler_class='llm_training.lr_schedulers.CosineAnnealingWarmupLR',
+                   lr_scheduler_kwargs=dict(num_warmup_steps=2, min_lr=1e-4)))))
+    dm = DummyDataModule(DummyDataModuleConfig(batch_size=2, vocab_size=128, max_length=16, num_samples=48,
+                                               base_seed=5, pin_memory=False))
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world), precision='32-true', logger=False,
+                      enable_progress_bar=False, max_steps=max_steps, gradient_clip_val=1.0, accelerator='cpu',
+                      default_root_dir=tmpdir, max_epochs=1,
+                      callbacks=[ModelCheckpoint(dirpath=tmpdir + '/ckpt', every_n_train_steps=4, save_top_k=-1)])
+    trainer.fit(lm, dm, ckpt_path=ckpt_path)
+    return ({n: p.detach().clone() for n, p in lm.named_parameters()}, trainer.global_step,
+            int(lm.consumed_samples.compute()))
+
+
+def test_fit_checkpoint_resume_is_bit_identical(tmp_path):
+    full = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'a'), None, 8))
+    assert full[0][1] == 8
+    ckpt = str(tmp_path / 'a' / 'ckpt' / 'epoch=0-step=4.ckpt')
+    import os
+    assert os.path.isdir(ckpt) and os.path.exists(os.path.join(ckpt, 'meta.pt')) \
+        and os.path.exists(os.path.join(ckpt, '.metadata'))
+    resumed = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'b'), ckpt, 8))
+    assert resumed[0][1] == 8
+    assert resumed[0][2] == full[0][2]                        # consumed-samples metric restored and continued
+    for n, p in full[0][0].items():
+        assert torch.allclose(resumed[0][0][n], p, atol=1e-6), n
