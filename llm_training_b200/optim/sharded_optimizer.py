@@ -122,9 +122,16 @@ class ShardedOptimizer(Optimizer):
         if self.fused:
             g = self._optimizer.param_groups[0]
             beta1, beta2 = g.get('betas', (0.9, 0.999))
-            for _, u, st in self._units():
+            for e, u, st in self._units():
                 shard = u.param_shard
                 low = 'master' in st
+                if e.nvlink and low and shard.dtype == torch.bfloat16:
+                    # fused: AdamW on the fp32 slice + bf16 result stored into every peer's parameter arena
+                    e.comm.adamw_push(st['master'], st['exp_avg'], st['exp_avg_sq'], u.local_grad(), e.param_arena,
+                                      u.arena_offset * 2, u.shard_numel, lr=g['lr'], beta1=beta1, beta2=beta2,
+                                      eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0),
+                                      step=self.step_count, max_norm=max_norm, norm_sq=norm_sq)
+                    continue
                 adamw_step(st['master'] if low else shard, st['exp_avg'], st['exp_avg_sq'], u.local_grad(),
                            shard if (low and shard.dtype == torch.bfloat16) else None, lr=g['lr'], beta1=beta1,
                            beta2=beta2, eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0),
@@ -146,7 +153,10 @@ class ShardedOptimizer(Optimizer):
                 if 'master' in st:
                     u.param_shard.copy_(st['master_param'].data)
         for e in self.engines:
-            e.gather_params()
+            if e.nvlink and self.fused:
+                e.comm.barrier()          # all pushed parameter slices have landed everywhere
+            else:
+                e.gather_params()
         return loss
 
     def zero_grad(self, set_to_none: bool = True) -> None:

@@ -85,8 +85,11 @@ _COMM_CACHE: dict[tuple, Comm] = {}
 def get_comm(axis: MeshAxis | None, kind: str = 'auto') -> Comm:
     """Comm for a mesh axis. ``kind``: 'torch' | 'nvlink' | 'auto' (nvlink when the axis is a multi-GPU
     CUDA group on one node and symmetric memory is available, else torch)."""
+    import os
     if axis is None:
         axis = MeshAxis('single', [0], 0, None)
+    if kind == 'auto':
+        kind = os.environ.get('LLMT_COMM', 'auto')      # torch | nvlink | auto
     key = (axis.name, tuple(axis.ranks), kind)
     if key in _COMM_CACHE:
         return _COMM_CACHE[key]

@@ -36,23 +36,30 @@ _ALIGN = 8   # elements: keeps every parameter 16-byte aligned for TMA / vector 
 
 
 class ShardedUnit:
+    @staticmethod
+    def layout(params: list[tuple[str, nn.Parameter]], world: int) -> tuple[list[int], int, int]:
+        offsets, off = [], 0
+        for _, p in params:
+            off = (off + _ALIGN - 1) // _ALIGN * _ALIGN
+            offsets.append(off)
+            off += p.numel()
+        chunk = _ALIGN * world
+        return offsets, off, max(chunk, (off + chunk - 1) // chunk * chunk)
+
     def __init__(self, name: str, params: list[tuple[str, nn.Parameter]], world: int, rank: int,
-                 device: torch.device, dtype: torch.dtype, grad_dtype: torch.dtype) -> None:
+                 device: torch.device, dtype: torch.dtype, grad_dtype: torch.dtype,
+                 flat_param: torch.Tensor | None = None, flat_grad: torch.Tensor | None = None,
+                 arena_offset: int = 0) -> None:
         self.name = name
         self.params = params
         self.world, self.rank = world, rank
-        self.offsets: list[int] = []
-        off = 0
-        for _, p in params:
-            off = (off + _ALIGN - 1) // _ALIGN * _ALIGN
-            self.offsets.append(off)
-            off += p.numel()
-        self.numel = off
-        chunk = _ALIGN * world
-        self.padded_numel = max(chunk, (off + chunk - 1) // chunk * chunk)
+        self.offsets, self.numel, self.padded_numel = self.layout(params, world)
         self.shard_numel = self.padded_numel // world
-        self.flat_param = torch.zeros(self.padded_numel, dtype=dtype, device=device)
-        self.flat_grad = torch.zeros(self.padded_numel, dtype=grad_dtype, device=device)
+        self.arena_offset = arena_offset          # element offset inside the engine's symmetric arenas
+        self.flat_param = flat_param if flat_param is not None else torch.zeros(self.padded_numel, dtype=dtype,
+                                                                                 device=device)
+        self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(self.padded_numel, dtype=grad_dtype,
+                                                                              device=device)
         for (_, p), o in zip(params, self.offsets):
             view = self.flat_param[o:o + p.numel()].view(p.shape)
             if not p.is_meta:
@@ -92,12 +99,33 @@ class FlatParamEngine:
         self.device = device
         self.world, self.rank = self.axis.size(), self.axis.rank
         self.units: list[ShardedUnit] = []
-        for name, params in units:
-            if not params:
-                continue
-            dtype = params[0][1].dtype
-            assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
-            self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype))
+        units = [(n, ps) for n, ps in units if ps]
+        self.nvlink = bool(getattr(self.comm, 'is_nvlink', False)) and self.world > 1
+        self.param_arena = self.grad_arena = None
+        dtypes = {ps[0][1].dtype for _, ps in units}
+        if self.nvlink and len(dtypes) == 1:
+            # one symmetric allocation for all parameters and one for all gradients: peers address any unit as
+            # arena base + offset, and a single rendezvous exchanges the handles
+            dtype = next(iter(dtypes))
+            sizes = [ShardedUnit.layout(ps, self.world)[2] for _, ps in units]
+            total = sum(sizes)
+            self.param_arena = self.comm.alloc(total, dtype)
+            self.grad_arena = self.comm.alloc(total, dtype)
+            self.param_arena.tensor.zero_()
+            self.grad_arena.tensor.zero_()
+            off = 0
+            for (name, params), size in zip(units, sizes):
+                self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, dtype,
+                                              flat_param=self.param_arena.tensor[off:off + size],
+                                              flat_grad=self.grad_arena.tensor[off:off + size], arena_offset=off))
+                off += size
+        else:
+            self.nvlink = False
+            for name, params in units:
+                dtype = params[0][1].dtype
+                assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
+                self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype))
+        self._norm_accumulating = False
         self.require_sync = True
         self._comm_stream = torch.cuda.Stream(device) if device.type == 'cuda' and self.world > 1 else None
         self._norm_sq = torch.zeros(1, dtype=torch.float32, device=device)
@@ -131,7 +159,17 @@ class FlatParamEngine:
         if self._comm_stream is not None:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(self._comm_stream):
-                self.comm.reduce_scatter_into(u.grad_shard, u.flat_grad, average=True)
+                self._reduce(u)
+        else:
+            self._reduce(u)
+
+    def _reduce(self, u: ShardedUnit) -> None:
+        if self.nvlink:
+            # barrier + pull of this rank's slice from every peer + squared-norm partial, one pass over NVLink
+            esize = u.flat_grad.element_size()
+            self.comm.reduce_scatter_sumsq(self.grad_arena, u.arena_offset * esize, u.shard_numel, u.grad_shard,
+                                           self._norm_sq, accumulate_norm=self._norm_accumulating)
+            self._norm_accumulating = True
         else:
             self.comm.reduce_scatter_into(u.grad_shard, u.flat_grad, average=True)
 
@@ -167,6 +205,13 @@ class FlatParamEngine:
         """Device scalar: squared L2 norm of the (already reduced) gradient, summed over the dp axis
         (and any extra axes the parameters are sharded over).  No host sync."""
         from ..ops.adamw_op import sumsq
+        if self.nvlink:
+            # per-unit partial norms were accumulated by the reduce-scatter kernels; one tiny all-reduce is left
+            self._norm_accumulating = False
+            self.comm.all_reduce(self._norm_sq)
+            for c in extra_axes or []:
+                c.all_reduce(self._norm_sq)
+            return self._norm_sq
         first = True
         for u in self.units:
             sumsq(u.local_grad(), self._norm_sq, accumulate=not first)
@@ -182,6 +227,12 @@ class FlatParamEngine:
     def gather_params(self) -> None:
         """After the optimizer updated every rank's slice: rebuild the full bf16 buffers in place."""
         if self.world == 1:
+            return
+        if self.nvlink:
+            esize = self.param_arena.tensor.element_size()
+            for u in self.units:
+                self.comm.allgather_pull(self.param_arena, u.arena_offset * esize, u.shard_numel * esize)
+            self.comm.barrier()
             return
         for u in self.units:
             self.comm.all_gather_into(u.flat_param, u.param_shard)

@@ -1,0 +1,126 @@
+"""NVLink 5 / NVSwitch communication backend built on symmetric memory + the kernels in ``csrc/kernels/comm.cu``.
+
+``torch.distributed._symmetric_memory`` is used ONLY as the allocator / handle exchange (cuMem + fabric or fd
+handles mapped into every peer, plus a signal pad per rank); every byte that crosses NVLink is moved by the
+in-tree kernels with plain loads / stores on the mapped peer addresses.
+
+Protocol notes
+  * barrier / one-shot all-reduce use uint32 slots in the signal pads with monotonically increasing epochs
+    (``st.release.sys`` by the writer, ``ld.acquire.sys`` spin by the reader);
+  * all ranks issue the same sequence of collectives (same model, same autograd order), so epochs agree
+    without any host-side negotiation;
+  * kernels run on the caller's current stream; the sharding engine puts them on its communication stream.
+"""
+import ctypes
+from typing import Any
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from .comm import Comm
+from .mesh import MeshAxis
+
+_BARRIER_SLOT = 256      # uint32 index inside the signal pad (torch's own channels use the low slots)
+_ALLREDUCE_SLOT = 320
+
+
+def _ptr_array(ptrs: list[int]):
+    arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+    return arr
+
+
+class SymmetricBuffer:
+    """A tensor that exists at the same offset on every rank of the axis, with the peers' addresses."""
+
+    def __init__(self, tensor: torch.Tensor, handle: Any) -> None:
+        self.tensor = tensor
+        self.handle = handle
+        self.peer_ptrs: list[int] = [int(p) for p in handle.buffer_ptrs]
+
+    def peer_ptrs_at(self, byte_offset: int):
+        return _ptr_array([p + byte_offset for p in self.peer_ptrs])
+
+
+class NVLinkComm(Comm):
+    is_nvlink = True
+
+    def __init__(self, axis: MeshAxis) -> None:
+        super().__init__(axis)
+        import torch.distributed._symmetric_memory as symm_mem
+        self._symm = symm_mem
+        assert axis.group is not None and axis.size() > 1
+        self.group = axis.group
+        self.device = torch.device('cuda', torch.cuda.current_device())
+        symm_mem.enable_symm_mem_for_group(self.group.group_name) if hasattr(symm_mem, 'enable_symm_mem_for_group') \
+            else None
+        self._scalars = self.alloc(32 * max(axis.size(), 1), torch.float32)      # [world][32] for one-shot reduce
+        self._scalars.tensor.zero_()
+        pad_bytes = int(self._scalars.handle.signal_pad_size)
+        assert pad_bytes >= 4 * (_ALLREDUCE_SLOT + axis.size()), f'signal pad too small ({pad_bytes} B)'
+        self._pads = _ptr_array([int(p) for p in self._scalars.handle.signal_pad_ptrs])
+        self._barrier_epoch = 0
+        self._allreduce_epoch = 0
+        self._lib = _lib.lib()
+        self._rs_partial = torch.empty(self._lib.llmt_comm_rs_num_partials(), dtype=torch.float32, device=self.device)
+        dist.barrier(group=self.group, device_ids=[self.device.index])
+
+    # ---------------------------------------------------------------- allocation
+    def alloc(self, numel: int, dtype: torch.dtype) -> SymmetricBuffer:
+        t = self._symm.empty(numel, dtype=dtype, device=self.device)
+        handle = self._symm.rendezvous(t, self.group)
+        return SymmetricBuffer(t, handle)
+
+    # ---------------------------------------------------------------- primitives
+    def barrier(self) -> None:
+        self._barrier_epoch += 1
+        _lib.check(self._lib.llmt_comm_barrier(self._pads, _lib.c_int(self.rank), _lib.c_int(self.size),
+                                               _lib.c_int(_BARRIER_SLOT), ctypes.c_uint32(self._barrier_epoch),
+                                               _lib.stream()), 'comm_barrier')
+
+    def all_reduce(self, t: torch.Tensor, op: str = 'sum', async_op: bool = False) -> None:
+        if op == 'sum' and t.dtype == torch.float32 and t.numel() <= 32 and t.is_contiguous():
+            self._allreduce_epoch += 1
+            _lib.check(self._lib.llmt_comm_allreduce_f32(
+                self._scalars.peer_ptrs_at(0), self._pads, _lib.c_int(self.rank), _lib.c_int(self.size),
+                _lib.c_int(_ALLREDUCE_SLOT), ctypes.c_uint32(self._allreduce_epoch), _lib.ptr(t),
+                _lib.c_int(t.numel()), _lib.stream()), 'comm_allreduce_f32')
+            return None
+        return dist.all_reduce(t, op={'sum': dist.ReduceOp.SUM, 'max': dist.ReduceOp.MAX}[op], group=self.group)
+
+    def broadcast(self, t: torch.Tensor, src_index: int = 0) -> None:
+        dist.broadcast(t, src=self.axis.ranks[src_index], group=self.group)
+
+    def all_gather_into(self, full: torch.Tensor, shard: torch.Tensor, async_op: bool = False) -> None:
+        """Generic tensors (not in the symmetric heap) fall back to NCCL; the engine uses ``allgather_pull``."""
+        return dist.all_gather_into_tensor(full, shard, group=self.group)
+
+    def reduce_scatter_into(self, shard, full, average: bool = True, async_op: bool = False) -> None:
+        return dist.reduce_scatter_tensor(shard, full, op=dist.ReduceOp.AVG if average else dist.ReduceOp.SUM,
+                                          group=self.group)
+
+    # ---------------------------------------------------------------- engine collectives on symmetric arenas
+    def allgather_pull(self, arena: SymmetricBuffer, byte_offset: int, shard_bytes: int) -> None:
+        self.barrier()                                           # every owner's slice is final
+        _lib.check(self._lib.llmt_comm_allgather_pull(arena.peer_ptrs_at(byte_offset), _lib.c_int(self.rank),
+                                                      _lib.c_int(self.size), _lib.c_i64(shard_bytes), _lib.stream()),
+                   'comm_allgather_pull')
+
+    def reduce_scatter_sumsq(self, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, out_shard: torch.Tensor,
+                             norm_sq: torch.Tensor, accumulate_norm: bool) -> None:
+        self.barrier()                                           # every rank finished writing this unit's grads
+        _lib.check(self._lib.llmt_comm_rs_sumsq(
+            arena.peer_ptrs_at(byte_offset), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
+            _lib.c_int(out_shard.dtype == torch.float32), _lib.ptr(out_shard), _lib.ptr(self._rs_partial),
+            _lib.ptr(norm_sq), _lib.c_int(accumulate_norm), _lib.stream()), 'comm_rs_sumsq')
+
+    def adamw_push(self, master: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
+                   grad_shard: torch.Tensor, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, *,
+                   lr: float, beta1: float, beta2: float, eps: float, weight_decay: float, step: int,
+                   max_norm: float, norm_sq: torch.Tensor | None) -> None:
+        _lib.check(self._lib.llmt_comm_adamw_push(
+            _lib.ptr(master), _lib.ptr(exp_avg), _lib.ptr(exp_avg_sq), _lib.ptr(grad_shard),
+            arena.peer_ptrs_at(byte_offset), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
+            _lib.c_int(grad_shard.dtype == torch.float32), _lib.c_f32(lr), _lib.c_f32(beta1), _lib.c_f32(beta2),
+            _lib.c_f32(eps), _lib.c_f32(weight_decay), _lib.c_int(step), _lib.c_f32(1.0), _lib.c_f32(max_norm),
+            _lib.ptr(norm_sq), _lib.stream()), 'comm_adamw_push')

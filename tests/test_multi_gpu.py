@@ -1,0 +1,93 @@
+"""Multi-GPU checks (need >= 2 CUDA devices; skipped otherwise): the NVLink symmetric-memory collectives and the
+fused AdamW + parameter-push kernel must reproduce the NCCL path."""
+import os
+import socket
+import traceback
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
+    try:
+        os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
+                          MASTER_PORT=str(port), LLMT_COMM=comm_kind)
+        import torch.distributed as dist
+        torch.cuda.set_device(rank)
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+        from llm_training_b200.models import Llama, LlamaConfig
+        from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+        from llm_training_b200.optim import ShardedOptimizer
+        from llm_training_b200.parallel import apply_fully_sharded, init_mesh
+        mesh = init_mesh(world, 1)
+        torch.manual_seed(0)
+        cfg = LlamaConfig(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                          num_attention_heads=4, num_key_value_heads=2)
+        with torch.device('cuda'):
+            model = Llama(cfg).to(torch.bfloat16)
+        engine = apply_fully_sharded(model, mesh.dp, device=torch.device('cuda', rank))
+        assert engine.nvlink == (comm_kind == 'nvlink')
+        opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
+                               max_grad_norm=1.0)
+        losses, norms = [], []
+        for step in range(4):
+            g = torch.Generator().manual_seed(1000 + step * world + rank)
+            ids = torch.randint(0, 1024, (2, 256), generator=g).cuda()
+            opt.zero_grad()
+            out = model(input_ids=ids, skip_logits=True)
+            loss = fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                              shift_labels(ids).flatten())
+            loss.backward()
+            opt.step()
+            losses.append(float(loss))
+            norms.append(float(opt.last_grad_norm))
+        torch.cuda.synchronize()
+        checksum = [float(p.float().sum()) for p in model.parameters()]
+        queue.put((rank, 'ok', (losses, norms, checksum)))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        queue.put((rank, 'error', traceback.format_exc()))
+
+
+def _run(comm_kind: str, world: int = 2):
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, comm_kind, queue)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = {}
+    for _ in range(world):
+        rank, status, payload = queue.get(timeout=240)
+        assert status == 'ok', f'rank {rank} ({comm_kind}):\n{payload}'
+        out[rank] = payload
+    for p in procs:
+        p.join(timeout=60)
+    return out
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
+def test_nvlink_engine_matches_nccl_engine():
+    ref = _run('torch')
+    got = _run('nvlink')
+    for rank in (0, 1):
+        l_ref, n_ref, c_ref = ref[rank]
+        l_got, n_got, c_got = got[rank]
+        for a, b in zip(l_ref, l_got):
+            assert abs(a - b) < 2e-2, (l_ref, l_got)
+        for a, b in zip(n_ref, n_got):
+            assert abs(a - b) < 2e-2 * max(1.0, a), (n_ref, n_got)
+        for a, b in zip(c_ref, c_got):
+            assert abs(a - b) <= 2e-2 * max(1.0, abs(a)), (a, b)
+    # every rank ends with the same parameters
+    assert all(abs(a - b) < 1e-6 * max(1.0, abs(a)) for a, b in zip(got[0][2], got[1][2]))
