@@ -72,9 +72,10 @@ ce_bwd_inplace_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restr
   const int64_t row = blockIdx.x;
   __nv_bfloat16* lr = logits + row * row_stride;
   const int nvec = vocab >> 3;
+  // ignored rows get a zero gradient; a label outside [0, vocab) (another rank's vocabulary shard under
+  // vocab parallelism) simply has no one-hot term on this rank
   const int64_t label = labels[row];
-  const bool valid = label != ignore_index && label >= 0 && label < vocab;
-  const float scale = valid ? row_scale[row] : 0.f;
+  const float scale = (label != ignore_index) ? row_scale[row] : 0.f;
   const float l = lse[row];
   if (scale == 0.f) {  // ignored row: zero gradient
     bf16x8 z;

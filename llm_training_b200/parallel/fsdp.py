@@ -93,8 +93,12 @@ class ShardedUnit:
 
 class FlatParamEngine:
     def __init__(self, units: list[tuple[str, list[tuple[str, nn.Parameter]]]], dp_axis: MeshAxis | None,
-                 device: torch.device, comm: Comm | None = None, grad_dtype: torch.dtype | None = None) -> None:
+                 device: torch.device, comm: Comm | None = None, grad_dtype: torch.dtype | None = None,
+                 tp_axis: MeshAxis | None = None) -> None:
         self.axis = dp_axis if dp_axis is not None else MeshAxis('data_parallel', [0], 0, None)
+        # tensor-parallel peers hold different shards of most parameters but REPLICAS of a few (norm weights);
+        # under sequence parallelism the replicas' gradients are partial sums over the tp axis
+        self.tp_axis = tp_axis if (tp_axis is not None and tp_axis.size() > 1) else None
         self.comm = comm if comm is not None else get_comm(self.axis)
         self.device = device
         self.world, self.rank = self.axis.size(), self.axis.rank
@@ -155,6 +159,8 @@ class FlatParamEngine:
             return
         u.reduced = True
         if self.world == 1:
+            if self.tp_axis is not None:
+                self._reduce(u)
             return
         if self._comm_stream is not None:
             self._comm_stream.wait_stream(torch.cuda.current_stream(self.device))
@@ -164,6 +170,13 @@ class FlatParamEngine:
             self._reduce(u)
 
     def _reduce(self, u: ShardedUnit) -> None:
+        if self.tp_axis is not None:
+            import torch.distributed as dist
+            for _, p in u.params:
+                if getattr(p, '_tp_replicated', False) and p.grad is not None:
+                    dist.all_reduce(p.grad, group=self.tp_axis.group)
+        if self.world == 1:
+            return
         if self.nvlink:
             # barrier + pull of this rank's slice from every peer + squared-norm partial, one pass over NVLink
             esize = u.flat_grad.element_size()
@@ -208,6 +221,7 @@ class FlatParamEngine:
         if self.nvlink:
             # per-unit partial norms were accumulated by the reduce-scatter kernels; one tiny all-reduce is left
             self._norm_accumulating = False
+            self._discount_tp_replicas()
             self.comm.all_reduce(self._norm_sq)
             for c in extra_axes or []:
                 c.all_reduce(self._norm_sq)
@@ -218,10 +232,21 @@ class FlatParamEngine:
             first = False
         if first:
             self._norm_sq.zero_()
+        self._discount_tp_replicas()
         self.comm.all_reduce(self._norm_sq)
         for c in extra_axes or []:
             c.all_reduce(self._norm_sq)
         return self._norm_sq
+
+    def _discount_tp_replicas(self) -> None:
+        """The norm is summed over the tp axis too; parameters replicated across it must count once."""
+        if self.tp_axis is None or self.tp_axis.rank == 0:
+            return
+        for u in self.units:
+            g = u.local_grad()
+            for _, p, _, start, length in u.shard_slices():
+                if getattr(p, '_tp_replicated', False):
+                    self._norm_sq -= g[start:start + length].float().pow(2).sum()
 
     # ------------------------------------------------------------------ parameters
     def gather_params(self) -> None:
@@ -284,7 +309,8 @@ def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_afte
         device = first.device if first is not None else torch.device('cpu')
     # gradients are reduced in the parameter dtype (bf16 for `bf16-true`, like the reference's default
     # MixedPrecisionPolicy, fsdp2_precision.py:72-76); `.grad` must match the parameter dtype anyway
-    engine = FlatParamEngine(_collect_units(model), dp_mesh, device, comm=comm)
+    tp_axis = getattr(getattr(model, 'tp_context', None), 'axis', None)
+    engine = FlatParamEngine(_collect_units(model), dp_mesh, device, comm=comm, tp_axis=tp_axis)
     model._flat_engine = engine
     if offload_policy is not None and getattr(offload_policy, 'pin_memory', None) is not None \
             and type(offload_policy).__name__ == 'CPUOffloadPolicy':

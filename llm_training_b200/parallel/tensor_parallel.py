@@ -1,0 +1,326 @@
+"""Megatron-style tensor parallelism with sequence parallelism for the decoder models.
+
+What the reference builds from DTensor ``parallelize_module`` plans (src/llm_training/models/llama/
+llama_model.py:197-244, phi3_model.py:212-256) is done here on plain tensors:
+
+  * q/k/v and gate/up are column-parallel (rows of the weight split by heads / features), o_proj and down_proj
+    are row-parallel (input features split); local head counts are ``H / tp``
+  * the residual stream and both RMSNorms live on ``[T/tp, d]`` token shards (sequence parallel):
+    ``gather_sequence`` all-gathers before attention / MLP, the row-parallel projections reduce-scatter back
+  * embedding and LM head are vocabulary-parallel; the loss never materialises full logits
+    (``vocab_parallel_cross_entropy`` / ``vocab_parallel_logprob``)
+  * fused weights (Phi-3 ``qkv_proj`` / ``gate_up_proj``) are sharded HEAD-ALIGNED: rank r holds
+    ``[q_r; k_r; v_r]`` / ``[gate_r; up_r]`` — the reference's plain column split is wrong for pre-trained
+    weights
+
+Collectives go through torch.distributed (gloo on CPU, NCCL on GPU) inside autograd Functions.
+"""
+from dataclasses import dataclass
+from typing import Any, Callable
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+from torch import nn
+
+from ..ops import _lib, embedding, linear
+from ..ops.gemm_op import gemm
+from .mesh import MeshAxis
+
+
+# ---------------------------------------------------------------------------------------------------
+# sharding descriptors (used by checkpoint I/O and weight loading)
+# ---------------------------------------------------------------------------------------------------
+@dataclass
+class TPInfo:
+    full_shape: torch.Size
+    scatter: Callable[[torch.Tensor], torch.Tensor]        # full tensor -> this rank's shard
+    gather: Callable[[torch.Tensor], torch.Tensor]         # this rank's shard -> full tensor (collective)
+
+
+def _all_gather_cat(local: torch.Tensor, axis: MeshAxis, dim: int) -> torch.Tensor:
+    parts = [torch.empty_like(local) for _ in range(axis.size())]
+    dist.all_gather(parts, local.contiguous(), group=axis.group)
+    return torch.cat(parts, dim=dim)
+
+
+def _plain_shard(axis: MeshAxis, dim: int) -> tuple[Callable, Callable]:
+    def scatter(full: torch.Tensor) -> torch.Tensor:
+        return full.chunk(axis.size(), dim=dim)[axis.rank].contiguous()
+
+    def gather(local: torch.Tensor) -> torch.Tensor:
+        return _all_gather_cat(local, axis, dim)
+    return scatter, gather
+
+
+def _blocked_shard(axis: MeshAxis, block_rows: list[int]) -> tuple[Callable, Callable]:
+    """Row-blocked weight (e.g. [q; k; v]): every block is split evenly, rank r keeps the r-th piece of each."""
+    tp = axis.size()
+
+    def scatter(full: torch.Tensor) -> torch.Tensor:
+        pieces = [b.chunk(tp, dim=0)[axis.rank] for b in full.split(block_rows, dim=0)]
+        return torch.cat(pieces, dim=0).contiguous()
+
+    def gather(local: torch.Tensor) -> torch.Tensor:
+        parts = [torch.empty_like(local) for _ in range(tp)]
+        dist.all_gather(parts, local.contiguous(), group=axis.group)
+        local_rows = [r // tp for r in block_rows]
+        blocks = []
+        for b in range(len(block_rows)):
+            blocks.append(torch.cat([p.split(local_rows, dim=0)[b] for p in parts], dim=0))
+        return torch.cat(blocks, dim=0)
+    return scatter, gather
+
+
+def _shard_param(module: nn.Module, name: str, scatter: Callable, gather: Callable) -> None:
+    p = getattr(module, name)
+    if p is None:
+        return
+    full_shape = p.shape
+    if p.is_meta:
+        local = torch.empty(scatter(torch.empty(full_shape, device='meta')).shape, dtype=p.dtype, device='meta')
+    else:
+        local = scatter(p.data)
+    new = nn.Parameter(local, requires_grad=p.requires_grad)
+    new._tp_info = TPInfo(full_shape, scatter, gather)
+    setattr(module, name, new)
+
+
+# ---------------------------------------------------------------------------------------------------
+# autograd collectives
+# ---------------------------------------------------------------------------------------------------
+class _GatherSeq(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, axis: MeshAxis) -> torch.Tensor:
+        ctx.axis = axis
+        out = torch.empty((x.shape[0] * axis.size(), *x.shape[1:]), dtype=x.dtype, device=x.device)
+        dist.all_gather_into_tensor(out, x.contiguous(), group=axis.group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        return _reduce_scatter_rows(g.contiguous(), ctx.axis), None
+
+
+class _ReduceScatterSeq(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, axis: MeshAxis) -> torch.Tensor:
+        ctx.axis = axis
+        return _reduce_scatter_rows(x.contiguous(), axis)
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        out = torch.empty((g.shape[0] * ctx.axis.size(), *g.shape[1:]), dtype=g.dtype, device=g.device)
+        dist.all_gather_into_tensor(out, g.contiguous(), group=ctx.axis.group)
+        return out, None
+
+
+class _ScatterSeq(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, axis: MeshAxis) -> torch.Tensor:
+        ctx.axis = axis
+        return x.chunk(axis.size(), dim=0)[axis.rank].contiguous()
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        out = torch.empty((g.shape[0] * ctx.axis.size(), *g.shape[1:]), dtype=g.dtype, device=g.device)
+        dist.all_gather_into_tensor(out, g.contiguous(), group=ctx.axis.group)
+        return out, None
+
+
+def _reduce_scatter_rows(x: torch.Tensor, axis: MeshAxis) -> torch.Tensor:
+    tp = axis.size()
+    assert x.shape[0] % tp == 0, f'token count {x.shape[0]} is not divisible by the tensor-parallel size {tp}'
+    if dist.get_backend(axis.group) == 'gloo':
+        full = x.clone()
+        dist.all_reduce(full, group=axis.group)
+        return full.chunk(tp, dim=0)[axis.rank].contiguous()
+    out = torch.empty((x.shape[0] // tp, *x.shape[1:]), dtype=x.dtype, device=x.device)
+    dist.reduce_scatter_tensor(out, x, group=axis.group)
+    return out
+
+
+class _VocabParallelLoss(torch.autograd.Function):
+    """CE / token log-prob over vocabulary shards: each rank holds ``W[v0:v1]``; max / sum-exp / target logit are
+    combined across ranks (reference: ``loss_parallel()``, lms/clm/clm.py:114-120 — 3 all-reduces of [T];
+    explicit all-reduce of per-token log-probs, lms/dpo/dpo.py:89-108).  Returns per-token ``lse - tgt``
+    (0 at ignored positions).  The hidden-state gradient is a partial sum (the caller's sequence gather turns it
+    into a reduce-scatter)."""
+
+    @staticmethod
+    def forward(ctx, hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int,
+                axis: MeshAxis) -> torch.Tensor:
+        v_local = weight.shape[0]
+        v0 = axis.rank * v_local
+        local_labels = labels - v0
+        in_shard = (local_labels >= 0) & (local_labels < v_local)
+        # out-of-shard labels must not look like `ignore_index`
+        local_labels = torch.where(in_shard, local_labels, torch.full_like(labels, -1))
+        local_labels = torch.where(labels == ignore_index, torch.full_like(labels, ignore_index), local_labels)
+        use_k = _lib.use_kernels(hidden) and weight.dtype == torch.bfloat16 and v_local % 8 == 0
+        if use_k:
+            logits = gemm(hidden.contiguous(), weight)
+            rows = logits.shape[0]
+            lse_local = torch.empty(rows, dtype=torch.float32, device=hidden.device)
+            tgt_local = torch.empty_like(lse_local)
+            _lib.check(_lib.lib().llmt_ce_fwd(_lib.ptr(logits), _lib.ptr(local_labels), _lib.ptr(lse_local),
+                                              _lib.ptr(tgt_local), _lib.c_int(rows), _lib.c_int(v_local),
+                                              _lib.c_i64(logits.stride(0)), _lib.c_i64(ignore_index),
+                                              _lib.c_f32(0.0), _lib.stream()), 'ce_fwd')
+        else:
+            logits = F.linear(hidden, weight).float()
+            lse_local = torch.logsumexp(logits, dim=-1)
+            tgt_local = logits.gather(1, local_labels.clamp(0, v_local - 1).unsqueeze(1)).squeeze(1) * in_shard
+        # combine shards: global lse = logsumexp over ranks of the local lse; target logit lives on one rank
+        gathered = torch.empty(axis.size() * lse_local.numel(), dtype=torch.float32, device=hidden.device)
+        dist.all_gather_into_tensor(gathered, lse_local.float().contiguous(), group=axis.group)
+        lse = torch.logsumexp(gathered.view(axis.size(), -1), dim=0)
+        tgt = tgt_local.float() * (labels != ignore_index)
+        dist.all_reduce(tgt, group=axis.group)
+        ctx.save_for_backward(hidden, weight, logits, local_labels, lse)
+        ctx.meta = (ignore_index, use_k, v_local)
+        return (lse - tgt) * (labels != ignore_index)
+
+    @staticmethod
+    def backward(ctx, grad: torch.Tensor):
+        hidden, weight, logits, local_labels, lse = ctx.saved_tensors
+        ignore_index, use_k, v_local = ctx.meta
+        scale = grad.float().contiguous()
+        if use_k:
+            rows = logits.shape[0]
+            _lib.check(_lib.lib().llmt_ce_bwd_inplace(_lib.ptr(logits), _lib.ptr(local_labels), _lib.ptr(lse),
+                                                      _lib.ptr(scale), _lib.c_int(rows), _lib.c_int(v_local),
+                                                      _lib.c_i64(logits.stride(0)), _lib.c_i64(ignore_index),
+                                                      _lib.c_f32(0.0), _lib.stream()), 'ce_bwd')
+            dh = gemm(logits, weight, b_mn_major=True)
+            dw = gemm(logits, hidden.contiguous(), a_mn_major=True, b_mn_major=True)
+        else:
+            probs = torch.exp(logits - lse.unsqueeze(1))
+            onehot = torch.zeros_like(probs)
+            ok = (local_labels >= 0) & (local_labels < v_local)
+            onehot[ok, local_labels[ok]] = 1.0
+            dlogits = (probs - onehot) * (scale * (local_labels != ignore_index)).unsqueeze(1)
+            dh = (dlogits @ weight.float()).to(hidden.dtype)
+            dw = (dlogits.t() @ hidden.float()).to(weight.dtype)
+        return dh, dw, None, None, None
+
+
+# ---------------------------------------------------------------------------------------------------
+# the context object handed to the models
+# ---------------------------------------------------------------------------------------------------
+class TensorParallelContext:
+    def __init__(self, axis: MeshAxis) -> None:
+        self.axis = axis
+        self.size = axis.size()
+        self.rank = axis.rank
+
+    def gather_sequence(self, x: torch.Tensor) -> torch.Tensor:
+        return _GatherSeq.apply(x, self.axis)
+
+    def scatter_sequence(self, x: torch.Tensor) -> torch.Tensor:
+        return _ScatterSeq.apply(x, self.axis)
+
+    def row_linear(self, x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None,
+                   residual: torch.Tensor | None) -> torch.Tensor:
+        """``x [T, in/tp] @ W_local^T`` -> partial sums -> reduce-scatter over tokens -> ``[T/tp, out]``."""
+        partial = linear(x, weight)
+        out = _ReduceScatterSeq.apply(partial, self.axis)
+        if bias is not None:
+            out = out + bias
+        return out if residual is None else out + residual
+
+    def vocab_parallel_embedding(self, input_ids: torch.Tensor, weight: torch.Tensor, padding_idx: int | None,
+                                 noise_scale: torch.Tensor | None, seed: int) -> torch.Tensor:
+        """Masked local lookup + reduce-scatter to token shards (reference: RowwiseParallel embedding,
+        llama_model.py:205-208).  NEFTune noise is added AFTER the reduction, per token shard, with the scale
+        computed from the global sequence length (fixes SURVEY Appendix B5)."""
+        v_local = weight.shape[0]
+        flat = input_ids.reshape(-1)
+        local = flat - self.rank * v_local
+        ok = (local >= 0) & (local < v_local)
+        local_pad = None
+        if padding_idx is not None and 0 <= padding_idx - self.rank * v_local < v_local:
+            local_pad = padding_idx - self.rank * v_local      # the padding row lives in this shard
+        rows = embedding(local.clamp(0, v_local - 1), weight, local_pad)
+        rows = rows * ok.unsqueeze(1).to(rows.dtype)
+        out = _ReduceScatterSeq.apply(rows, self.axis)
+        if noise_scale is not None:
+            shard = noise_scale.chunk(self.size)[self.rank]
+            gen = torch.Generator(device=out.device).manual_seed(seed * 1009 + self.rank)
+            noise = torch.rand(out.shape, generator=gen, device=out.device, dtype=torch.float32) * 2 - 1
+            out = out + (noise * shard.unsqueeze(1)).to(out.dtype)
+        return out
+
+    def lm_head(self, normed_local: torch.Tensor, weight: torch.Tensor) -> torch.Tensor:
+        """Full logits ``[T, V]`` (API parity path; the training losses use the vocab-parallel functions)."""
+        h = self.gather_sequence(normed_local)
+        local = linear(h, weight)
+        parts = [torch.empty_like(local) for _ in range(self.size)]
+        dist.all_gather(parts, local.contiguous(), group=self.axis.group)
+        parts[self.rank] = local
+        return torch.cat(parts, dim=-1)
+
+    def _token_nll(self, normed_local: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int
+                   ) -> torch.Tensor:
+        h = self.gather_sequence(normed_local)
+        return _VocabParallelLoss.apply(h, weight, labels.contiguous(), ignore_index, self.axis)
+
+    def vocab_parallel_cross_entropy(self, normed_local: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                                     ignore_index: int = -100) -> torch.Tensor:
+        nll = self._token_nll(normed_local, weight, labels, ignore_index)
+        return nll.sum() / labels.ne(ignore_index).sum().clamp_min(1)
+
+    def vocab_parallel_logprob(self, normed_local: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                               ignore_index: int = -100) -> torch.Tensor:
+        return -self._token_nll(normed_local, weight, labels, ignore_index)
+
+
+# ---------------------------------------------------------------------------------------------------
+# applying the plan
+# ---------------------------------------------------------------------------------------------------
+def apply_decoder_tensor_parallel(model: nn.Module, tp_axis: MeshAxis, fused_qkv: bool, fused_gate_up: bool) -> None:
+    tp = tp_axis.size()
+    cfg = model.config
+    n_heads = cfg.num_attention_heads
+    n_kv = getattr(cfg, 'num_key_value_heads', None) or n_heads
+    if n_heads % tp or n_kv % tp:
+        raise ValueError(f'tensor_parallel_size={tp} must divide num_attention_heads={n_heads} and '
+                         f'num_key_value_heads={n_kv} (the reference silently computes 0 heads, SURVEY §5.7)')
+    if cfg.vocab_size % tp or cfg.intermediate_size % tp:
+        raise ValueError(f'tensor_parallel_size={tp} must divide vocab_size and intermediate_size')
+    head_dim = getattr(cfg, 'head_dim', None) or cfg.hidden_size // n_heads
+    col = _plain_shard(tp_axis, 0)
+    row = _plain_shard(tp_axis, 1)
+    for layer in model.layers:
+        attn, mlp = layer.self_attn, layer.mlp
+        if fused_qkv:
+            _shard_param(attn.qkv_proj, 'weight', *_blocked_shard(tp_axis, [n_heads * head_dim, n_kv * head_dim,
+                                                                            n_kv * head_dim]))
+        else:
+            for proj in (attn.q_proj, attn.k_proj, attn.v_proj):
+                _shard_param(proj, 'weight', *col)
+                if proj.bias is not None:
+                    _shard_param(proj, 'bias', *col)
+        _shard_param(attn.o_proj, 'weight', *row)
+        if fused_gate_up:
+            _shard_param(mlp.gate_up_proj, 'weight',
+                         *_blocked_shard(tp_axis, [cfg.intermediate_size, cfg.intermediate_size]))
+        else:
+            for proj in (mlp.gate_proj, mlp.up_proj):
+                _shard_param(proj, 'weight', *col)
+                if proj.bias is not None:
+                    _shard_param(proj, 'bias', *col)
+        _shard_param(mlp.down_proj, 'weight', *row)
+        for norm in (layer.input_layernorm, layer.post_attention_layernorm):
+            norm.weight._tp_replicated = True
+        for proj in (attn.o_proj, mlp.down_proj):
+            if getattr(proj, 'bias', None) is not None:
+                proj.bias._tp_replicated = True
+    tied = model.lm_head.weight is model.embed_tokens.weight
+    _shard_param(model.embed_tokens, 'weight', *col)
+    if tied:
+        model.lm_head.weight = model.embed_tokens.weight
+    else:
+        _shard_param(model.lm_head, 'weight', *col)
+    model.norm.weight._tp_replicated = True
+    model.tp_context = TensorParallelContext(tp_axis)
