@@ -1,0 +1,372 @@
+"""Config loader / CLI, LR schedules, RoPE initialisers, op references, objectives, checkpoint + HF export."""
+import math
+import os
+
+import pytest
+import torch
+
+from tests.helpers import TINY_LLAMA
+
+
+# ---------------------------------------------------------------------------------------------------- config / CLI
+def test_alias_package_shares_module_objects():
+    import llm_training
+    import llm_training.lms
+    import llm_training_b200.lms
+    from llm_training.models import Llama
+    from llm_training_b200.models import Llama as Llama2
+    assert llm_training.lms is llm_training_b200.lms and Llama is Llama2
+
+
+def test_yaml_loader_dotted_keys_overrides_and_instantiation(tmp_path):
+    from llm_training_b200.lightning import FSDP2Strategy, LearningRateMonitor
+    from llm_training_b200.lightning.cli.config import (instantiate, instantiate_nested, load_config, parse_overrides,
+                                                        set_by_path)
+    cfg_file = tmp_path / 'c.yaml'
+    cfg_file.write_text('''
+trainer:
+  strategy:
+    class_path: llm_training.lightning.FSDP2Strategy
+    init_args:
+      tensor_parallel_size: 2
+  callbacks:
+    - class_path: LearningRateMonitor
+model:
+  class_path: llm_training.lms.CLM
+  init_args.config:
+    model:
+      model_class: llm_training.models.Llama
+      model_config: {vocab_size: 64, hidden_size: 32, intermediate_size: 64, num_hidden_layers: 1,
+                     num_attention_heads: 2, num_key_value_heads: 1}
+    optim:
+      optimizer_class: deepspeed.ops.adam.FusedAdam
+      optimizer_kwargs: {lr: 1e-5}
+''')
+    configs, overrides, positional = parse_overrides(['fit', '--config', str(cfg_file), '--trainer.num_nodes', '2',
+                                                      '--model.init_args.config.optim.optimizer_kwargs.lr=3e-4'])
+    assert positional == ['fit'] and overrides['trainer.num_nodes'] == 2
+    cfg = load_config(configs)
+    for k, v in overrides.items():
+        set_by_path(cfg, k, v)
+    assert cfg['model']['init_args']['config']['optim']['optimizer_kwargs']['lr'] == 3e-4      # '1e-5' style floats
+    assert cfg['trainer']['num_nodes'] == 2
+    trainer_kwargs = instantiate_nested(cfg['trainer'])
+    assert isinstance(trainer_kwargs['strategy'], FSDP2Strategy)
+    assert isinstance(trainer_kwargs['callbacks'][0], LearningRateMonitor)          # short name resolution
+    lm = instantiate(cfg['model'])
+    from llm_training_b200.lms import CLM, ModelProvider
+    from llm_training_b200.optim import FusedAdamW
+    assert isinstance(lm, CLM) and isinstance(lm.config.model, ModelProvider)
+    assert lm.config.optim.optimizer_class is FusedAdamW                            # DeepSpeed class aliased
+    assert lm.config.model.model_config.hidden_size == 32
+
+
+def test_cli_fit_runs_and_checkpoint_embeds_config(tmp_path):
+    from llm_training_b200.lightning.cli import LightningCLI
+    cfg_file = tmp_path / 'fit.yaml'
+    cfg_file.write_text(f'''
+seed_everything: 1
+trainer:
+  precision: 32-true
+  accelerator: cpu
+  logger:
+    class_path: llm_training.lightning.CSVLogger
+    init_args: {{save_dir: {tmp_path}/logs}}
+  max_epochs: 1
+  enable_progress_bar: false
+  callbacks:
+    - class_path: llm_training.lightning.ModelCheckpoint
+      init_args: {{save_on_train_epoch_end: true, save_top_k: -1}}
+model:
+  class_path: llm_training.lms.CLM
+  init_args.config:
+    init_weights: true
+    load_weights: false
+    model:
+      model_class: llm_training.models.Llama
+      model_config: {dict(TINY_LLAMA)}
+    optim:
+      optimizer_class: torch.optim.AdamW
+      optimizer_kwargs: {{lr: 1e-3}}
+data:
+  class_path: llm_training.data.DummyDataModule
+  init_args.config: {{batch_size: 2, vocab_size: 256, max_length: 16, num_samples: 8, base_seed: 1, pin_memory: false}}
+''')
+    cli = LightningCLI(['fit', '--config', str(cfg_file)])
+    assert cli.trainer.global_step == 4
+    ckpt = os.path.join(cli.trainer.log_dir, 'checkpoints', 'epoch=0-step=4.ckpt')
+    assert os.path.exists(ckpt)
+    from llm_training_b200.lightning.checkpoint_io import read_checkpoint_state_dict
+    state, meta = read_checkpoint_state_dict(ckpt)
+    assert meta['config']['model']['class_path'] == 'llm_training.lms.CLM' and meta['config']['world_size'] == 1
+    assert 'model.layers.0.self_attn.q_proj.weight' in state and 'consumed_samples.n' in state
+    assert int(state['consumed_samples.n']) == 8
+
+
+# ---------------------------------------------------------------------------------------------------- schedules
+def _lrs(cls, steps=12, **kw):
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.SGD([p], lr=1.0)
+    sched = cls(opt, **kw)
+    out = []
+    for _ in range(steps):
+        out.append(opt.param_groups[0]['lr'])
+        opt.step()
+        sched.step()
+    return out, sched, opt
+
+
+def test_lr_schedules_values_and_resume():
+    from llm_training_b200.lr_schedulers import ConstantWarmupLR, CosineAnnealingWarmupLR, LinearWarmupLR
+    cos, _, _ = _lrs(CosineAnnealingWarmupLR, num_warmup_steps=3, num_total_steps=10, min_lr=0.1)
+    assert cos[:3] == pytest.approx([1 / 3, 2 / 3, 1.0]) and cos[3] == pytest.approx(1.0)
+    assert cos[10] == pytest.approx(0.1) and all(a >= b - 1e-12 for a, b in zip(cos[3:10], cos[4:11]))
+    assert cos[6] == pytest.approx(0.1 + 0.9 * (1 + math.cos(math.pi * 3 / 7)) / 2)
+    const, _, _ = _lrs(ConstantWarmupLR, num_warmup_steps=4)
+    assert const[:4] == pytest.approx([0.25, 0.5, 0.75, 1.0]) and set(const[4:]) == {1.0}
+    lin, _, _ = _lrs(LinearWarmupLR, num_warmup_steps=3, num_total_steps=10, min_lr=0.1)
+    assert lin[:4] == pytest.approx([0.25, 0.5, 0.75, 1.0]) and lin[10] == pytest.approx(0.1)
+    # state_dict round trip continues the same curve
+    first, sched, opt = _lrs(CosineAnnealingWarmupLR, steps=5, num_warmup_steps=3, num_total_steps=10, min_lr=0.1)
+    state = sched.state_dict()
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt2 = torch.optim.SGD([p], lr=1.0)
+    sched2 = CosineAnnealingWarmupLR(opt2, num_warmup_steps=3, num_total_steps=10, min_lr=0.1)
+    sched2.load_state_dict(state)
+    opt2.param_groups[0]['lr'] = opt.param_groups[0]['lr']
+    rest = []
+    for _ in range(5):
+        rest.append(opt2.param_groups[0]['lr'])
+        opt2.step()
+        sched2.step()
+    assert first + rest == pytest.approx(cos[:10])
+
+
+# ---------------------------------------------------------------------------------------------------- rope
+@pytest.mark.parametrize('kind,scaling', [
+    ('default', None), ('linear', {'factor': 4.0}), ('dynamic', {'factor': 2.0}),
+    ('yarn', {'factor': 8.0}), ('longrope', {'factor': 4.0, 'short_factor': [1.0] * 16, 'long_factor': [2.0] * 16}),
+    ('llama3', {'factor': 8.0, 'low_freq_factor': 1.0, 'high_freq_factor': 4.0,
+                'original_max_position_embeddings': 64})])
+def test_rope_initialisers(kind, scaling):
+    from llm_training_b200.ops import ROPE_INIT_FUNCTIONS, RoPEConfig
+    cfg = RoPEConfig(type=kind, base=10000.0, dim=32, max_position_embeddings=256, scaling_config=scaling)
+    inv, factor = ROPE_INIT_FUNCTIONS[kind](cfg, None, 1024)
+    base = 1.0 / (10000.0 ** (torch.arange(0, 32, 2).float() / 32))
+    assert inv.shape == (16,) and torch.isfinite(inv).all() and factor > 0
+    if kind == 'default':
+        assert torch.allclose(inv, base)
+    if kind == 'linear':
+        assert torch.allclose(inv, base / 4)
+    if kind == 'longrope':
+        assert torch.allclose(inv, base / 2) and factor == pytest.approx(math.sqrt(1 + math.log(4) / math.log(256)))
+    if kind == 'llama3':
+        assert torch.allclose(inv[0], base[0]) and torch.allclose(inv[-1], base[-1] / 8)    # high freq kept, low / 8
+    if kind == 'yarn':
+        assert factor == pytest.approx(0.1 * math.log(8) + 1) and (inv <= base + 1e-9).all()
+    if kind == 'dynamic':
+        assert (inv <= base + 1e-9).all() and inv[0] == pytest.approx(1.0)
+    with pytest.raises(KeyError):
+        RoPEConfig(type='linear', base=1e4, dim=32, max_position_embeddings=8, scaling_config={})
+
+
+# ---------------------------------------------------------------------------------------------------- ops (CPU)
+def test_shift_labels_and_segment_bounds_and_packed_attention_reference():
+    from llm_training_b200.ops import prepare_4d_causal_attention_mask, segment_bounds, shift_labels
+    from llm_training_b200.ops.reference import attention_ref
+    labels = torch.tensor([[1, 2, 3], [4, 5, 6]])
+    assert shift_labels(labels).tolist() == [[2, 3, -100], [5, 6, -100]]
+    mask = torch.tensor([[1, 1, 2, 2, 2, 0], [1, 1, 1, 1, 1, 1]])
+    start, end = segment_bounds(mask, 2, 6, torch.device('cpu'))
+    assert start.tolist() == [0, 0, 2, 2, 2, 5, 6, 6, 6, 6, 6, 6]
+    assert end.tolist() == [2, 2, 5, 5, 5, 6, 12, 12, 12, 12, 12, 12]
+    # packed reference == eager attention with the 4-D block-diagonal mask, per batch row
+    torch.manual_seed(0)
+    hq, hkv, d = 4, 2, 8
+    q, k, v = torch.randn(12, hq, d), torch.randn(12, hkv, d), torch.randn(12, hkv, d)
+    packed = attention_ref(q, k, v, start)
+    add = prepare_4d_causal_attention_mask(mask, (2, 6), torch.zeros(1), 0)
+    for b in range(2):
+        qb = q[b * 6:(b + 1) * 6].transpose(0, 1)
+        kb = k[b * 6:(b + 1) * 6].transpose(0, 1).repeat_interleave(2, 0)
+        vb = v[b * 6:(b + 1) * 6].transpose(0, 1).repeat_interleave(2, 0)
+        w = torch.softmax(qb @ kb.transpose(1, 2) / math.sqrt(d) + add[b], dim=-1)
+        eager = (w @ vb).transpose(0, 1)
+        valid = mask[b] != 0
+        assert torch.allclose(packed[b * 6:(b + 1) * 6][valid], eager[valid], atol=1e-5)
+
+
+def test_fused_loss_functions_cpu_paths_match_reference_math():
+    from llm_training_b200.ops import cross_entropy, fused_linear_cross_entropy, fused_linear_logprob
+    torch.manual_seed(0)
+    h, w = torch.randn(10, 16), torch.randn(32, 16)
+    labels = torch.randint(0, 32, (10,))
+    labels[3] = -100
+    logits = h @ w.t()
+    ref = torch.nn.functional.cross_entropy(logits, labels, ignore_index=-100)
+    assert fused_linear_cross_entropy(h, w, labels) == pytest.approx(ref.item(), rel=1e-5)
+    assert cross_entropy(logits.view(2, 5, 32), labels.view(2, 5)) == pytest.approx(ref.item(), rel=1e-5)
+    lp = fused_linear_logprob(h, w, labels)
+    manual = logits.log_softmax(-1).gather(1, labels.clamp_min(0)[:, None])[:, 0] * (labels != -100)
+    assert torch.allclose(lp, manual, atol=1e-5)
+
+
+# ---------------------------------------------------------------------------------------------------- objectives
+def _preference_batch(vocab=256, rows=2):
+    g = torch.Generator().manual_seed(0)
+    batch = {}
+    for side, n in (('chosen', 12), ('rejected', 9)):
+        ids = torch.randint(1, vocab, (rows, n), generator=g)
+        labels = ids.clone()
+        labels[:, :4] = -100
+        batch |= {f'{side}_input_ids': ids, f'{side}_attention_mask': torch.ones_like(ids),
+                  f'{side}_position_ids': torch.arange(n)[None], f'{side}_labels': labels}
+    return batch
+
+
+def _lm(kind, **extra):
+    from llm_training_b200.lms import DPO, ORPO, DPOConfig, ORPOConfig
+    cfg = dict(init_weights=True, load_weights=False,
+               model=dict(model_class='llm_training.models.Llama', model_config=dict(TINY_LLAMA)), **extra)
+    lm = DPO(DPOConfig.model_validate(cfg)) if kind == 'dpo' else ORPO(ORPOConfig.model_validate(cfg))
+    torch.manual_seed(0)
+    lm.configure_model()
+    return lm
+
+
+def test_dpo_loss_matches_manual_computation():
+    lm = _lm('dpo', beta=0.2, label_smoothing=0.1)
+    batch = _preference_batch()
+    with torch.no_grad():                       # make policy != reference
+        for p in lm.model.parameters():
+            p.add_(0.01 * torch.randn_like(p))
+    loss = lm.training_step(batch, 0)
+
+    def logps(model, side):
+        ids, labels = batch[f'{side}_input_ids'], batch[f'{side}_labels']
+        logp = model(input_ids=ids).logits.float().log_softmax(-1)[:, :-1]
+        tgt = labels[:, 1:]
+        m = tgt != -100
+        return (logp.gather(2, tgt.clamp_min(0)[..., None])[..., 0] * m).sum(-1)
+
+    pi = logps(lm.model, 'chosen') - logps(lm.model, 'rejected')
+    ref = logps(lm.ref_model, 'chosen') - logps(lm.ref_model, 'rejected')
+    z = 0.2 * (pi - ref)
+    manual = (-torch.nn.functional.logsigmoid(z) * 0.9 - torch.nn.functional.logsigmoid(-z) * 0.1).mean()
+    assert loss.item() == pytest.approx(manual.item(), rel=1e-4, abs=1e-5)
+    assert not any(p.requires_grad for p in lm.ref_model.parameters())
+    loss.backward()
+    assert all(p.grad is not None for p in lm.model.parameters())
+
+
+def test_orpo_loss_matches_manual_computation():
+    lm = _lm('orpo', beta=0.25)
+    batch = _preference_batch()
+    loss = lm.training_step(batch, 0)
+
+    def mean_logps(side):
+        ids, labels = batch[f'{side}_input_ids'], batch[f'{side}_labels']
+        logits = lm.model(input_ids=ids).logits.float()
+        logp = logits.log_softmax(-1)[:, :-1]
+        tgt = labels[:, 1:]
+        m = tgt != -100
+        per = (logp.gather(2, tgt.clamp_min(0)[..., None])[..., 0] * m).sum(-1) / m.sum(-1)
+        return per, logits, tgt
+
+    c, c_logits, c_tgt = mean_logps('chosen')
+    r, _, _ = mean_logps('rejected')
+    log_odds = (c - r) - (torch.log1p(-torch.exp(c)) - torch.log1p(-torch.exp(r)))
+    or_loss = -(0.25 * torch.nn.functional.logsigmoid(log_odds)).mean()
+    ce = torch.nn.functional.cross_entropy(c_logits[:, :-1].flatten(0, 1), c_tgt.flatten(), ignore_index=-100)
+    assert loss.item() == pytest.approx((or_loss + ce).item(), rel=1e-4)
+
+
+def test_clm_neftune_and_frozen_modules():
+    from llm_training_b200.lms import CLM, CLMConfig
+    cfg = CLMConfig.model_validate(dict(init_weights=True, load_weights=False, neftune_alpha=5.0,
+                                        frozen_modules=[r'layers\.0\.'],
+                                        model=dict(model_class='llm_training.models.Llama',
+                                                   model_config=dict(TINY_LLAMA))))
+    lm = CLM(cfg)
+    lm.configure_model()
+    assert lm.model.neftune_alpha == 5.0
+    assert not any(p.requires_grad for p in lm.model.layers[0].parameters())
+    assert all(p.requires_grad for p in lm.model.layers[1].parameters())
+    ids = torch.randint(0, 256, (2, 10))
+    batch = dict(input_ids=ids, attention_mask=torch.ones_like(ids), labels=ids)
+    lm.train()
+    a = lm.training_step(batch, 0).item()
+    b = lm.training_step(batch, 0).item()
+    assert a != b                                   # fresh noise every step
+    lm.eval()
+    assert lm._forward_loss(batch)[0].item() == lm._forward_loss(batch)[0].item()
+    assert 'model.lm_head.weight' in lm.required_keys
+
+
+# ---------------------------------------------------------------------------------------------------- HF interop
+def test_hf_state_dict_round_trip_and_logit_parity_with_transformers():
+    transformers = pytest.importorskip('transformers')
+    from llm_training_b200.models import Llama, LlamaConfig
+    torch.manual_seed(0)
+    model = Llama(LlamaConfig(**TINY_LLAMA, rope_theta=10000.0, rms_norm_eps=1e-5)).eval()
+    sd = model.state_dict()
+    hf_sd = model.convert_state_dict_to_hf(sd)
+    assert 'model.layers.0.self_attn.q_proj.weight' in hf_sd and 'lm_head.weight' in hf_sd
+    assert set(model.convert_state_dict_from_hf(hf_sd)) == set(sd)
+    hf = model.get_hf_model().eval()
+    assert isinstance(hf, transformers.LlamaForCausalLM)
+    ids = torch.randint(0, 256, (2, 12))
+    with torch.no_grad():
+        ours = model(input_ids=ids).logits
+        theirs = hf(input_ids=ids).logits
+    assert torch.allclose(ours, theirs, atol=2e-4), (ours - theirs).abs().max()
+
+
+def test_convert_to_hf_from_dcp_checkpoint(tmp_path):
+    pytest.importorskip('transformers')
+    from llm_training_b200.lightning.cli import LightningCLI
+    cfg_file = tmp_path / 'fit.yaml'
+    cfg_file.write_text(f'''
+trainer:
+  strategy:
+    class_path: llm_training.lightning.FSDP2Strategy
+    init_args: {{data_parallel_size: 1}}
+  precision: 32-true
+  accelerator: cpu
+  logger:
+    class_path: llm_training.lightning.CSVLogger
+    init_args: {{save_dir: {tmp_path}/logs}}
+  max_epochs: 1
+  enable_progress_bar: false
+  callbacks:
+    - class_path: llm_training.lightning.ModelCheckpoint
+      init_args: {{save_on_train_epoch_end: true}}
+model:
+  class_path: llm_training.lms.CLM
+  init_args.config:
+    init_weights: true
+    load_weights: false
+    model:
+      model_class: llm_training.models.Llama
+      model_config: {dict(TINY_LLAMA)}
+    optim:
+      optimizer_class: torch.optim.AdamW
+      optimizer_kwargs: {{lr: 1e-3}}
+data:
+  class_path: llm_training.data.DummyDataModule
+  init_args.config: {{batch_size: 2, vocab_size: 256, max_length: 16, num_samples: 4, base_seed: 1, pin_memory: false}}
+''')
+    cli = LightningCLI(['fit', '--config', str(cfg_file)])
+    ckpt = os.path.join(cli.trainer.log_dir, 'checkpoints', 'epoch=0-step=2.ckpt')
+    assert os.path.isdir(ckpt)                                   # sharded layout: DCP directory + meta.pt
+    import importlib.util
+    spec = importlib.util.spec_from_file_location(
+        'convert_to_hf', os.path.join(os.path.dirname(os.path.dirname(__file__)), 'scripts', 'convert_to_hf.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = mod.convert(ckpt, str(tmp_path / 'hf'))
+    from transformers import AutoModelForCausalLM
+    hf = AutoModelForCausalLM.from_pretrained(out)
+    trained = cli.model.model
+    assert torch.allclose(hf.model.layers[1].mlp.down_proj.weight, trained.layers[1].mlp.down_proj.weight.detach())
+    assert torch.allclose(hf.lm_head.weight, trained.lm_head.weight.detach())
