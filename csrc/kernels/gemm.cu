@@ -18,6 +18,7 @@
 #include <cuda.h>
 
 #include <mutex>
+#include <type_traits>
 #include <unordered_map>
 
 #include "common.cuh"
@@ -56,7 +57,20 @@ struct Cfg {
 struct Params {
   int M, N, K;
   int has_residual;
+  int rows_per_rank;   // dist variants: rows of the gathered A / scattered C owned by one rank
 };
+
+// Fused collective variants (tensor parallel paths):
+//   kDistA : A is the row-wise concatenation of every rank's [rows_per_rank, K] block living in symmetric memory;
+//            the TMA producer loads each A tile straight from its owner over NVLink (all-gather -> GEMM)
+//   kDistC : the [M, N] result is reduce-scattered by rows; each tile is TMA-reduce-ADDED into the owner rank's
+//            [rows_per_rank, N] buffer (GEMM -> reduce-scatter)
+constexpr int kMaxDistRanks = 8;
+struct DistMaps {
+  CUtensorMap a[kMaxDistRanks];
+  CUtensorMap c[kMaxDistRanks];
+};
+struct NoDist {};
 
 // grouped rasterisation: consecutive tile ids walk down M inside a band of kGroupM m-tiles so that the
 // ~148 tiles in flight share A and B panels in L2
@@ -71,10 +85,12 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   tn = r / group_m;
 }
 
-template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT>
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, bool kDistA = false, bool kDistC = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, Params p) {
+                 const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, Params p,
+                 const __grid_constant__ typename std::conditional<(kDistA || kDistC), DistMaps, NoDist>::type dist) {
+  static_assert(!(kDistA && kAMn), "gathered A must be K-major");
   using C = Cfg<kCtaGroup>;
   constexpr int kOutChunkCols = 128 / (int)sizeof(OutT);  // columns per 128-byte staging row: 64 bf16 / 32 fp32
   constexpr int kNumChunks = BN / kOutChunkCols;
@@ -152,8 +168,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t fb = full0 + 8u * stage;
           const int k0 = kb * BK;
           if (kCtaGroup == 1 || is_leader) mbar_arrive_expect_tx(full_bar(stage), C::kStageBytes * kCtaGroup);
+          [[maybe_unused]] const CUtensorMap* mapA = &tmA;
+          [[maybe_unused]] int m_local = m0;
+          if constexpr (kDistA) {                      // A tile lives on rank m0 / rows_per_rank
+            const int owner = min(m0 / p.rows_per_rank, kMaxDistRanks - 1);
+            mapA = &dist.a[owner];
+            m_local = m0 - owner * p.rows_per_rank;
+          }
           if constexpr (kCtaGroup == 1) {
-            if constexpr (!kAMn) tma_load_2d(sa, &tmA, fb, k0, m0);
+            if constexpr (kDistA) tma_load_2d(sa, mapA, fb, k0, m_local);
+            else if constexpr (!kAMn) tma_load_2d(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j) tma_load_2d(sa + j * (BK * 128), &tmA, fb, m0 + j * 64, k0);
@@ -164,7 +188,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int j = 0; j < C::kBRows / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tmB, fb, n0 + j * 64, k0);
             }
           } else {
-            if constexpr (!kAMn) tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
+            if constexpr (kDistA) tma_load_2d_cg2(sa, mapA, fb, k0, m_local);
+            else if constexpr (!kAMn) tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j) tma_load_2d_cg2(sa + j * (BK * 128), &tmA, fb, m0 + j * 64, k0);
@@ -303,7 +328,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         fence_proxy_async_smem();
         asm volatile("bar.sync 2, 128;" ::: "memory");
         if (store_leader) {
-          tma_store_2d(&tmC, sbuf, c0, m0);
+          if constexpr (kDistC) {
+            const int owner = min(m0 / p.rows_per_rank, kMaxDistRanks - 1);
+            tma_reduce_add_2d(&dist.c[owner], sbuf, c0, m0 - owner * p.rows_per_rank);
+          } else {
+            tma_store_2d(&tmC, sbuf, c0, m0);
+          }
           tma_store_commit();
         }
       }
@@ -361,11 +391,11 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows
   return 0;
 }
 
-template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT>
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, bool kDistA = false, bool kDistC = false>
 int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const CUtensorMap& r, Params p,
-           int max_ctas, cudaStream_t stream) {
+           int max_ctas, cudaStream_t stream, const DistMaps* dist_maps = nullptr) {
   using C = Cfg<kCtaGroup>;
-  auto kern = gemm_bf16_kernel<kCtaGroup, kAMn, kBMn, OutT>;
+  auto kern = gemm_bf16_kernel<kCtaGroup, kAMn, kBMn, OutT, kDistA, kDistC>;
   static bool configured = false;  // per instantiation
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
@@ -392,7 +422,9 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p);
+  cudaError_t e;
+  if constexpr (kDistA || kDistC) e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, *dist_maps);
+  else e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, NoDist{});
   if (e != cudaSuccess) {
     set_error("gemm launch: %s", cudaGetErrorString(e));
     return 2;
@@ -443,7 +475,7 @@ extern "C" int llmt_gemm_bf16(const void* A, const void* B, void* Cout, const vo
   } else {
     tr = tc;
   }
-  Params p{M, N, K, R ? 1 : 0};
+  Params p{M, N, K, R ? 1 : 0, 0};
 
 #define LLMT_GEMM_DISPATCH(CG, AMN, BMN)                                                        \
   return out_fp32 ? launch<CG, AMN, BMN, float>(ta, tb, tc, tr, p, max_ctas, stream)            \
@@ -460,4 +492,66 @@ extern "C" int llmt_gemm_bf16(const void* A, const void* B, void* Cout, const vo
     LLMT_GEMM_DISPATCH(2, true, false);
   }
 #undef LLMT_GEMM_DISPATCH
+}
+
+
+// Fused collective GEMMs for tensor / sequence parallelism.  Both operands K-major, bf16 output.
+//   mode 1 (all-gather -> GEMM):  C[M, N] = concat_r(A_r)[M, K] * B[N, K]^T, A_r = a_ptrs[r] is rank r's
+//          [rows_per_rank, K] block in symmetric memory (lda elements per row); C is a local buffer.
+//   mode 2 (GEMM -> reduce-scatter): A local [M, K]; the [M, N] product is added, rows r*rows_per_rank.., into
+//          c_ptrs[r] ([rows_per_rank, N], ldc elements per row) on rank r.  The targets must be initialised
+//          (zeros or the residual) and a cross-rank barrier must separate initialisation, this kernel and the
+//          first read of the result.
+extern "C" int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a_ptrs, const void* B, void* Cout,
+                                   void* const* c_ptrs, int world, int rows_per_rank, int M, int N, int K,
+                                   int64_t lda, int64_t ldb, int64_t ldc, int b_mn_major, int cta_group,
+                                   int max_ctas, cudaStream_t stream) {
+  LLMT_REQUIRE(mode == 1 || mode == 2, "gemm_dist: mode must be 1 (AG->GEMM) or 2 (GEMM->RS)");
+  LLMT_REQUIRE(world >= 1 && world <= kMaxDistRanks, "gemm_dist: world size %d not in [1, %d]", world, kMaxDistRanks);
+  LLMT_REQUIRE(rows_per_rank > 0 && rows_per_rank % BM == 0 && (int64_t)rows_per_rank * world == M,
+               "gemm_dist: rows_per_rank=%d must be a multiple of %d and rows_per_rank * world == M=%d",
+               rows_per_rank, BM, M);
+  LLMT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "gemm_dist: leading dimensions must be multiples of 8");
+  LLMT_REQUIRE(cta_group == 1 || cta_group == 2, "gemm_dist: cta_group must be 1 or 2");
+  if (max_ctas <= 0) max_ctas = num_sms();
+  static DistMaps maps;   // filled per call; copied into kernel parameters by the launch
+  CUtensorMap ta, tb, tc;
+  int rc;
+  const int b_rows = BN / cta_group;
+  if (!b_mn_major) rc = make_tmap_2d(&tb, B, 2, N, K, ldb, BK, b_rows);   // B stored [N, K]
+  else             rc = make_tmap_2d(&tb, B, 2, K, N, ldb, 64, BK);       // B stored [K, N]
+  if (rc) return rc;
+  Params p{M, N, K, 0, rows_per_rank};
+  if (mode == 1) {
+    for (int r = 0; r < kMaxDistRanks; ++r) {
+      const void* src = a_ptrs[r < world ? r : world - 1];
+      rc = make_tmap_2d(&maps.a[r], src, 2, rows_per_rank, K, lda, BK, BM);
+      if (rc) return rc;
+      maps.c[r] = maps.a[r];
+    }
+    rc = make_tmap_2d(&tc, Cout, 2, M, N, ldc, 64, BM);
+    if (rc) return rc;
+    ta = maps.a[0];
+    if (b_mn_major) {
+      if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+      return launch<2, false, true, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    }
+    if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    return launch<2, false, false, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  }
+  rc = make_tmap_2d(&ta, A, 2, M, K, lda, BK, BM);
+  if (rc) return rc;
+  for (int r = 0; r < kMaxDistRanks; ++r) {
+    void* dst = c_ptrs[r < world ? r : world - 1];
+    rc = make_tmap_2d(&maps.c[r], dst, 2, rows_per_rank, N, ldc, 64, BM);
+    if (rc) return rc;
+    maps.a[r] = ta;
+  }
+  tc = maps.c[0];
+  if (b_mn_major) {
+    if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    return launch<2, false, true, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  }
+  if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  return launch<2, false, false, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
 }

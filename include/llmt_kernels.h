@@ -29,6 +29,33 @@ int llmt_gemm_bf16(const void* A, const void* B, void* C, const void* R, int M, 
                    int64_t ldb, int64_t ldc, int64_t ldr, int a_mn_major, int b_mn_major, int out_fp32,
                    int cta_group, int max_ctas, cudaStream_t stream);
 
+/* Fused collective GEMMs for tensor/sequence parallelism over symmetric (peer-mapped) memory; replaces the
+ * DTensor all-gather / reduce-scatter around the column-/row-parallel linears
+ * (src/llm_training/models/llama/llama_model.py:223-238).  a_ptrs / c_ptrs are HOST arrays of `world` device
+ * pointers (this rank's view of every peer's buffer).
+ *   mode 1: C[M,N] = concat_r(A_r)[M,K] * op(B)   (A tiles are TMA-loaded from their owner rank over NVLink)
+ *   mode 2: rows r*rows_per_rank.. of A[M,K] * op(B) are TMA-reduce-added into c_ptrs[r] (must be initialised;
+ *           barrier before and after). */
+int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a_ptrs, const void* B, void* C,
+                        void* const* c_ptrs, int world, int rows_per_rank, int M, int N, int K, int64_t lda,
+                        int64_t ldb, int64_t ldc, int b_mn_major, int cta_group, int max_ctas, cudaStream_t stream);
+
+/* ---- NVLink collectives for the sharding engine (csrc/kernels/comm.cu); replace NCCL all-gather /
+ *      reduce-scatter issued by FSDP2 / ZeRO (llama_model.py:263-268, deepspeed_strategy.py:39-44) ------------ */
+int llmt_comm_barrier(const void* const* signal_pads, int rank, int world, int slot_base, uint32_t epoch,
+                      cudaStream_t stream);
+int llmt_comm_allgather_pull(const void* const* full_ptrs, int rank, int world, int64_t shard_bytes,
+                             cudaStream_t stream);
+int llmt_comm_rs_num_partials(void);
+int llmt_comm_rs_sumsq(const void* const* grad_ptrs, int rank, int world, int64_t shard_elems, int is_fp32,
+                       void* out_shard, float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream);
+int llmt_comm_allreduce_f32(const void* const* buf_ptrs, const void* const* signal_pads, int rank, int world,
+                            int slot_base, uint32_t epoch, float* value, int n, cudaStream_t stream);
+int llmt_comm_adamw_push(float* master, float* m, float* v, const void* grad_shard, const void* const* param_ptrs,
+                         int rank, int world, int64_t shard_elems, int grad_is_fp32, float lr, float beta1,
+                         float beta2, float eps, float weight_decay, int step, float grad_scale, float max_norm,
+                         const float* norm_sq, cudaStream_t stream);
+
 /* ---- packed causal attention (src/llm_training/ops/attention_op.py:538-654, flash-attn varlen) -----------
  * qkv: bf16 [T, (Hq+2Hkv)*D]; out: bf16 [T, Hq*D]; lse: fp32 [Hq, T] (log2 units); seg_start/seg_end int32 [T].
  * bwd scratch: delta fp32 [Hq, T]; dq_acc fp32 [T, Hq*D], must be zero on entry. */

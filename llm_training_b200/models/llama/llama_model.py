@@ -56,6 +56,9 @@ class LlamaMLP(nn.Module):
         if pre_norm is not None:
             gate_up = norm_multi_linear(x, pre_norm.weight, pre_norm.variance_epsilon,
                                         [self.gate_proj.weight, self.up_proj.weight])
+        elif tp is not None:
+            gate_up = tp.column_linear(x, [self.gate_proj.weight, self.up_proj.weight],
+                                       [self.gate_proj.bias, self.up_proj.bias])
         else:
             gate_up = multi_linear(x, [self.gate_proj.weight, self.up_proj.weight],
                                    [self.gate_proj.bias, self.up_proj.bias])
@@ -94,6 +97,9 @@ class LlamaAttention(nn.Module):
         if pre_norm is not None:
             qkv = norm_multi_linear(hidden_states, pre_norm.weight, pre_norm.variance_epsilon,
                                     [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight])
+        elif tp is not None:
+            qkv = tp.column_linear(hidden_states, [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
+                                   [self.q_proj.bias, self.k_proj.bias, self.v_proj.bias])
         else:
             qkv = multi_linear(hidden_states, [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
                                [self.q_proj.bias, self.k_proj.bias, self.v_proj.bias])
@@ -129,13 +135,11 @@ class LlamaDecoderLayer(nn.Module):
             # norm + projection fused (normalised activations are recomputed in backward, not stored)
             hidden_states = self.self_attn(hidden_states, ctx, residual=hidden_states, pre_norm=self.input_layernorm)
             return self.mlp(hidden_states, residual=hidden_states, pre_norm=self.post_attention_layernorm)
+        # tensor parallel: the norms run on [T/tp, d] token shards (sequence parallel); the column-parallel
+        # projections gather them (fused all-gather -> GEMM on NVLink), the row-parallel ones reduce-scatter back
         normed = self.input_layernorm(hidden_states)
-        if tp is not None:
-            normed = tp.gather_sequence(normed)          # SP: [T/tp, d] -> [T, d]
         hidden_states = self.self_attn(normed, ctx, residual=hidden_states)
         normed = self.post_attention_layernorm(hidden_states)
-        if tp is not None:
-            normed = tp.gather_sequence(normed)
         return self.mlp(normed, residual=hidden_states, tp=tp)
 
 

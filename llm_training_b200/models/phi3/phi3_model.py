@@ -40,7 +40,8 @@ class Phi3MLP(nn.Module):
 
     def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None, tp: Any = None,
                 resid_pdrop: float = 0.0) -> torch.Tensor:
-        act = silu_mul_fused(linear(x, self.gate_up_proj.weight))
+        gate_up = linear(x, self.gate_up_proj.weight) if tp is None else tp.column_linear(x, [self.gate_up_proj.weight])
+        act = silu_mul_fused(gate_up)
         if resid_pdrop > 0.0 and self.training:
             out = tp.row_linear(act, self.down_proj.weight, None, None) if tp is not None else \
                 linear(act, self.down_proj.weight)
@@ -72,7 +73,8 @@ class Phi3Attention(nn.Module):
                 resid_pdrop: float = 0.0) -> torch.Tensor:
         tp = ctx.tp
         shards = 1 if tp is None else tp.size
-        qkv = linear(hidden_states, self.qkv_proj.weight)
+        qkv = linear(hidden_states, self.qkv_proj.weight) if tp is None \
+            else tp.column_linear(hidden_states, [self.qkv_proj.weight])
         attn = attention_core(
             qkv, ctx, num_heads=self.num_heads // shards, num_kv_heads=self.num_key_value_heads // shards,
             head_dim=self.head_dim, impl=self.config._attn_implementation, window=self.sliding_window,
@@ -104,13 +106,9 @@ class Phi3DecoderLayer(nn.Module):
 
     def forward(self, hidden_states: torch.Tensor, ctx: PackedContext) -> torch.Tensor:
         tp = ctx.tp
-        normed = self.input_layernorm(hidden_states)
-        if tp is not None:
-            normed = tp.gather_sequence(normed)
+        normed = self.input_layernorm(hidden_states)          # [T/tp, d] token shard under tensor parallelism
         hidden_states = self.self_attn(normed, ctx, residual=hidden_states, resid_pdrop=self.resid_pdrop)
         normed = self.post_attention_layernorm(hidden_states)
-        if tp is not None:
-            normed = tp.gather_sequence(normed)
         return self.mlp(normed, residual=hidden_states, tp=tp, resid_pdrop=self.resid_pdrop)
 
 

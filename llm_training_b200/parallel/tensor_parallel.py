@@ -206,6 +206,116 @@ class _VocabParallelLoss(torch.autograd.Function):
 
 
 # ---------------------------------------------------------------------------------------------------
+# fused collective GEMMs over NVLink symmetric memory (CUDA/bf16 path)
+# ---------------------------------------------------------------------------------------------------
+class _SymmetricRing:
+    """Two alternating symmetric buffers per shape: buffer k is rewritten only after the barrier of use k+1, i.e.
+    after every peer has finished reading it (see the protocol note in ``parallel/nvlink.py``)."""
+
+    def __init__(self, comm: Any) -> None:
+        self.comm = comm
+        self.buffers: dict[tuple, list] = {}
+        self.turn: dict[tuple, int] = {}
+
+    def next(self, rows: int, cols: int):
+        key = (rows, cols)
+        if key not in self.buffers:
+            self.buffers[key] = [self.comm.alloc(rows * cols, torch.bfloat16) for _ in range(2)]
+            self.turn[key] = 0
+        self.turn[key] ^= 1
+        buf = self.buffers[key][self.turn[key]]
+        return buf, buf.tensor.view(rows, cols)
+
+
+def _gemm_dist(mode: int, a: torch.Tensor | None, a_ptrs, b: torch.Tensor, c: torch.Tensor | None, c_ptrs, world: int,
+               rows_per_rank: int, m: int, n: int, k: int, lda: int, ldc: int, b_mn_major: bool) -> None:
+    import ctypes
+    null = (ctypes.c_void_p * 1)(0)
+    _lib.check(_lib.lib().llmt_gemm_bf16_dist(
+        _lib.c_int(mode), _lib.ptr(a), a_ptrs if a_ptrs is not None else null, _lib.ptr(b), _lib.ptr(c),
+        c_ptrs if c_ptrs is not None else null, _lib.c_int(world), _lib.c_int(rows_per_rank), _lib.c_int(m),
+        _lib.c_int(n), _lib.c_int(k), _lib.c_i64(lda), _lib.c_i64(b.stride(0)), _lib.c_i64(ldc),
+        _lib.c_int(b_mn_major), _lib.c_int(2), _lib.c_int(0), _lib.stream()), 'gemm_bf16_dist')
+
+
+class _FusedGatherLinear(torch.autograd.Function):
+    """``all_gather(x_local) @ [W_1; W_2; ...]^T`` as ONE kernel: A tiles are TMA-loaded from the peers' symmetric
+    buffers.  Backward: dW needs the gathered input (NCCL all-gather), dx is ``dy @ W`` fused with the
+    reduce-scatter."""
+
+    @staticmethod
+    def forward(ctx, x_local: torch.Tensor, tp: 'TensorParallelContext', *weights: torch.Tensor) -> torch.Tensor:
+        from ..ops.linear_op import _adjacent_rows_view
+        weight = weights[0] if len(weights) == 1 else _adjacent_rows_view(weights)
+        if weight is None:
+            weight = torch.cat([w.detach() for w in weights], dim=0)
+        rows, k = x_local.shape
+        n = weight.shape[0]
+        buf, view = tp.ring.next(rows, k)
+        view.copy_(x_local)
+        tp.comm.barrier()
+        out = torch.empty((rows * tp.size, n), dtype=x_local.dtype, device=x_local.device)
+        _gemm_dist(1, None, buf.peer_ptrs_at(0), weight, out, None, tp.size, rows, rows * tp.size, n, k, k, n, False)
+        ctx.save_for_backward(x_local, weight)
+        ctx.tp = tp
+        ctx.splits = [w.shape[0] for w in weights]
+        return out
+
+    @staticmethod
+    def backward(ctx, dy: torch.Tensor):
+        x_local, weight = ctx.saved_tensors
+        tp = ctx.tp
+        dy = dy.contiguous()
+        rows, k = x_local.shape
+        x_full = torch.empty((rows * tp.size, k), dtype=x_local.dtype, device=x_local.device)
+        dist.all_gather_into_tensor(x_full, x_local.contiguous(), group=tp.axis.group)
+        dws = gemm(dy, x_full, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0)
+        dx = _fused_linear_reduce_scatter(tp, dy, weight, None, b_mn_major=True)   # dy @ W, reduce-scattered
+        return (dx, None, *dws)
+
+
+def _fused_linear_reduce_scatter(tp: 'TensorParallelContext', x: torch.Tensor, weight: torch.Tensor,
+                                 residual: torch.Tensor | None, b_mn_major: bool) -> torch.Tensor:
+    m, k = x.shape
+    n = weight.shape[1] if b_mn_major else weight.shape[0]
+    rows = m // tp.size
+    buf, view = tp.ring.next(rows, n)
+    if residual is not None:
+        view.copy_(residual)            # the residual add rides in the reduction target
+    else:
+        view.zero_()
+    tp.comm.barrier()                   # every target is initialised
+    _gemm_dist(2, x, None, weight, None, buf.peer_ptrs_at(0), tp.size, rows, m, n, k, k, n, b_mn_major)
+    tp.comm.barrier()                   # every contribution has landed
+    return view.clone()
+
+
+class _FusedLinearReduceScatter(torch.autograd.Function):
+    """``reduce_scatter(x @ W_local^T) (+ residual)`` as ONE kernel: each output tile is TMA-reduce-added into its
+    owner rank's buffer.  Backward: the gathered dy feeds dx (fused all-gather -> GEMM) and dW."""
+
+    @staticmethod
+    def forward(ctx, x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor | None,
+                tp: 'TensorParallelContext') -> torch.Tensor:
+        ctx.save_for_backward(x, weight)
+        ctx.tp = tp
+        ctx.has_residual = residual is not None
+        return _fused_linear_reduce_scatter(tp, x.contiguous(), weight, residual, b_mn_major=False)
+
+    @staticmethod
+    def backward(ctx, dy_local: torch.Tensor):
+        x, weight = ctx.saved_tensors
+        tp = ctx.tp
+        dy_local = dy_local.contiguous()
+        rows, n = dy_local.shape
+        dy_full = torch.empty((rows * tp.size, n), dtype=dy_local.dtype, device=dy_local.device)
+        dist.all_gather_into_tensor(dy_full, dy_local, group=tp.axis.group)
+        dx = gemm(dy_full, weight, b_mn_major=True)
+        dw = gemm(dy_full, x.contiguous(), a_mn_major=True, b_mn_major=True)
+        return dx, dw, (dy_local if ctx.has_residual else None), None
+
+
+# ---------------------------------------------------------------------------------------------------
 # the context object handed to the models
 # ---------------------------------------------------------------------------------------------------
 class TensorParallelContext:
@@ -213,6 +323,30 @@ class TensorParallelContext:
         self.axis = axis
         self.size = axis.size()
         self.rank = axis.rank
+        self.comm = None
+        self.ring = None
+        if torch.cuda.is_available() and dist.is_initialized() and dist.get_backend(axis.group) == 'nccl':
+            from .comm import get_comm
+            comm = get_comm(axis)
+            if getattr(comm, 'is_nvlink', False):
+                self.comm = comm
+                self.ring = _SymmetricRing(comm)
+
+    def _fused_ok(self, x: torch.Tensor, weight: torch.Tensor, rows_per_rank: int) -> bool:
+        return (self.comm is not None and _lib.use_kernels(x) and weight.dtype == torch.bfloat16
+                and rows_per_rank % 128 == 0 and self.size <= 8)
+
+    def column_linear(self, x_local: torch.Tensor, weights: list[torch.Tensor],
+                      biases: list[torch.Tensor | None] | None = None) -> torch.Tensor:
+        """Sequence-sharded input ``[T/tp, d]`` -> ``[T, sum(out_i)/tp]``: all-gather + column-parallel projection(s),
+        one fused kernel on the NVLink path (reference: PrepareModuleInput + ColwiseParallel,
+        llama_model.py:223-229)."""
+        from ..ops.linear_op import multi_linear
+        no_bias = biases is None or all(b is None for b in biases)
+        if no_bias and x_local.dim() == 2 and all(w.dtype == torch.bfloat16 for w in weights) \
+                and self._fused_ok(x_local, weights[0], x_local.shape[0]):
+            return _FusedGatherLinear.apply(x_local, self, *weights)
+        return multi_linear(self.gather_sequence(x_local), weights, biases)
 
     def gather_sequence(self, x: torch.Tensor) -> torch.Tensor:
         return _GatherSeq.apply(x, self.axis)
@@ -223,6 +357,9 @@ class TensorParallelContext:
     def row_linear(self, x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None,
                    residual: torch.Tensor | None) -> torch.Tensor:
         """``x [T, in/tp] @ W_local^T`` -> partial sums -> reduce-scatter over tokens -> ``[T/tp, out]``."""
+        if bias is None and x.dim() == 2 and x.shape[0] % self.size == 0 \
+                and self._fused_ok(x, weight, x.shape[0] // self.size):
+            return _FusedLinearReduceScatter.apply(x, weight, residual, self)
         partial = linear(x, weight)
         out = _ReduceScatterSeq.apply(partial, self.axis)
         if bias is not None:

@@ -91,3 +91,73 @@ def test_nvlink_engine_matches_nccl_engine():
             assert abs(a - b) <= 2e-2 * max(1.0, abs(a)), (a, b)
     # every rank ends with the same parameters
     assert all(abs(a - b) < 1e-6 * max(1.0, abs(a)) for a, b in zip(got[0][2], got[1][2]))
+
+
+def _tp_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
+    try:
+        os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
+                          MASTER_PORT=str(port), LLMT_COMM=comm_kind)
+        import torch.distributed as dist
+        torch.cuda.set_device(rank)
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+        from llm_training_b200.models import Phi3, Phi3Config
+        from llm_training_b200.ops import shift_labels
+        from llm_training_b200.parallel import init_mesh
+        from llm_training_b200.parallel.tensor_parallel import _FusedGatherLinear
+        mesh = init_mesh(1, world)
+        torch.manual_seed(0)
+        cfg = Phi3Config(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                         num_attention_heads=4, num_key_value_heads=2, pad_token_id=0)
+        with torch.device('cuda'):
+            model = Phi3(cfg).to(torch.bfloat16)
+        model.parallelize(dp_mesh=mesh.dp, tp_mesh=mesh.tp)
+        tp = model.tp_context
+        assert (tp.comm is not None) == (comm_kind == 'nvlink')
+        ids = torch.randint(0, 1024, (2, 256), generator=torch.Generator().manual_seed(5)).cuda()
+        out = model(input_ids=ids, skip_logits=True)
+        loss = tp.vocab_parallel_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                               shift_labels(ids).flatten())
+        loss.backward()
+        grads = [float(p.grad.float().abs().sum()) for p in model.parameters()]
+        extra = None
+        if comm_kind == 'nvlink':       # the fused all-gather -> GEMM kernel against NCCL all-gather + GEMM
+            x = torch.randn(256, 256, device='cuda', generator=torch.Generator('cuda').manual_seed(rank)).bfloat16()
+            w = (torch.randn(384, 256, device='cuda', generator=torch.Generator('cuda').manual_seed(7)) * 0.05).bfloat16()
+            y = _FusedGatherLinear.apply(x, tp, w)
+            full = torch.empty(256 * world, 256, dtype=x.dtype, device='cuda')
+            dist.all_gather_into_tensor(full, x)
+            extra = float((y.float() - full.float() @ w.float().t()).abs().max())
+        torch.cuda.synchronize()
+        queue.put((rank, 'ok', (float(loss), grads, extra)))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        queue.put((rank, 'error', traceback.format_exc()))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
+def test_fused_tensor_parallel_kernels_match_nccl_path():
+    import torch.multiprocessing as mp
+
+    def run(kind):
+        ctx = mp.get_context('spawn')
+        queue = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_tp_worker, args=(r, 2, port, kind, queue)) for r in range(2)]
+        for p in procs:
+            p.start()
+        out = {}
+        for _ in range(2):
+            rank, status, payload = queue.get(timeout=240)
+            assert status == 'ok', f'rank {rank} ({kind}):\n{payload}'
+            out[rank] = payload
+        for p in procs:
+            p.join(timeout=60)
+        return out
+
+    ref, got = run('torch'), run('nvlink')
+    for rank in (0, 1):
+        assert abs(ref[rank][0] - got[rank][0]) < 2e-2, (ref[rank][0], got[rank][0])
+        for a, b in zip(ref[rank][1], got[rank][1]):
+            assert abs(a - b) <= 5e-2 * max(1e-3, abs(a)), (a, b)
+        assert got[rank][2] is not None and got[rank][2] < 5e-2
