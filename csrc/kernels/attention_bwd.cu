@@ -45,8 +45,8 @@ struct BwdCfg {
   static constexpr int kDSOff = kPOff + kPBytes;
   static constexpr int kDQOff = kDSOff + kPBytes;           // fp32 [64 q][128 d] staging for the TMA reduce-add
   static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB
-  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 2 x {L[64], delta[64], seg_start[64]}
-  static constexpr int kMetaBytes = 2 * 3 * 64 * 4;
+  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 3 x {L[64], delta[64], seg_start[64]}
+  static constexpr int kMetaBytes = 3 * 3 * 64 * 4;      // 3-deep ring
   static constexpr int kBarOff = kMetaOff + kMetaBytes;
   // kv_full, qdo_full[2], qdo_empty[2], st_full, st_empty, pds_full, pds_empty, dq_full, dq_empty, acc_done
   static constexpr int kNumBars = 12;
@@ -274,27 +274,35 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
     uint8_t* p_row = smem + C::kPOff + r * 128;
     uint8_t* ds_row = smem + C::kDSOff + r * 128;
 
-    for (int it = 0; it < n_total; ++it) {
+    // Per-step metadata {L[64], delta[64], seg_start[64]} lives in a 3-deep smem ring: step it+2 is fetched
+    // from global memory while step it is processed, so the loads never sit on the critical path.
+    auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 192; };
+    float pre0 = 0.f, pre1 = 0.f;                       // prefetched values (r < 64: L, delta; r >= 64: seg_start)
+    auto meta_fetch = [&](int it) {
       const int h = g * G + it / nq;
-      const int q0 = (i_lo + it % nq) * kBwdQ;
-      float* mL = reinterpret_cast<float*>(smem + C::kMetaOff) + (it & 1) * 192;
-      float* mD = mL + 64;
-      int* mS = reinterpret_cast<int*>(mL + 128);
+      const int q = (i_lo + it % nq) * kBwdQ + (r & 63);
+      const bool ok = q < p.tokens;
       if (r < 64) {
-        const int q = q0 + r;
-        const bool ok = q < p.tokens;
-        mL[r] = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
-        mD[r] = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
+        pre0 = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
+        pre1 = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
       } else {
-        const int q = q0 + r - 64;
-        mS[r - 64] = q < p.tokens ? p.seg_start[q] : 0x7fffffff;
+        pre0 = __int_as_float(ok ? p.seg_start[q] : 0x7fffffff);
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+    };
+    auto meta_store = [&](int it) {
+      float* m = meta(it);
+      if (r < 64) { m[r] = pre0; m[64 + r] = pre1; }
+      else        { m[128 + (r - 64)] = pre0; }
+    };
+    // P^T of step `it` from S^T in TMEM -> registers (fp32 bit patterns in sv)
+    uint32_t sv[64];
+    auto compute_p = [&](int it) {
+      const int q0 = (i_lo + it % nq) * kBwdQ;
+      const float* mL = meta(it);
+      const int* mS = reinterpret_cast<const int*>(mL + 128);
       const bool need_mask = (q0 < k0 + kBwdKV - 1) || (mS[63] > k0) || (p.window > 0);
-
       mbar_wait(st_full, it & 1);
       tc_fence_after();
-      uint32_t sv[64];
       {
         uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[0]);
         uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[32]);
@@ -302,7 +310,6 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
         tmem_ld_32x32b_x32(t_lane + C::kColST + 32, b);
       }
       tmem_ld_wait();
-      // P^T (fp32, kept in sv)
 #pragma unroll
       for (int c = 0; c < 64; ++c) {
         float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c]));
@@ -313,7 +320,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
         }
         sv[c] = __float_as_uint(pv);
       }
-      mbar_wait(pds_empty, (it & 1) ^ 1);       // dV/dK/dQ MMAs of the previous step have read P^T / dS^T
+    };
+
+    // prologue: metadata of steps 0 and 1, then P^T(0)
+    meta_fetch(0);
+    meta_store(0);
+    if (n_total > 1) { meta_fetch(1); meta_store(1); }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    compute_p(0);
+
+    for (int it = 0; it < n_total; ++it) {
+      const int h = g * G + it / nq;
+      const int q0 = (i_lo + it % nq) * kBwdQ;
+      const float* mD = meta(it) + 64;
+      if (it + 2 < n_total) meta_fetch(it + 2);           // global loads in flight during this whole step
+
+      // ---- P^T(it) (registers) -> smem, dS^T(it) from dP^T -> smem
+      mbar_wait(pds_empty, (it & 1) ^ 1);                 // dV/dK/dQ MMAs of the previous step have read the tiles
 #pragma unroll
       for (int ch = 0; ch < 8; ++ch) {
         float f[8];
@@ -328,7 +351,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
         tmem_ld_wait();
         if (half == 1) {
           tc_fence_before();
-          mbar_arrive(st_empty);                // S^T and dP^T are fully in registers
+          mbar_arrive(st_empty);                          // S^T and dP^T of this step are fully in registers
         }
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
@@ -344,28 +367,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       fence_proxy_async_smem();
       mbar_arrive(pds_full);
 
+      // ---- overlap: while the tensor cores run S^T/dP^T(it+1) and dV/dK/dQ^T(it), build P^T(it+1)
+      if (it + 1 < n_total) compute_p(it + 1);
+
+      // ---- dQ^T(it): TMEM [lane = d][col = q] -> smem [q][d] fp32 -> one TMA reduce-add into dq_acc
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
+      uint32_t dq[64];
       {
-        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[0]);
-        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[32]);
+        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&dq[0]);
+        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&dq[32]);
         tmem_ld_32x32b_x32(t_lane + C::kColDQT, a);
         tmem_ld_32x32b_x32(t_lane + C::kColDQT + 32, b);
       }
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(dq_empty);
-      // dQ^T tile [lane = d][col = q] -> smem [q][d] fp32 (lanes are consecutive d: conflict-free), then ONE
-      // TMA reduce-add of the 64 x 128 tile into dq_acc (replaces 8192 scalar atomics per step)
       if (threadIdx.x == 0) tma_store_wait_read<0>();     // previous reduce has finished reading the staging tile
       asm volatile("bar.sync 2, 128;" ::: "memory");
       {
         float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
 #pragma unroll
-        for (int c = 0; c < 64; ++c) stage[c * kBwdD + r] = __uint_as_float(sv[c]);
+        for (int c = 0; c < 64; ++c) stage[c * kBwdD + r] = __uint_as_float(dq[c]);
       }
+      if (it + 2 < n_total) meta_store(it + 2);           // ring slot (it+2)%3 == (it-1)%3 is no longer read
       fence_proxy_async_smem();
-      asm volatile("bar.sync 2, 128;" ::: "memory");
+      asm volatile("bar.sync 2, 128;" ::: "memory");      // also publishes the metadata stored above
       if (threadIdx.x == 0) {
         tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, h * p.head_dim, q0);
         tma_store_commit();

@@ -75,7 +75,7 @@ def cross_entropy(logits: torch.Tensor, labels: torch.Tensor, ignore_index: int 
 # ---------------------------------------------------------------------------------------------------
 # fused linear + CE / log-prob
 # ---------------------------------------------------------------------------------------------------
-_CHUNK_ROWS = 4096
+_CHUNK_ROWS = 8192      # 8192 x 128256 bf16 logits = 2.1 GB; one chunk for the usual 8k-token micro-batch
 
 
 def _chunked_logits_pass(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int,
@@ -93,7 +93,12 @@ def _chunked_logits_pass(hidden: torch.Tensor, weight: torch.Tensor, labels: tor
     vpad = (vocab + 7) // 8 * 8
     buf = torch.empty((chunk, vpad), dtype=torch.bfloat16, device=dev)
     dh = torch.empty_like(hidden) if need_grads else None
-    dw = torch.zeros((vocab, dim), dtype=torch.float32, device=dev) if need_grads else None
+    single = rows <= chunk
+    # several chunks accumulate dW in fp32; a single chunk writes the bf16 gradient directly
+    dw = None
+    if need_grads:
+        dw = torch.empty((vocab, dim), dtype=weight.dtype, device=dev) if single \
+            else torch.zeros((vocab, dim), dtype=torch.float32, device=dev)
     for r0 in range(0, rows, chunk):
         r1 = min(rows, r0 + chunk)
         n = r1 - r0
@@ -109,8 +114,8 @@ def _chunked_logits_pass(hidden: torch.Tensor, weight: torch.Tensor, labels: tor
                                              _lib.c_int(n), _lib.c_int(vocab), _lib.c_i64(vpad),
                                              _lib.c_i64(ignore_index), _lib.c_f32(0.0), _lib.stream()), 'ce_bwd')
             gemm(logits, weight, b_mn_major=True, out=dh[r0:r1])                      # dH = dlogits @ W
-            gemm(logits, hidden[r0:r1], a_mn_major=True, b_mn_major=True, out=dw,     # dW += dlogits^T @ H
-                 residual=dw)
+            gemm(logits, hidden[r0:r1], a_mn_major=True, b_mn_major=True, out=dw,     # dW (+)= dlogits^T @ H
+                 residual=None if single else dw)
     return lse, tgt, dh, dw
 
 
@@ -136,7 +141,7 @@ class _FusedLinearCEFn(torch.autograd.Function):
     def backward(ctx, grad_out: torch.Tensor):
         dh, dw = ctx.saved_tensors
         g = grad_out.float()
-        return (dh * g.to(dh.dtype)), (dw * g).to(ctx.weight_dtype), None, None
+        return (dh * g.to(dh.dtype)), (dw * g.to(dw.dtype)).to(ctx.weight_dtype), None, None
 
 
 def fused_linear_cross_entropy(hidden_states: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
