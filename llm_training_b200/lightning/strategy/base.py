@@ -153,6 +153,9 @@ class Strategy:
         # anything still on CPU / wrong dtype (metrics, user-built submodules)
         self._materialize(module)
         self.engines = self._build_engines(module)
+        if getattr(module, 'weights_used_once_per_step', False):
+            for e in self.engines:
+                e.enable_direct_grad_accumulation(True)
         trainer.optimizers, trainer.lr_scheduler_configs = self._setup_optimizers(trainer, module)
 
     def _materialize(self, module: nn.Module) -> None:

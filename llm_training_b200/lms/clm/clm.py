@@ -25,6 +25,8 @@ logger = logging.getLogger(__name__)
 
 class CLM(BaseLightningModule):
     config: CLMConfig
+    # one forward/backward per weight per step: wgrad GEMMs may accumulate directly into the flat grad buffers
+    weights_used_once_per_step = True
 
     def __init__(self, config: CLMConfig) -> None:
         super().__init__(config)

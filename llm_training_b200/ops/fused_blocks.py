@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from .gemm_op import gemm
-from .linear_op import _adjacent_rows_view, _as_2d, linear, multi_linear
+from .linear_op import _adjacent_rows_view, _as_2d, linear, multi_linear, wgrad
 from .rms_norm_op import rms_norm, rmsnorm_bwd_raw, rmsnorm_fwd_raw
 from .swiglu_op import silu_mul_bwd_raw, silu_mul_fused, silu_mul_fwd_raw
 
@@ -35,6 +35,7 @@ class _NormMultiLinearFn(torch.autograd.Function):
         ctx.eps = eps
         ctx.x_shape = x.shape
         ctx.splits = [w.shape[0] for w in weights]
+        ctx.weights = weights
         ctx.norm_dtype = norm_weight.dtype
         return y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])
 
@@ -45,7 +46,7 @@ class _NormMultiLinearFn(torch.autograd.Function):
         xn, _ = rmsnorm_fwd_raw(x2, nw, ctx.eps, want_rstd=False)          # recompute (bandwidth-bound, cheap)
         dws: list = [None] * len(ctx.splits)
         if any(ctx.needs_input_grad[3:]):
-            dws = list(gemm(dy2, xn, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0))
+            dws = wgrad(dy2, xn, ctx.weights)
         del xn
         dxn = gemm(dy2, fused, b_mn_major=True)
         dx, dnw = rmsnorm_bwd_raw(dxn, x2, nw, rstd)
@@ -72,6 +73,7 @@ class _SwiGLUDownFn(torch.autograd.Function):
         r2 = _as_2d(residual) if residual is not None else None
         y = gemm(act, w, residual=r2)
         ctx.save_for_backward(gu, w)
+        ctx.weights = (w_down,)
         ctx.shape = gate_up.shape
         ctx.has_residual = residual is not None
         return y if gate_up.dim() == 2 else y.view(*gate_up.shape[:-1], w.shape[0])
@@ -83,7 +85,7 @@ class _SwiGLUDownFn(torch.autograd.Function):
         dw = None
         if ctx.needs_input_grad[1]:
             act = silu_mul_fwd_raw(gu)                                       # recompute
-            dw = gemm(dy2, act, a_mn_major=True, b_mn_major=True)
+            dw = wgrad(dy2, act, ctx.weights)[0]
             del act
         dact = gemm(dy2, w, b_mn_major=True)
         dgu = silu_mul_bwd_raw(dact, gu)

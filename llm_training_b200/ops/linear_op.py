@@ -19,6 +19,24 @@ def _as_2d(t: torch.Tensor) -> torch.Tensor:
     return t2
 
 
+def wgrad(dy2: torch.Tensor, x2: torch.Tensor, weights: tuple[torch.Tensor, ...]) -> list:
+    """dW_i = dY_i^T X for row-stacked weights.  When the sharding engine has given every weight a gradient view
+    inside its flat buffer and marked it ``_llmt_direct_grad`` (weights used once per step), the GEMM epilogue
+    accumulates straight into that buffer (C += A^T B) and the engine is notified — no temporary dW, no
+    AccumulateGrad pass.  Otherwise returns the gradients for autograd to accumulate."""
+    direct = all(getattr(w, '_llmt_direct_grad', False) and w.grad is not None and w.grad.dtype == dy2.dtype
+                 for w in weights)
+    if direct:
+        target = weights[0].grad if len(weights) == 1 else _adjacent_rows_view(tuple(w.grad for w in weights))
+        if target is not None and target.is_contiguous():
+            gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=target, residual=target)
+            for w in weights:
+                w._llmt_grad_ready(w)
+            return [None] * len(weights)
+    dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
+    return [dw] if len(weights) == 1 else list(dw.split([w.shape[0] for w in weights], dim=0))
+
+
 class _LinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor | None) -> torch.Tensor:
@@ -29,6 +47,7 @@ class _LinearFn(torch.autograd.Function):
         ctx.save_for_backward(x2, w)
         ctx.x_shape = x.shape
         ctx.has_residual = residual is not None
+        ctx.weights = (weight,)
         return y if x.dim() == 2 else y.view(*x.shape[:-1], weight.shape[0])
 
     @staticmethod
@@ -39,7 +58,7 @@ class _LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, w, b_mn_major=True).view(ctx.x_shape)        # [T,out] @ [out,in]
         if ctx.needs_input_grad[1]:
-            dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)        # [T,out]^T @ [T,in]
+            dw = wgrad(dy2, x2, ctx.weights)[0]                         # [T,out]^T @ [T,in]
         dres = dy if ctx.has_residual else None
         return dx, dw, dres
 
@@ -85,6 +104,7 @@ class _MultiLinearFn(torch.autograd.Function):
         ctx.save_for_backward(x2, fused)
         ctx.x_shape = x.shape
         ctx.splits = [w.shape[0] for w in weights]
+        ctx.weights = weights
         # no view for the (usual) 2-D packed case: RoPE rotates this tensor in place
         return y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])
 
@@ -95,8 +115,7 @@ class _MultiLinearFn(torch.autograd.Function):
         dx = gemm(dy2, fused, b_mn_major=True).view(ctx.x_shape) if ctx.needs_input_grad[0] else None
         dws: list = [None] * len(ctx.splits)
         if any(ctx.needs_input_grad[1:]):
-            dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)
-            dws = list(dw.split(ctx.splits, dim=0))
+            dws = wgrad(dy2, x2, ctx.weights)
         return (dx, *dws)
 
 

@@ -186,6 +186,16 @@ class FlatParamEngine:
         else:
             self.comm.reduce_scatter_into(u.grad_shard, u.flat_grad, average=True)
 
+    def enable_direct_grad_accumulation(self, flag: bool = True) -> None:
+        """Let the wgrad GEMMs accumulate straight into the flat gradient buffer (``ops.linear_op.wgrad``).  Only
+        valid when every weight is used ONCE per backward pass (the engine counts one notification per
+        parameter to know when a unit's gradients are complete) — CLM turns it on, DPO / ORPO do not."""
+        for u in self.units:
+            for _, p in u.params:
+                if p.requires_grad and p.dim() == 2:
+                    p._llmt_direct_grad = flag
+                    p._llmt_grad_ready = self._on_grad_ready
+
     def set_requires_gradient_sync(self, flag: bool) -> None:
         """False on non-boundary micro-batches of gradient accumulation (reference:
         ``block_backward_sync``, fsdp2_strategy.py:430-442): grads keep accumulating locally."""

@@ -327,3 +327,30 @@ def test_llama_gpu_matches_cpu_fp32():
         g, r = pg.grad.float().cpu(), pc.grad
         err, scale = (g - r).abs().max().item(), r.abs().max().item()
         assert err <= 0.08 * scale + 2e-3, f'{n}: grad err {err} vs scale {scale}'
+
+
+def test_direct_wgrad_accumulation_matches_autograd_path():
+    """wgrad GEMMs accumulating straight into the flat gradient buffer == autograd's AccumulateGrad path,
+    including accumulation over two micro-batches."""
+    import copy
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    from llm_training_b200.parallel import apply_fully_sharded
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2)
+    with torch.device(DEV):
+        a = Llama(cfg).to(torch.bfloat16)
+    b = copy.deepcopy(a)
+    ea = apply_fully_sharded(a, None, device=torch.device(DEV))
+    eb = apply_fully_sharded(b, None, device=torch.device(DEV))
+    ea.enable_direct_grad_accumulation(True)
+    for model in (a, b):
+        for micro in range(2):
+            ids = torch.randint(0, 512, (2, 192), generator=torch.Generator().manual_seed(micro)).to(DEV)
+            out = model(input_ids=ids, skip_logits=True)
+            fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                       shift_labels(ids).flatten()).backward()
+    assert all(u.pending_grads <= 0 for u in ea.units)          # every parameter reported in
+    for ua, ub in zip(ea.units, eb.units):
+        _close(ua.flat_grad, ub.flat_grad, rtol=2e-2, atol=2e-3)
