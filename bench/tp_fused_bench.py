@@ -33,7 +33,7 @@ def main():
     os.environ['LLMT_COMM'] = 'nvlink'
     from llm_training_b200.ops.gemm_op import gemm
     from llm_training_b200.parallel import init_mesh
-    from llm_training_b200.parallel.tensor_parallel import (TensorParallelContext, _FusedGatherLinear,
+    from llm_training_b200.parallel.tensor_parallel import (TensorParallelContext, _FusedGatherLinear, _gemm_dist,
                                                             _fused_linear_reduce_scatter)
     mesh = init_mesh(1, world)
     tp = TensorParallelContext(mesh.tp)
@@ -56,9 +56,19 @@ def main():
             dist.all_gather_into_tensor(full, x)
             return gemm(full, w)
 
+        def direct():       # earlier variant: A tiles TMA-loaded straight from the owner, once per N tile
+            buf, view = tp.ring.next(T // world, d)
+            view.copy_(x)
+            tp.comm.barrier()
+            out = torch.empty((T, n_local), dtype=x.dtype, device='cuda')
+            _gemm_dist(1, None, buf.peer_ptrs_at(0), w, out, None, world, T // world, T, n_local, d, d, n_local, False)
+            return out
+
         with torch.no_grad():
             fused = timeit(lambda: _FusedGatherLinear.apply(x, tp, w))
             base = timeit(nccl)
+            direct_ms = timeit(direct)
+            gemm_only = timeit(lambda: gemm(full, w))
             err = float((_FusedGatherLinear.apply(x, tp, w).float() - nccl().float()).abs().max())
         flops = 2.0 * T * n_local * d
         n_tiles = (n_local + 255) // 256
@@ -66,7 +76,8 @@ def main():
         roof = max(flops / peak, bytes_min / link)
         results.append(dict(op=f'AG->GEMM {name}', shape=[T, n_local, d], fused_ms=fused, nccl_plus_gemm_ms=base,
                             roofline_ms=roof * 1e3, frac_of_roofline=roof * 1e3 / fused, max_abs_diff=err,
-                            nvlink_reread_factor=n_tiles))
+                            direct_from_peer_ms=direct_ms, local_gemm_only_ms=gemm_only,
+                            direct_nvlink_reread_factor=n_tiles))
     for name, k_local in (('o_proj', d // world), ('down', ffn // world)):
         x = (torch.randn(T, k_local, device='cuda', generator=g) * 0.5).bfloat16()
         w = (torch.randn(d, k_local, device='cuda', generator=g) * 0.05).bfloat16()

@@ -58,17 +58,31 @@ struct Params {
   int M, N, K;
   int has_residual;
   int rows_per_rank;   // dist variants: rows of the gathered A / scattered C owned by one rank
+  int tm_rot;          // land-once gather: first m-block of the tile walk (this rank's own rows)
 };
 
 // Fused collective variants (tensor parallel paths):
-//   kDistA : A is the row-wise concatenation of every rank's [rows_per_rank, K] block living in symmetric memory;
-//            the TMA producer loads each A tile straight from its owner over NVLink (all-gather -> GEMM)
+//   kDistA : A is the row-wise concatenation of every rank's [rows_per_rank, K] block living in symmetric memory
+//            (all-gather -> GEMM).
+//            1: the TMA producer loads each A tile straight from its owner over NVLink; simple, but a remote row
+//               panel crosses NVLink once per N tile.
+//            2: "land once": eight extra warps per CTA pull the remote blocks over NVLink into a local [M, K]
+//               buffer, block by block in the order the tile schedule consumes them (own rows first, then rank+1,
+//               rank+2, ...), and bump a per-block arrival counter; the TMA producer waits on the counter of a
+//               remote block before its first load.  Every byte crosses NVLink once, the copy hides under the
+//               MMAs of the earlier blocks, and the gathered activation is left behind for the backward pass.
 //   kDistC : the [M, N] result is reduce-scattered by rows; each tile is TMA-reduce-ADDED into the owner rank's
 //            [rows_per_rank, N] buffer (GEMM -> reduce-scatter)
 constexpr int kMaxDistRanks = 8;
 struct DistMaps {
   CUtensorMap a[kMaxDistRanks];
   CUtensorMap c[kMaxDistRanks];
+  // land-once all-gather (kDistA == 2): raw views for the pull warps + arrival counters
+  const void* a_raw[kMaxDistRanks];   // rank r's [rows_per_rank, K] block (symmetric memory), lda elements per row
+  void* a_full;                       // local [M, K] landing buffer, ld_full elements per row
+  int* flags;                         // one counter per (BM * kCtaGroup)-row block of a_full, zero on entry
+  int64_t lda, ld_full;
+  int rank, world;
 };
 struct NoDist {};
 
@@ -85,12 +99,12 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
   tn = r / group_m;
 }
 
-template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, bool kDistA = false, bool kDistC = false>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, int kDistA = 0, bool kDistC = false>
+__global__ void __launch_bounds__((kDistA == 2 ? 2 : 1) * kThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, Params p,
-                 const __grid_constant__ typename std::conditional<(kDistA || kDistC), DistMaps, NoDist>::type dist) {
-  static_assert(!(kDistA && kAMn), "gathered A must be K-major");
+                 const __grid_constant__ typename std::conditional<(kDistA != 0 || kDistC), DistMaps, NoDist>::type dist) {
+  static_assert(!(kDistA != 0 && kAMn), "gathered A must be K-major");
   using C = Cfg<kCtaGroup>;
   constexpr int kOutChunkCols = 128 / (int)sizeof(OutT);  // columns per 128-byte staging row: 64 bf16 / 32 fp32
   constexpr int kNumChunks = BN / kOutChunkCols;
@@ -119,6 +133,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int num_k = (p.K + BK - 1) / BK;
   const int worker = blockIdx.x / kCtaGroup;
   const int num_workers = gridDim.x / kCtaGroup;
+  // land-once gather: walk the m-blocks starting at this rank's own rows (the order the pull warps fill them)
+  auto tile_mn = [&](int tile, int& tm, int& tn) {
+    tile_coords(tile, num_m, num_n, tm, tn);
+    if constexpr (kDistA == 2) {
+      tm += p.tm_rot;
+      if (tm >= num_m) tm -= num_m;
+    }
+  };
 
   // ---------------------------------------------------------------- one-time setup
   if (warp == 0 && lane == 0) {
@@ -158,9 +180,27 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       for (int tile = worker; tile < num_tiles; tile += num_workers) {
         int tm, tn;
-        tile_coords(tile, num_m, num_n, tm, tn);
+        tile_mn(tile, tm, tn);
         const int m0 = (tm * kCtaGroup + (int)cta_rank) * BM;
         const int n0 = tn * BN + (int)cta_rank * C::kBRows;
+        [[maybe_unused]] const CUtensorMap* mapA = &tmA;
+        [[maybe_unused]] int m_local = m0;
+        if constexpr (kDistA != 0) {                   // A tile lives on rank m0 / rows_per_rank
+          const int owner = min(m0 / p.rows_per_rank, kMaxDistRanks - 1);
+          if (kDistA == 1 || owner == dist.rank) {
+            mapA = &dist.a[owner];
+            m_local = m0 - owner * p.rows_per_rank;
+          } else {
+            // remote rows come from the landing buffer once the pull warps of every CTA have delivered the block
+            const int* flag = dist.flags + tm;
+            const int target = (int)gridDim.x;
+            uint32_t spins = 0;
+            while (ld_acquire_gpu_s32(flag) < target) {
+              if (++spins > (1u << 26)) __trap();
+            }
+            fence_proxy_async_all();                   // generic-proxy writes (pull warps) -> async-proxy reads (TMA)
+          }
+        }
         for (int kb = 0; kb < num_k; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t sa = smem_base + stage * C::kStageBytes;
@@ -168,15 +208,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const uint32_t fb = full0 + 8u * stage;
           const int k0 = kb * BK;
           if (kCtaGroup == 1 || is_leader) mbar_arrive_expect_tx(full_bar(stage), C::kStageBytes * kCtaGroup);
-          [[maybe_unused]] const CUtensorMap* mapA = &tmA;
-          [[maybe_unused]] int m_local = m0;
-          if constexpr (kDistA) {                      // A tile lives on rank m0 / rows_per_rank
-            const int owner = min(m0 / p.rows_per_rank, kMaxDistRanks - 1);
-            mapA = &dist.a[owner];
-            m_local = m0 - owner * p.rows_per_rank;
-          }
           if constexpr (kCtaGroup == 1) {
-            if constexpr (kDistA) tma_load_2d(sa, mapA, fb, k0, m_local);
+            if constexpr (kDistA != 0) tma_load_2d(sa, mapA, fb, k0, m_local);
             else if constexpr (!kAMn) tma_load_2d(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
@@ -188,7 +221,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int j = 0; j < C::kBRows / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tmB, fb, n0 + j * 64, k0);
             }
           } else {
-            if constexpr (kDistA) tma_load_2d_cg2(sa, mapA, fb, k0, m_local);
+            if constexpr (kDistA != 0) tma_load_2d_cg2(sa, mapA, fb, k0, m_local);
             else if constexpr (!kAMn) tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
@@ -241,7 +274,53 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
       }
     }
-  } else if (warp >= kEpiWarp0) {
+  } else if (kDistA == 2 && warp >= kThreads / 32) {
+    // ===== pull warps (land-once gather): remote blocks -> local landing buffer, one arrival per CTA and block =====
+    if constexpr (kDistA == 2) {
+      constexpr int kPullThreads = kThreads;
+      const int pt = (int)threadIdx.x - kThreads;
+      const int64_t g = (int64_t)blockIdx.x * kPullThreads + pt, G = (int64_t)gridDim.x * kPullThreads;
+      constexpr int kBlkRows = BM * kCtaGroup;
+      const int bpr = p.rows_per_rank / kBlkRows;
+      const int vec_per_row = p.K >> 3;
+      const int64_t vecs = (int64_t)kBlkRows * vec_per_row;
+      for (int s = 1; s <= dist.world; ++s) {          // s == world is this rank's own block: copied last, unflagged
+        const int owner = (dist.rank + s) % dist.world;
+#pragma unroll 1
+        for (int b = 0; b < bpr; ++b) {
+          const __nv_bfloat16* src =
+              reinterpret_cast<const __nv_bfloat16*>(dist.a_raw[owner]) + (int64_t)b * kBlkRows * dist.lda;
+          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dist.a_full) +
+                               ((int64_t)owner * p.rows_per_rank + (int64_t)b * kBlkRows) * dist.ld_full;
+          for (int64_t v0 = g; v0 < vecs; v0 += 4 * G) {
+            uint4 r[4];
+            int64_t off[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int64_t v = v0 + u * G;
+              off[u] = -1;
+              if (v < vecs) {
+                const int64_t row = v / vec_per_row;
+                const int64_t col = (v - row * vec_per_row) << 3;
+                off[u] = row * dist.ld_full + col;
+                r[u] = ld_relaxed_sys_16(src + row * dist.lda + col);
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (off[u] >= 0) *reinterpret_cast<uint4*>(dst + off[u]) = r[u];
+          }
+          if (owner != dist.rank) {
+            asm volatile("bar.sync 3, 256;" ::: "memory");
+            if (pt == 0) {
+              __threadfence();
+              red_release_gpu_add_s32(dist.flags + owner * bpr + b, 1);
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= kEpiWarp0 && warp < kEpiWarp0 + 4) {
     // ===== epilogue: TMEM -> registers -> (+R) -> swizzled smem -> TMA store =====
     const int ew = warp - kEpiWarp0;       // == warp % 4 -> TMEM lanes [32*ew, 32*ew+32)
     const int row = ew * 32 + lane;        // row of the 128-row CTA tile owned by this thread
@@ -255,7 +334,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int chunk_counter = 0;
     for (int tile = worker; tile < num_tiles; tile += num_workers) {
       int tm, tn;
-      tile_coords(tile, num_m, num_n, tm, tn);
+      tile_mn(tile, tm, tn);
       const int m0 = (tm * kCtaGroup + (int)cta_rank) * BM;
       const int n0 = tn * BN;
       mbar_wait_cluster(tmem_full_bar(acc), acc_phase);
@@ -391,7 +470,7 @@ int make_tmap_2d(CUtensorMap* out, const void* ptr, int elem_bytes, int64_t rows
   return 0;
 }
 
-template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, bool kDistA = false, bool kDistC = false>
+template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, int kDistA = 0, bool kDistC = false>
 int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, const CUtensorMap& r, Params p,
            int max_ctas, cudaStream_t stream, const DistMaps* dist_maps = nullptr) {
   using C = Cfg<kCtaGroup>;
@@ -412,7 +491,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
   if (workers > cap) workers = cap;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(workers * kCtaGroup);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3((kDistA == 2 ? 2 : 1) * kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -423,7 +502,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e;
-  if constexpr (kDistA || kDistC) e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, *dist_maps);
+  if constexpr (kDistA != 0 || kDistC) e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, *dist_maps);
   else e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, NoDist{});
   if (e != cudaSuccess) {
     set_error("gemm launch: %s", cudaGetErrorString(e));
@@ -475,7 +554,7 @@ extern "C" int llmt_gemm_bf16(const void* A, const void* B, void* Cout, const vo
   } else {
     tr = tc;
   }
-  Params p{M, N, K, R ? 1 : 0, 0};
+  Params p{M, N, K, R ? 1 : 0, 0, 0};
 
 #define LLMT_GEMM_DISPATCH(CG, AMN, BMN)                                                        \
   return out_fp32 ? launch<CG, AMN, BMN, float>(ta, tb, tc, tr, p, max_ctas, stream)            \
@@ -521,7 +600,7 @@ extern "C" int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a
   if (!b_mn_major) rc = make_tmap_2d(&tb, B, 2, N, K, ldb, BK, b_rows);   // B stored [N, K]
   else             rc = make_tmap_2d(&tb, B, 2, K, N, ldb, 64, BK);       // B stored [K, N]
   if (rc) return rc;
-  Params p{M, N, K, 0, rows_per_rank};
+  Params p{M, N, K, 0, rows_per_rank, 0};
   if (mode == 1) {
     for (int r = 0; r < kMaxDistRanks; ++r) {
       const void* src = a_ptrs[r < world ? r : world - 1];
@@ -533,11 +612,11 @@ extern "C" int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a
     if (rc) return rc;
     ta = maps.a[0];
     if (b_mn_major) {
-      if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
-      return launch<2, false, true, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+      if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, 1, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+      return launch<2, false, true, __nv_bfloat16, 1, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
     }
-    if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
-    return launch<2, false, false, __nv_bfloat16, true, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, 1, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    return launch<2, false, false, __nv_bfloat16, 1, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
   }
   rc = make_tmap_2d(&ta, A, 2, M, K, lda, BK, BM);
   if (rc) return rc;
@@ -549,9 +628,67 @@ extern "C" int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a
   }
   tc = maps.c[0];
   if (b_mn_major) {
-    if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
-    return launch<2, false, true, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, 0, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    return launch<2, false, true, __nv_bfloat16, 0, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
   }
-  if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
-  return launch<2, false, false, __nv_bfloat16, false, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, 0, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  return launch<2, false, false, __nv_bfloat16, 0, true>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+}
+
+// All-gather -> GEMM, "land once":  C[M, N] = concat_r(A_r)[M, K] * op(B), and a_full[M, K] = concat_r(A_r).
+// a_ptrs[r] is rank r's [rows_per_rank, K] block in symmetric memory (HOST array of `world` device pointers, lda
+// elements per row).  Extra warps of the GEMM kernel copy the remote blocks over NVLink into a_full while the
+// tensor cores work on the blocks that are already local; the TMA producer waits on per-block arrival counters
+// (`flags`, int32 [M / (128 * cta_group)], zeroed here on `stream`).  A cross-rank barrier must precede the call
+// (every A_r written) and follow it before A_r is overwritten.
+extern "C" int llmt_gemm_bf16_ag(const void* const* a_ptrs, void* a_full, const void* B, void* Cout, int* flags,
+                                 int rank, int world, int rows_per_rank, int M, int N, int K, int64_t lda,
+                                 int64_t ld_full, int64_t ldb, int64_t ldc, int b_mn_major, int cta_group,
+                                 int max_ctas, cudaStream_t stream) {
+  LLMT_REQUIRE(world >= 1 && world <= kMaxDistRanks && rank >= 0 && rank < world,
+               "gemm_ag: rank %d / world %d not supported (max %d ranks)", rank, world, kMaxDistRanks);
+  LLMT_REQUIRE(cta_group == 1 || cta_group == 2, "gemm_ag: cta_group must be 1 or 2");
+  const int blk = BM * cta_group;
+  LLMT_REQUIRE(rows_per_rank > 0 && rows_per_rank % blk == 0 && (int64_t)rows_per_rank * world == M,
+               "gemm_ag: rows_per_rank=%d must be a multiple of %d and rows_per_rank * world == M=%d", rows_per_rank,
+               blk, M);
+  LLMT_REQUIRE(K % 8 == 0 && lda % 8 == 0 && ld_full % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0,
+               "gemm_ag: K and the leading dimensions must be multiples of 8");
+  LLMT_REQUIRE((uintptr_t)a_full % 16 == 0 && (uintptr_t)flags % 4 == 0, "gemm_ag: misaligned buffers");
+  if (max_ctas <= 0) max_ctas = num_sms();
+  if (max_ctas > num_sms()) max_ctas = num_sms();   // every CTA must be resident: the producers wait on all pullers
+  static DistMaps maps;
+  CUtensorMap ta, tb, tc;
+  int rc;
+  const int b_rows = BN / cta_group;
+  if (!b_mn_major) rc = make_tmap_2d(&tb, B, 2, N, K, ldb, BK, b_rows);
+  else             rc = make_tmap_2d(&tb, B, 2, K, N, ldb, 64, BK);
+  if (rc) return rc;
+  for (int r = 0; r < kMaxDistRanks; ++r) {
+    const void* src = a_ptrs[r < world ? r : world - 1];
+    LLMT_REQUIRE((uintptr_t)src % 16 == 0, "gemm_ag: misaligned peer buffer");
+    rc = make_tmap_2d(&maps.a[r], src, 2, rows_per_rank, K, lda, BK, BM);
+    if (rc) return rc;
+    maps.c[r] = maps.a[r];
+    maps.a_raw[r] = src;
+  }
+  rc = make_tmap_2d(&ta, a_full, 2, M, K, ld_full, BK, BM);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tc, Cout, 2, M, N, ldc, 64, BM);
+  if (rc) return rc;
+  maps.a_full = a_full;
+  maps.flags = flags;
+  maps.lda = lda;
+  maps.ld_full = ld_full;
+  maps.rank = rank;
+  maps.world = world;
+  cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)(M / blk), stream);
+  LLMT_REQUIRE(e == cudaSuccess, "gemm_ag: flag reset failed: %s", cudaGetErrorString(e));
+  Params p{M, N, K, 0, rows_per_rank, rank * (rows_per_rank / blk)};
+  if (b_mn_major) {
+    if (cta_group == 1) return launch<1, false, true, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+    return launch<2, false, true, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  }
+  if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  return launch<2, false, false, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
 }

@@ -40,6 +40,14 @@ int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a_ptrs, cons
                         void* const* c_ptrs, int world, int rows_per_rank, int M, int N, int K, int64_t lda,
                         int64_t ldb, int64_t ldc, int b_mn_major, int cta_group, int max_ctas, cudaStream_t stream);
 
+/* All-gather -> GEMM, "land once": extra warps of the GEMM kernel copy each remote [rows_per_rank, K] block over
+ * NVLink into a_full [M, K] exactly once while the tensor cores consume the blocks already present; the TMA
+ * producer waits on per-block arrival counters (flags: int32 [M / (128 * cta_group)], reset by the call).  a_full
+ * is left holding the gathered activation for the backward pass. */
+int llmt_gemm_bf16_ag(const void* const* a_ptrs, void* a_full, const void* B, void* C, int* flags, int rank,
+                      int world, int rows_per_rank, int M, int N, int K, int64_t lda, int64_t ld_full, int64_t ldb,
+                      int64_t ldc, int b_mn_major, int cta_group, int max_ctas, cudaStream_t stream);
+
 /* ---- NVLink collectives for the sharding engine (csrc/kernels/comm.cu); replace NCCL all-gather /
  *      reduce-scatter issued by FSDP2 / ZeRO (llama_model.py:263-268, deepspeed_strategy.py:39-44) ------------ */
 int llmt_comm_barrier(const void* const* signal_pads, int rank, int world, int slot_base, uint32_t epoch,

@@ -238,10 +238,38 @@ def _gemm_dist(mode: int, a: torch.Tensor | None, a_ptrs, b: torch.Tensor, c: to
         _lib.c_int(b_mn_major), _lib.c_int(2), _lib.c_int(0), _lib.stream()), 'gemm_bf16_dist')
 
 
+_AG_FLAGS: dict[torch.device, torch.Tensor] = {}
+
+
+def _gather_gemm(tp: 'TensorParallelContext', x_local: torch.Tensor, weight: torch.Tensor, b_mn_major: bool
+                 ) -> tuple[torch.Tensor, torch.Tensor]:
+    """``(all_gather(x_local) @ op(W), all_gather(x_local))`` in ONE kernel (csrc/kernels/gemm.cu, kDistA == 2):
+    pull warps land every remote block in ``x_full`` once while the tensor cores work on the blocks already there."""
+    rows, k = x_local.shape
+    n = weight.shape[1] if b_mn_major else weight.shape[0]
+    m = rows * tp.size
+    cta_group = 2 if rows % 256 == 0 else 1
+    buf, view = tp.ring.next(rows, k)
+    view.copy_(x_local)
+    tp.comm.barrier()                   # every rank's block is in place
+    dev = x_local.device
+    flags = _AG_FLAGS.get(dev)
+    if flags is None or flags.numel() < m // 128:
+        flags = _AG_FLAGS[dev] = torch.zeros(max(4096, m // 128), dtype=torch.int32, device=dev)
+    x_full = torch.empty((m, k), dtype=x_local.dtype, device=dev)
+    out = torch.empty((m, n), dtype=x_local.dtype, device=dev)
+    _lib.check(_lib.lib().llmt_gemm_bf16_ag(
+        buf.peer_ptrs_at(0), _lib.ptr(x_full), _lib.ptr(weight), _lib.ptr(out), _lib.ptr(flags),
+        _lib.c_int(tp.rank), _lib.c_int(tp.size), _lib.c_int(rows), _lib.c_int(m), _lib.c_int(n), _lib.c_int(k),
+        _lib.c_i64(k), _lib.c_i64(k), _lib.c_i64(weight.stride(0)), _lib.c_i64(n), _lib.c_int(b_mn_major),
+        _lib.c_int(cta_group), _lib.c_int(0), _lib.stream()), 'gemm_bf16_ag')
+    return out, x_full
+
+
 class _FusedGatherLinear(torch.autograd.Function):
-    """``all_gather(x_local) @ [W_1; W_2; ...]^T`` as ONE kernel: A tiles are TMA-loaded from the peers' symmetric
-    buffers.  Backward: dW needs the gathered input (NCCL all-gather), dx is ``dy @ W`` fused with the
-    reduce-scatter."""
+    """``all_gather(x_local) @ [W_1; W_2; ...]^T`` as ONE kernel (land-once gather inside the GEMM, see
+    ``_gather_gemm``).  The gathered input the kernel leaves behind is what dW needs in backward; dx is ``dy @ W``
+    fused with the reduce-scatter."""
 
     @staticmethod
     def forward(ctx, x_local: torch.Tensor, tp: 'TensorParallelContext', *weights: torch.Tensor) -> torch.Tensor:
@@ -249,26 +277,17 @@ class _FusedGatherLinear(torch.autograd.Function):
         weight = weights[0] if len(weights) == 1 else _adjacent_rows_view(weights)
         if weight is None:
             weight = torch.cat([w.detach() for w in weights], dim=0)
-        rows, k = x_local.shape
-        n = weight.shape[0]
-        buf, view = tp.ring.next(rows, k)
-        view.copy_(x_local)
-        tp.comm.barrier()
-        out = torch.empty((rows * tp.size, n), dtype=x_local.dtype, device=x_local.device)
-        _gemm_dist(1, None, buf.peer_ptrs_at(0), weight, out, None, tp.size, rows, rows * tp.size, n, k, k, n, False)
-        ctx.save_for_backward(x_local, weight)
+        out, x_full = _gather_gemm(tp, x_local.contiguous(), weight, b_mn_major=False)
+        ctx.save_for_backward(x_full, weight)
         ctx.tp = tp
         ctx.splits = [w.shape[0] for w in weights]
         return out
 
     @staticmethod
     def backward(ctx, dy: torch.Tensor):
-        x_local, weight = ctx.saved_tensors
+        x_full, weight = ctx.saved_tensors
         tp = ctx.tp
         dy = dy.contiguous()
-        rows, k = x_local.shape
-        x_full = torch.empty((rows * tp.size, k), dtype=x_local.dtype, device=x_local.device)
-        dist.all_gather_into_tensor(x_full, x_local.contiguous(), group=tp.axis.group)
         dws = gemm(dy, x_full, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0)
         dx = _fused_linear_reduce_scatter(tp, dy, weight, None, b_mn_major=True)   # dy @ W, reduce-scattered
         return (dx, None, *dws)
@@ -292,7 +311,8 @@ def _fused_linear_reduce_scatter(tp: 'TensorParallelContext', x: torch.Tensor, w
 
 class _FusedLinearReduceScatter(torch.autograd.Function):
     """``reduce_scatter(x @ W_local^T) (+ residual)`` as ONE kernel: each output tile is TMA-reduce-added into its
-    owner rank's buffer.  Backward: the gathered dy feeds dx (fused all-gather -> GEMM) and dW."""
+    owner rank's buffer.  Backward: dx = all_gather(dy) @ W is the land-once gather GEMM, whose gathered dy then
+    feeds dW."""
 
     @staticmethod
     def forward(ctx, x: torch.Tensor, weight: torch.Tensor, residual: torch.Tensor | None,
@@ -306,11 +326,7 @@ class _FusedLinearReduceScatter(torch.autograd.Function):
     def backward(ctx, dy_local: torch.Tensor):
         x, weight = ctx.saved_tensors
         tp = ctx.tp
-        dy_local = dy_local.contiguous()
-        rows, n = dy_local.shape
-        dy_full = torch.empty((rows * tp.size, n), dtype=dy_local.dtype, device=dy_local.device)
-        dist.all_gather_into_tensor(dy_full, dy_local, group=tp.axis.group)
-        dx = gemm(dy_full, weight, b_mn_major=True)
+        dx, dy_full = _gather_gemm(tp, dy_local.contiguous(), weight, b_mn_major=True)   # dy @ W, gathered dy kept
         dw = gemm(dy_full, x.contiguous(), a_mn_major=True, b_mn_major=True)
         return dx, dw, (dy_local if ctx.has_residual else None), None
 

@@ -127,6 +127,21 @@ def _tp_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
             full = torch.empty(256 * world, 256, dtype=x.dtype, device='cuda')
             dist.all_gather_into_tensor(full, x)
             extra = float((y.float() - full.float() @ w.float().t()).abs().max())
+            # land-once gather GEMM: several row blocks per rank, both CTA-group forms, both B layouts; the
+            # gathered operand it leaves behind must be exact
+            from llm_training_b200.parallel.tensor_parallel import _gather_gemm
+            for rows, k, n, b_mn in ((1024, 512, 768, False), (384, 256, 320, False), (512, 384, 512, True)):
+                gen = torch.Generator('cuda').manual_seed(100 + rank)
+                xl = torch.randn(rows, k, device='cuda', generator=gen).bfloat16()
+                gw = torch.Generator('cuda').manual_seed(9)
+                wl = (torch.randn((k, n) if b_mn else (n, k), device='cuda', generator=gw) * 0.05).bfloat16()
+                want_full = torch.empty(rows * world, k, dtype=xl.dtype, device='cuda')
+                dist.all_gather_into_tensor(want_full, xl)
+                for _ in range(3):      # repeated use exercises the flag reset and the buffer ring
+                    got, got_full = _gather_gemm(tp, xl, wl, b_mn)
+                want = want_full.float() @ (wl.float() if b_mn else wl.float().t())
+                assert torch.equal(got_full, want_full), 'gathered operand differs'
+                extra = max(extra, float((got.float() - want).abs().max()))
         torch.cuda.synchronize()
         queue.put((rank, 'ok', (float(loss), grads, extra)))
         dist.barrier()
