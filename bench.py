@@ -112,6 +112,7 @@ def main() -> None:
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--model', default='llama-3-8b', choices=sorted(MODELS))
     ap.add_argument('--seq-len', type=int, default=8192)
+    ap.add_argument('--layers', type=int, default=0, help='override the layer count (comparison runs only)')
     ap.add_argument('--micro-batch', type=int, default=1)
     ap.add_argument('--recompute', default='auto', choices=['auto', 'none', 'full', 'selective'])
     ap.add_argument('--tp', type=int, default=1)
@@ -143,7 +144,10 @@ def main() -> None:
         # norm+linear / swiglu+down blocks rebuild their elementwise intermediates) -> fits 180 GB without
         # layer-level checkpointing
         recompute = 'none'
-    model_cfg = dict(MODELS[args.model], enable_gradient_checkpointing=recompute != 'none',
+    base_cfg = dict(MODELS[args.model])
+    if args.layers > 0:
+        base_cfg['num_hidden_layers'] = args.layers
+    model_cfg = dict(base_cfg, enable_gradient_checkpointing=recompute != 'none',
                      recompute_granularity='selective' if recompute == 'selective' else 'full',
                      attn_implementation='flash_attention_2' if cuda else 'sdpa')
     lm = CLM(CLMConfig.model_validate(dict(
@@ -277,7 +281,7 @@ def main() -> None:
             'metric': 'tokens_per_sec', 'value': value, 'unit': 'tokens/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'bf16' if cuda else 'fp32', 'data': 'synthetic', 'impl': 'ours',
-            'config': {'model': args.model, 'global_batch': args.micro_batch * dp, 'seq_len': args.seq_len,
+            'config': {'model': args.model if args.layers <= 0 else f'{args.model}-{args.layers}layers', 'global_batch': args.micro_batch * dp, 'seq_len': args.seq_len,
                        'parallelism': f'dp{dp}' + (f'xtp{args.tp}' if args.tp > 1 else ''),
                        'sharding': 'flat-param ZeRO (optimizer+grad sharded, params resident)',
                        'optimizer': 'AdamW fp32 master, grad clip 1.0', 'recompute': recompute,
