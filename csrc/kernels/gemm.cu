@@ -80,11 +80,14 @@ struct DistMaps {
   // land-once all-gather (kDistA == 2): raw views for the pull warps + arrival counters
   const void* a_raw[kMaxDistRanks];   // rank r's [rows_per_rank, K] block (symmetric memory), lda elements per row
   void* a_full;                       // local [M, K] landing buffer, ld_full elements per row
-  int* flags;                         // one counter per (BM * kCtaGroup)-row block of a_full, zero on entry
+  int* flags;                         // one counter per (BM * kCtaGroup)-row block of a_full (counts 4 KB pieces
+                                      // delivered), zero on entry
   int64_t lda, ld_full;
   int rank, world;
 };
 struct NoDist {};
+constexpr int kPullUnroll = 8;                  // 16-byte loads in flight per lane of a pull warp
+constexpr int kPieceVecs = 32 * kPullUnroll;    // vectors per pull work unit (4 KB)
 
 // grouped rasterisation: consecutive tile ids walk down M inside a band of kGroupM m-tiles so that the
 // ~148 tiles in flight share A and B panels in L2
@@ -193,7 +196,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           } else {
             // remote rows come from the landing buffer once the pull warps of every CTA have delivered the block
             const int* flag = dist.flags + tm;
-            const int target = (int)gridDim.x;
+            const int target = (int)(((int64_t)BM * kCtaGroup * (p.K >> 3) + kPieceVecs - 1) / kPieceVecs);
             uint32_t spins = 0;
             while (ld_acquire_gpu_s32(flag) < target) {
               if (++spins > (1u << 26)) __trap();
@@ -277,45 +280,51 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (kDistA == 2 && warp >= kThreads / 32) {
     // ===== pull warps (land-once gather): remote blocks -> local landing buffer, one arrival per CTA and block =====
     if constexpr (kDistA == 2) {
-      constexpr int kPullThreads = kThreads;
-      const int pt = (int)threadIdx.x - kThreads;
-      const int64_t g = (int64_t)blockIdx.x * kPullThreads + pt, G = (int64_t)gridDim.x * kPullThreads;
+      // Work unit = one "piece": kPieceVecs consecutive 16-byte vectors of a block, moved by ONE warp with
+      // kPullUnroll loads in flight per lane.  Pieces are numbered over all remote blocks in consumption order
+      // and dealt round-robin to every pull warp of the grid, so warps never meet at a CTA barrier and the
+      // copy of block b+1 overlaps the tail of block b.  A block is complete when all of its pieces have
+      // arrived (one counter increment per piece).
+      constexpr int kPullWarps = kThreads / 32;
       constexpr int kBlkRows = BM * kCtaGroup;
+      const int pw = warp - kThreads / 32;
+      const int64_t gw = (int64_t)blockIdx.x * kPullWarps + pw, GW = (int64_t)gridDim.x * kPullWarps;
       const int bpr = p.rows_per_rank / kBlkRows;
       const int vec_per_row = p.K >> 3;
       const int64_t vecs = (int64_t)kBlkRows * vec_per_row;
-      for (int s = 1; s <= dist.world; ++s) {          // s == world is this rank's own block: copied last, unflagged
+      const int64_t ppb = (vecs + kPieceVecs - 1) / kPieceVecs;           // pieces per block
+      const int64_t remote_pieces = (int64_t)(dist.world - 1) * bpr * ppb;
+      const int64_t all_pieces = (int64_t)dist.world * bpr * ppb;         // own block last: copied, not flagged
+      for (int64_t piece = gw; piece < all_pieces; piece += GW) {
+        const int64_t blk_seq = piece / ppb;                              // position in consumption order
+        const int64_t in_blk = piece - blk_seq * ppb;
+        const int s = (int)(blk_seq / bpr) + 1, b = (int)(blk_seq % bpr);
         const int owner = (dist.rank + s) % dist.world;
-#pragma unroll 1
-        for (int b = 0; b < bpr; ++b) {
-          const __nv_bfloat16* src =
-              reinterpret_cast<const __nv_bfloat16*>(dist.a_raw[owner]) + (int64_t)b * kBlkRows * dist.lda;
-          __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dist.a_full) +
-                               ((int64_t)owner * p.rows_per_rank + (int64_t)b * kBlkRows) * dist.ld_full;
-          for (int64_t v0 = g; v0 < vecs; v0 += 4 * G) {
-            uint4 r[4];
-            int64_t off[4];
+        const __nv_bfloat16* src =
+            reinterpret_cast<const __nv_bfloat16*>(dist.a_raw[owner]) + (int64_t)b * kBlkRows * dist.lda;
+        __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(dist.a_full) +
+                             ((int64_t)owner * p.rows_per_rank + (int64_t)b * kBlkRows) * dist.ld_full;
+        uint4 r[kPullUnroll];
+        int64_t off[kPullUnroll];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-              const int64_t v = v0 + u * G;
-              off[u] = -1;
-              if (v < vecs) {
-                const int64_t row = v / vec_per_row;
-                const int64_t col = (v - row * vec_per_row) << 3;
-                off[u] = row * dist.ld_full + col;
-                r[u] = ld_relaxed_sys_16(src + row * dist.lda + col);
-              }
-            }
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (off[u] >= 0) *reinterpret_cast<uint4*>(dst + off[u]) = r[u];
+        for (int u = 0; u < kPullUnroll; ++u) {
+          const int64_t v = in_blk * kPieceVecs + u * 32 + lane;
+          off[u] = -1;
+          if (v < vecs) {
+            const int64_t row = v / vec_per_row;
+            const int64_t col = (v - row * vec_per_row) << 3;
+            off[u] = row * dist.ld_full + col;
+            r[u] = ld_relaxed_sys_16(src + row * dist.lda + col);
           }
-          if (owner != dist.rank) {
-            asm volatile("bar.sync 3, 256;" ::: "memory");
-            if (pt == 0) {
-              __threadfence();
-              red_release_gpu_add_s32(dist.flags + owner * bpr + b, 1);
-            }
+        }
+#pragma unroll
+        for (int u = 0; u < kPullUnroll; ++u)
+          if (off[u] >= 0) *reinterpret_cast<uint4*>(dst + off[u]) = r[u];
+        if (piece < remote_pieces) {
+          __syncwarp();
+          if (lane == 0) {
+            __threadfence();
+            red_release_gpu_add_s32(dist.flags + owner * bpr + b, 1);
           }
         }
       }
