@@ -49,6 +49,7 @@ s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True
 torch.cuda.cudart().cudaProfilerStart()
 s.record()
 step()
+trainer.strategy.synchronize_optimizer()
 e.record()
 torch.cuda.synchronize()
 torch.cuda.cudart().cudaProfilerStop()

@@ -83,6 +83,20 @@ allgather_pull_kernel(Peers full, int rank, int world, int64_t shard_vec16) {
   }
 }
 
+// ---- ZeRO-3 parameter gather: dst[r * shard .. (r+1) * shard) = rank r's persistent slice, every rank's slice
+// (this rank's included) read from the symmetric shard arena.  Same stagger as above.
+__global__ void __launch_bounds__(512)
+gather_shards_kernel(Peers shards, uint4* __restrict__ dst, int rank, int world, int64_t shard_vec16) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int p = 0; p < world; ++p) {
+    const int src_rank = (rank + 1 + p) % world;       // own slice last
+    const uint4* src = reinterpret_cast<const uint4*>(shards.ptr[src_rank]);
+    uint4* out = dst + (int64_t)src_rank * shard_vec16;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < shard_vec16; i += stride)
+      out[i] = ld_peer_16_fresh(src + i);
+  }
+}
+
 // ---- reduce-scatter (mean) by pulling this rank's slice from every peer + sum of squares of the result
 template <typename T>
 __global__ void __launch_bounds__(512)
@@ -271,6 +285,19 @@ extern "C" int llmt_comm_allgather_pull(const void* const* full_ptrs, int rank, 
   return check_launch("comm_allgather_pull");
 }
 
+// dst_full[r * shard_bytes ..] <- shard_ptrs[r][0 .. shard_bytes) for every rank r (shard_ptrs: this rank's view of
+// every peer's slice, HOST array).  The caller separates this from the writers of the slices with a barrier.
+extern "C" int llmt_comm_gather_shards(const void* const* shard_ptrs, void* dst_full, int rank, int world,
+                                       int64_t shard_bytes, cudaStream_t stream) {
+  LLMT_REQUIRE(shard_bytes % 16 == 0 && (uintptr_t)dst_full % 16 == 0, "gather_shards: 16-byte alignment required");
+  Peers shards;
+  if (fill_peers(&shards, shard_ptrs, world)) return 1;
+  if (shard_bytes == 0) return 0;
+  const int64_t nvec = shard_bytes / 16;
+  gather_shards_kernel<<<grid_for(nvec, 512, 2), 512, 0, stream>>>(shards, (uint4*)dst_full, rank, world, nvec);
+  return check_launch("comm_gather_shards");
+}
+
 extern "C" int llmt_comm_rs_num_partials() { return num_sms() * 2; }
 
 // out_shard[i] = mean over ranks of grad_r[rank*shard_elems + i]; norm_sq[0] (+)= sum(out_shard^2).
@@ -325,7 +352,7 @@ extern "C" int llmt_comm_adamw_push(float* master, float* m, float* v, const voi
   a.bc1 = 1.f - powf(beta1, (float)step);
   a.bc2 = 1.f - powf(beta2, (float)step);
   a.grad_scale = grad_scale; a.max_norm = max_norm;
-  const int grid = grid_for(shard_elems / 8, 256, 8);
+  const int grid = grid_for(shard_elems / 8, 256, update_ctas_per_sm());
   if (grad_is_fp32)
     adamw_push_kernel<float><<<grid, 256, 0, stream>>>(master, m, v, (const float*)grad_shard, params, rank, world,
                                                        shard_elems, a, norm_sq);

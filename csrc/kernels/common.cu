@@ -35,3 +35,12 @@ extern "C" int llmt_abi_version() { return 1; }
 // Number of kernels this library has launched since load (bench.py reports the delta as `gpu_launches`).
 extern "C" unsigned long long llmt_launch_count() { return llmt::g_launches; }
 namespace llmt { void count_launch() { __atomic_add_fetch(&g_launches, 1ull, __ATOMIC_RELAXED); } }
+
+namespace llmt {
+static int g_update_ctas_per_sm = 8;
+int update_ctas_per_sm() { return g_update_ctas_per_sm; }
+}  // namespace llmt
+
+extern "C" void llmt_set_update_ctas_per_sm(int ctas) {
+  llmt::g_update_ctas_per_sm = ctas < 1 ? 1 : (ctas > 8 ? 8 : ctas);
+}

@@ -91,6 +91,10 @@ __device__ __forceinline__ float block_max(float v, float* red) {
   return warp_max(v);
 }
 
+// CTAs per SM used by the optimizer-update kernels (llmt_set_update_ctas_per_sm): 8 when they own the GPU, 2 when
+// they run in the background of the next forward pass so GEMM / attention CTAs can share every SM with them.
+int update_ctas_per_sm();
+
 inline int num_sms() {
   static int n = 0;
   if (n == 0) {

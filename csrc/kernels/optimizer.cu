@@ -156,7 +156,7 @@ extern "C" int llmt_adamw(float* master, float* m, float* v, const void* grad, v
   a.bc2 = 1.f - powf(beta2, (float)step);
   a.grad_scale = grad_scale; a.max_norm = max_norm;
   int64_t blocks = (n / 4 + 255) / 256;
-  const int64_t cap = (int64_t)num_sms() * 8;
+  const int64_t cap = (int64_t)num_sms() * update_ctas_per_sm();
   const int grid = (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
   auto P = (__nv_bfloat16*)param_bf16;
   if (grad_is_fp32) {

@@ -20,6 +20,9 @@ extern "C" {
 const char* llmt_last_error(void);
 int llmt_abi_version(void);
 unsigned long long llmt_launch_count(void); /* kernels launched by this library since load */
+/* CTAs per SM for the optimizer-update kernels (1..8, default 8).  2 lets them run in the background of the next
+ * forward pass: tensor-core CTAs of other streams still fit on every SM. */
+void llmt_set_update_ctas_per_sm(int ctas);
 
 /* ---- GEMM: C[M,N] = op(A)[M,K] * op(B)[K,N] (+ R), bf16 in, fp32 accumulate, tcgen05/TMEM/TMA ----------
  * replaces cuBLAS behind nn.Linear (src/llm_training/models/llama/llama_model.py:459-462,421-423,55).
@@ -54,6 +57,9 @@ int llmt_comm_barrier(const void* const* signal_pads, int rank, int world, int s
                       cudaStream_t stream);
 int llmt_comm_allgather_pull(const void* const* full_ptrs, int rank, int world, int64_t shard_bytes,
                              cudaStream_t stream);
+/* ZeRO-3 parameter gather: full[r * shard_bytes ..] <- rank r's slice, pulled from the symmetric shard arena */
+int llmt_comm_gather_shards(const void* const* shard_ptrs, void* dst_full, int rank, int world, int64_t shard_bytes,
+                            cudaStream_t stream);
 int llmt_comm_rs_num_partials(void);
 int llmt_comm_rs_sumsq(const void* const* grad_ptrs, int rank, int world, int64_t shard_elems, int is_fp32,
                        void* out_shard, float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream);

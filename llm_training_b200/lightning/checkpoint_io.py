@@ -41,15 +41,33 @@ def _full_tensor(strategy, name: str, tensor: torch.Tensor, writer: int | None) 
     return full.to('cpu', copy=True)
 
 
+class _Unsharded:
+    """Every engine's parameters whole for the duration (ZeRO-3 engines gather, resident engines just sync)."""
+
+    def __init__(self, strategy, writeback: bool = False) -> None:
+        self.ctxs = [e.unsharded(writeback=writeback) for e in getattr(strategy, 'engines', [])]
+
+    def __enter__(self):
+        for c in self.ctxs:
+            c.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        for c in reversed(self.ctxs):
+            c.__exit__(*exc)
+        return False
+
+
 def module_state_dict(strategy, balanced: bool) -> dict[str, torch.Tensor]:
     module = strategy.lightning_module
     world = strategy.world_size
     out: dict[str, torch.Tensor] = {}
-    for i, (name, tensor) in enumerate(module.state_dict(keep_vars=True).items()):
-        writer = (i % world) if balanced else None
-        full = _full_tensor(strategy, name, tensor, writer)
-        if full is not None:
-            out[name] = full
+    with _Unsharded(strategy):
+        for i, (name, tensor) in enumerate(module.state_dict(keep_vars=True).items()):
+            writer = (i % world) if balanced else None
+            full = _full_tensor(strategy, name, tensor, writer)
+            if full is not None:
+                out[name] = full
     return out
 
 
@@ -111,7 +129,7 @@ def _load_module_state(strategy, state: dict[str, torch.Tensor]) -> None:
     module = strategy.lightning_module
     own = module.state_dict(keep_vars=True)
     missing = [k for k in own if k not in state]
-    with torch.no_grad():
+    with torch.no_grad(), _Unsharded(strategy, writeback=True):
         for name, target in own.items():
             if name not in state:
                 continue

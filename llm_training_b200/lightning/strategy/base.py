@@ -153,9 +153,15 @@ class Strategy:
         # anything still on CPU / wrong dtype (metrics, user-built submodules)
         self._materialize(module)
         self.engines = self._build_engines(module)
+        for e in self.engines:
+            e.sync_shards_from_full()     # weights were loaded / broadcast into the full buffers after sharding
         if getattr(module, 'weights_used_once_per_step', False):
             for e in self.engines:
                 e.enable_direct_grad_accumulation(True)
+        if self.overlap_optimizer_step and self.root_device.type == 'cuda':
+            # the fused AdamW (+ parameter exchange) of step k runs under the forward pass of step k+1
+            for e in self.engines:
+                e.overlap_optimizer = True
         trainer.optimizers, trainer.lr_scheduler_configs = self._setup_optimizers(trainer, module)
 
     def _materialize(self, module: nn.Module) -> None:
@@ -280,9 +286,11 @@ class Strategy:
 
     # ---------------------------------------------------------------- checkpoint I/O (see checkpoint_io.py)
     save_distributed_checkpoint: bool = False
+    overlap_optimizer_step: bool = os.environ.get('LLMT_OVERLAP_OPT', '1') != '0'
 
     def save_checkpoint(self, checkpoint: dict[str, Any], filepath: str) -> None:
         from ..checkpoint_io import save_checkpoint
+        self.synchronize_optimizer()
         save_checkpoint(self, checkpoint, filepath)
 
     def load_checkpoint(self, filepath: str) -> dict[str, Any]:
@@ -297,8 +305,14 @@ class Strategy:
             elif os.path.exists(filepath):
                 os.remove(filepath)
 
+    def synchronize_optimizer(self) -> None:
+        """The current stream waits for in-flight (overlapped) optimizer work; call before touching parameters or
+        optimizer state outside a model forward, and at timing boundaries."""
+        for e in getattr(self, 'engines', []):
+            e.synchronize_optimizer()
+
     def teardown(self) -> None:
-        pass
+        self.synchronize_optimizer()
 
 
 class _Stack:

@@ -18,7 +18,7 @@ class FSDP2Strategy(Strategy):
                  tensor_parallel_size: int | Literal['auto'] = 1, save_distributed_checkpoint: bool = True,
                  process_group_backend: str | None = None,
                  timeout: datetime.timedelta | None = datetime.timedelta(minutes=30),
-                 reshard_after_forward: bool | int = True, mp_policy: MixedPrecisionPolicy | None = None,
+                 reshard_after_forward: bool | int | str = 'auto', mp_policy: MixedPrecisionPolicy | None = None,
                  offload_policy: OffloadPolicy | None = None, use_master_weights: bool = True) -> None:
         super().__init__(process_group_backend, timeout)
         self._data_parallel_size = data_parallel_size

@@ -311,6 +311,8 @@ class Trainer:
         try:
             self._run_training()
         finally:
+            if hasattr(self.strategy, 'synchronize_optimizer'):
+                self.strategy.synchronize_optimizer()
             self._flush_logs(force=True)
             self._call('on_fit_end')
             model.on_fit_end()
@@ -413,6 +415,8 @@ class Trainer:
         if loader is None:
             return
         model = self.lightning_module
+        if hasattr(self.strategy, 'synchronize_optimizer'):
+            self.strategy.synchronize_optimizer()
         model.eval()
         self.validating = True
         self._val_accum = {}
@@ -465,6 +469,8 @@ class Trainer:
     # ------------------------------------------------------------------ checkpoints
     def dump_checkpoint(self) -> dict[str, Any]:
         model = self.lightning_module
+        if hasattr(self.strategy, 'synchronize_optimizer'):
+            self.strategy.synchronize_optimizer()
         ckpt: dict[str, Any] = {
             'epoch': self.fit_loop.epoch,
             'global_step': self.fit_loop.global_step,

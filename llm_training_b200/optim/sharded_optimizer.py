@@ -20,6 +20,13 @@ from ..ops.adamw_op import adamw_step
 from ..parallel.comm import Comm
 from ..parallel.fsdp import FlatParamEngine
 
+import os
+
+from ..ops import _lib
+
+# occupancy of the update kernels while they share the GPU with the next forward pass
+_BACKGROUND_CTAS_PER_SM = int(os.environ.get('LLMT_OPT_BG_CTAS', '2'))
+
 _ADAMW_LIKE = ('AdamW', 'FusedAdamW', 'FusedAdam', 'Adam', 'DeepSpeedCPUAdam')
 
 
@@ -100,6 +107,7 @@ class ShardedOptimizer(Optimizer):
     # -- step ------------------------------------------------------------------------------------------
     def sync_master_from_params(self) -> None:
         """Call after weights were loaded into the flat buffers (pre-trained weights / checkpoint)."""
+        self.synchronize()
         for _, u, st in self._units():
             if 'master' in st:
                 st['master'].copy_(u.param_shard)
@@ -121,23 +129,14 @@ class ShardedOptimizer(Optimizer):
         max_norm = float(self.max_grad_norm) if self.max_grad_norm else 0.0
         if self.fused:
             g = self._optimizer.param_groups[0]
-            beta1, beta2 = g.get('betas', (0.9, 0.999))
+            hyper = dict(lr=g['lr'], beta1=g.get('betas', (0.9, 0.999))[0], beta2=g.get('betas', (0.9, 0.999))[1],
+                         eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0), step=self.step_count,
+                         max_norm=max_norm, norm_sq=norm_sq)
+            if self._overlap_enabled():
+                self._step_overlapped(hyper)
+                return loss
             for e, u, st in self._units():
-                shard = u.param_shard
-                low = 'master' in st
-                if e.nvlink and low and shard.dtype == torch.bfloat16:
-                    # fused: AdamW on the fp32 slice + bf16 result stored into every peer's parameter arena
-                    e.comm.adamw_push(st['master'], st['exp_avg'], st['exp_avg_sq'], u.local_grad(), e.param_arena,
-                                      u.arena_offset * 2, u.shard_numel, lr=g['lr'], beta1=beta1, beta2=beta2,
-                                      eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0),
-                                      step=self.step_count, max_norm=max_norm, norm_sq=norm_sq)
-                    continue
-                adamw_step(st['master'] if low else shard, st['exp_avg'], st['exp_avg_sq'], u.local_grad(),
-                           shard if (low and shard.dtype == torch.bfloat16) else None, lr=g['lr'], beta1=beta1,
-                           beta2=beta2, eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0),
-                           step=self.step_count, max_norm=max_norm, norm_sq=norm_sq)
-                if low and shard.dtype != torch.bfloat16:
-                    shard.copy_(st['master'])
+                self._update_unit(e, u, st, hyper)
         else:
             clip = 1.0
             if max_norm > 0 and norm_sq is not None:
@@ -153,11 +152,68 @@ class ShardedOptimizer(Optimizer):
                 if 'master' in st:
                     u.param_shard.copy_(st['master_param'].data)
         for e in self.engines:
+            if e.reshard:
+                continue                  # ZeRO-3: the slices are gathered again right before their next use
             if e.nvlink and self.fused:
                 e.comm.barrier()          # all pushed parameter slices have landed everywhere
             else:
                 e.gather_params()
         return loss
+
+    def _update_unit(self, e: FlatParamEngine, u, st: dict, hyper: dict) -> bool:
+        """Fused AdamW on one unit's slice.  Returns True when the new parameters were also pushed to the peers."""
+        shard = u.param_shard
+        low = 'master' in st
+        if e.nvlink and not e.reshard and low and shard.dtype == torch.bfloat16:
+            # fused: AdamW on the fp32 slice + bf16 result stored into every peer's parameter arena
+            e.comm.adamw_push(st['master'], st['exp_avg'], st['exp_avg_sq'], u.local_grad(), e.param_arena,
+                              u.arena_offset * 2, u.shard_numel, **hyper)
+            return True
+        adamw_step(st['master'] if low else shard, st['exp_avg'], st['exp_avg_sq'], u.local_grad(),
+                   shard if (low and shard.dtype == torch.bfloat16) else None, **hyper)
+        if low and shard.dtype != torch.bfloat16:
+            shard.copy_(st['master'])
+        return False
+
+    def _overlap_enabled(self) -> bool:
+        return all(e.overlap_optimizer and e._opt_stream is not None for e in self.engines)
+
+    def _step_overlapped(self, hyper: dict) -> None:
+        """Per-unit update -> (push | gather) -> barrier -> grad clear on the engine's side stream, in the order the
+        next forward pass touches the units; each unit's first use waits on its own event (engine forward
+        pre-hooks), so the memory-bound AdamW and the parameter exchange run under the next step's GEMMs."""
+        i = 0
+        for e in self.engines:
+            states = self.unit_state[i:i + len(e.units)]
+            i += len(e.units)
+            stream = e._opt_stream
+            stream.wait_stream(torch.cuda.current_stream(e.device))
+            order = sorted(range(len(e.units)), key=lambda k: (e.units[k].hook_seen, k))   # un-hooked units first
+            background = _lib.kernels_available() and e.device.type == 'cuda'
+            if background:
+                _lib.lib().llmt_set_update_ctas_per_sm(_BACKGROUND_CTAS_PER_SM)
+            with torch.cuda.stream(stream):
+                for k in order:
+                    u, st = e.units[k], states[k]
+                    pushed = self._update_unit(e, u, st, hyper)
+                    if pushed:
+                        e.comm.barrier()              # this unit's slices have landed on every rank
+                    else:
+                        e.gather_unit(u)
+                    if u.grad_live:
+                        u.flat_grad.zero_()
+                        u.grad_zeroed = True
+                    if u.ready_event is None:
+                        u.ready_event = torch.cuda.Event()
+                    u.ready_event.record(stream)
+                    u.ready_pending = True
+            if background:
+                _lib.lib().llmt_set_update_ctas_per_sm(8)
+
+    def synchronize(self) -> None:
+        """Make the current stream wait for in-flight unit updates (before reading parameters / state directly)."""
+        for e in self.engines:
+            e.synchronize_optimizer()
 
     def zero_grad(self, set_to_none: bool = True) -> None:
         for e in self.engines:
@@ -165,6 +221,7 @@ class ShardedOptimizer(Optimizer):
 
     # -- checkpointing: per-unit shards, keyed by unit name ---------------------------------------------
     def state_dict(self) -> dict:
+        self.synchronize()
         units = {}
         for _, u, st in self._units():
             units[u.name] = {k: v for k, v in st.items() if k in ('master', 'exp_avg', 'exp_avg_sq')}
@@ -175,6 +232,7 @@ class ShardedOptimizer(Optimizer):
         return sd
 
     def load_state_dict(self, state_dict: dict) -> None:
+        self.synchronize()
         self.step_count = int(state_dict.get('step', 0))
         for _, u, st in self._units():
             saved = state_dict['units'].get(u.name, {})

@@ -49,7 +49,7 @@ class ShardedUnit:
     def __init__(self, name: str, params: list[tuple[str, nn.Parameter]], world: int, rank: int,
                  device: torch.device, dtype: torch.dtype, grad_dtype: torch.dtype,
                  flat_param: torch.Tensor | None = None, flat_grad: torch.Tensor | None = None,
-                 arena_offset: int = 0) -> None:
+                 arena_offset: int = 0, reshard: bool = False, shard_store: torch.Tensor | None = None) -> None:
         self.name = name
         self.params = params
         self.world, self.rank = world, rank
@@ -72,11 +72,30 @@ class ShardedUnit:
         self.pending_grads = 0
         self.reduced = False
         self.work: Any = None
+        # ZeRO-3 mode: the owned slice lives in its own persistent tensor; the full parameter / gradient buffers
+        # only have storage between `unshard` and `reshard` (their tensor objects, and every view of them held
+        # by parameters or saved by autograd, stay valid across the storage resize)
+        self.reshard = reshard and world > 1
+        self._shard: torch.Tensor | None = None
+        if self.reshard:
+            self._shard = shard_store if shard_store is not None else torch.zeros(
+                self.shard_numel, dtype=dtype, device=device)
+            self._shard.copy_(self.flat_param[rank * self.shard_numel:(rank + 1) * self.shard_numel])
+        self.is_sharded = False       # flat_param currently has no storage
+        self.grad_live = True         # flat_grad currently has storage (and holds zeros or partial sums)
+        self.in_backward = False
+        self.gather_event: Any = None
+        self.gather_pending = False
 
     @property
     def param_shard(self) -> torch.Tensor:
+        if self._shard is not None:
+            return self._shard
         s = self.shard_numel
         return self.flat_param[self.rank * s:(self.rank + 1) * s]
+
+    def _set_storage(self, t: torch.Tensor, present: bool) -> None:
+        t.untyped_storage().resize_(self.padded_numel * t.element_size() if present else 0)
 
     def local_grad(self) -> torch.Tensor:
         return self.grad_shard[:self.shard_numel] if self.world == 1 else self.grad_shard
@@ -94,7 +113,7 @@ class ShardedUnit:
 class FlatParamEngine:
     def __init__(self, units: list[tuple[str, list[tuple[str, nn.Parameter]]]], dp_axis: MeshAxis | None,
                  device: torch.device, comm: Comm | None = None, grad_dtype: torch.dtype | None = None,
-                 tp_axis: MeshAxis | None = None) -> None:
+                 tp_axis: MeshAxis | None = None, reshard: bool = False) -> None:
         self.axis = dp_axis if dp_axis is not None else MeshAxis('data_parallel', [0], 0, None)
         # tensor-parallel peers hold different shards of most parameters but REPLICAS of a few (norm weights);
         # under sequence parallelism the replicas' gradients are partial sums over the tp axis
@@ -105,9 +124,27 @@ class FlatParamEngine:
         self.units: list[ShardedUnit] = []
         units = [(n, ps) for n, ps in units if ps]
         self.nvlink = bool(getattr(self.comm, 'is_nvlink', False)) and self.world > 1
-        self.param_arena = self.grad_arena = None
+        self.param_arena = self.grad_arena = self.shard_arena = None
+        self.reshard = bool(reshard) and self.world > 1
         dtypes = {ps[0][1].dtype for _, ps in units}
-        if self.nvlink and len(dtypes) == 1:
+        if self.reshard:
+            # ZeRO-3: only the owned slices are persistent.  On NVLink they sit in ONE symmetric arena so that any
+            # rank can pull any slice (csrc/kernels/comm.cu gather_shards / the weight-gathering GEMM); gradients
+            # are reduced by the generic reduce-scatter of the backend.
+            shard_sizes = [ShardedUnit.layout(ps, self.world)[2] // self.world for _, ps in units]
+            if self.nvlink and len(dtypes) == 1:
+                self.shard_arena = self.comm.alloc(sum(shard_sizes), next(iter(dtypes)))
+                self.shard_arena.tensor.zero_()
+            off = 0
+            for (name, params), ssz in zip(units, shard_sizes):
+                dtype = params[0][1].dtype
+                assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
+                store = self.shard_arena.tensor[off:off + ssz] if self.shard_arena is not None else None
+                self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype,
+                                              arena_offset=off, reshard=True, shard_store=store))
+                off += ssz
+            self.nvlink_grads = False
+        elif self.nvlink and len(dtypes) == 1:
             # one symmetric allocation for all parameters and one for all gradients: peers address any unit as
             # arena base + offset, and a single rendezvous exchanges the handles
             dtype = next(iter(dtypes))
@@ -129,10 +166,23 @@ class FlatParamEngine:
                 dtype = params[0][1].dtype
                 assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
                 self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype))
+        # `nvlink` = parameters travel through our kernels; `nvlink_grads` = gradients do too (resident mode only)
+        self.nvlink_grads = self.nvlink and not self.reshard
+        self._forward_order: list[ShardedUnit] = []      # hooked units in the order the last forward used them
         self._norm_accumulating = False
         self.require_sync = True
         self._comm_stream = torch.cuda.Stream(device) if device.type == 'cuda' and self.world > 1 else None
         self._norm_sq = torch.zeros(1, dtype=torch.float32, device=device)
+        # optimizer overlap (see ShardedOptimizer.step): per-unit updates run on a side stream while the next
+        # forward pass starts; a unit's first use waits on the event recorded after its update
+        self.overlap_optimizer = False
+        self._opt_stream = self._comm_stream if self._comm_stream is not None else (
+            torch.cuda.Stream(device) if device.type == 'cuda' else None)
+        for u in self.units:
+            u.ready_event = None          # recorded on the optimizer stream after the unit's update (+ gather)
+            u.ready_pending = False
+            u.hook_seen = False           # the unit's module runs a forward pre-hook (else: waited at model entry)
+            u.grad_zeroed = False         # flat_grad was cleared by the optimizer stream after the update
         self._param_to_unit: dict[int, ShardedUnit] = {}
         for u in self.units:
             for _, p in u.params:
@@ -150,6 +200,7 @@ class FlatParamEngine:
 
     def _on_grad_ready(self, param: nn.Parameter) -> None:
         u = self._param_to_unit[id(param)]
+        u.grad_zeroed = False
         u.pending_grads -= 1
         if u.pending_grads == 0 and self.require_sync:
             self._launch_reduce(u)
@@ -168,6 +219,8 @@ class FlatParamEngine:
                 self._reduce(u)
         else:
             self._reduce(u)
+        if self.reshard:
+            self._after_unit_backward(u)
 
     def _reduce(self, u: ShardedUnit) -> None:
         if self.tp_axis is not None:
@@ -177,7 +230,7 @@ class FlatParamEngine:
                     dist.all_reduce(p.grad, group=self.tp_axis.group)
         if self.world == 1:
             return
-        if self.nvlink:
+        if self.nvlink_grads:
             # barrier + pull of this rank's slice from every peer + squared-norm partial, one pass over NVLink
             esize = u.flat_grad.element_size()
             self.comm.reduce_scatter_sumsq(self.grad_arena, u.arena_offset * esize, u.shard_numel, u.grad_shard,
@@ -206,19 +259,189 @@ class FlatParamEngine:
         if not self.require_sync:
             self._rearm()
             return
+        if self.reshard:
+            for u in self.units:       # un-hooked units / units that saw no backward still need gradient storage
+                if not u.reduced:
+                    self._alloc_grad(u)
         for u in self.units:
             if not u.reduced:          # params that received no grad this step (unused / frozen siblings)
                 self._launch_reduce(u)
         if self._comm_stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        if self.reshard:
+            for u in self.units:
+                u.in_backward = False
+                self.reshard_unit(u)
+                self._free_grad(u)
 
     def _rearm(self) -> None:
         for u in self.units:
             u.pending_grads = sum(1 for _, p in u.params if p.requires_grad)
+            if self.reshard:              # non-boundary micro-batch: keep the partial gradients, drop the parameters
+                u.in_backward = False
+                self.reshard_unit(u)
+
+    # ------------------------------------------------------------------ optimizer overlap
+    def attach_module_hooks(self, model: nn.Module) -> None:
+        """Forward pre-hooks that make a unit's first use wait for its (possibly still running) optimizer update."""
+        by_name: dict[str, list[ShardedUnit]] = {}
+        for u in self.units:
+            by_name.setdefault(u.name.split('#')[0], []).append(u)
+        unit_modules = dict(model.sharding_units()) if hasattr(model, 'sharding_units') else {}
+
+        def make_hook(units: list[ShardedUnit]):
+            def hook(module, args):
+                for u in units:
+                    u.hook_seen = True
+                    self.wait_unit(u)
+                    if self.reshard:
+                        self._pre_forward(u)
+            return hook
+
+        def make_post_hook(units: list[ShardedUnit]):
+            def hook(module, args, output):
+                if not self.reshard:
+                    return
+                self._post_forward(units, output)
+            return hook
+
+        for name, module in unit_modules.items():
+            if name in by_name and module is not model:
+                module.register_forward_pre_hook(make_hook(by_name[name]))
+                module.register_forward_hook(make_post_hook(by_name[name]))
+
+        def root_hook(module, args):
+            if self.reshard:
+                self._forward_order = []
+            for u in self.units:
+                if not u.hook_seen:
+                    self.wait_unit(u)
+                    if self.reshard:          # units used without a module call stay whole for the entire step
+                        self.unshard(u)
+                        self.wait_unshard(u)
+                        if torch.is_grad_enabled():
+                            self._alloc_grad(u)
+
+        model.register_forward_pre_hook(root_hook)
+
+    # ------------------------------------------------------------------ ZeRO-3: gather before use, drop after use
+    def unshard(self, u: ShardedUnit) -> None:
+        """Give ``flat_param`` storage and start gathering every rank's slice into it on the side stream."""
+        if not u.is_sharded:
+            return
+        u._set_storage(u.flat_param, True)
+        u.is_sharded = False
+        main = torch.cuda.current_stream(self.device) if self._comm_stream is not None else None
+        if self._comm_stream is not None:
+            self._comm_stream.wait_stream(main)        # the slice may have just been written by the optimizer
+            with torch.cuda.stream(self._comm_stream):
+                self._gather_into_full(u)
+                if u.gather_event is None:
+                    u.gather_event = torch.cuda.Event()
+                u.gather_event.record(self._comm_stream)
+            u.gather_pending = True
+        else:
+            self._gather_into_full(u)
+
+    def _gather_into_full(self, u: ShardedUnit) -> None:
+        if self.shard_arena is not None:
+            esize = u.flat_param.element_size()
+            self.comm.gather_shards(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param)
+        else:
+            self.comm.all_gather_into(u.flat_param, u.param_shard)
+
+    def wait_unshard(self, u: ShardedUnit) -> None:
+        if u.gather_pending:
+            torch.cuda.current_stream(self.device).wait_event(u.gather_event)
+            u.gather_pending = False
+
+    def reshard_unit(self, u: ShardedUnit) -> None:
+        if u.is_sharded or not self.reshard:
+            return
+        self.wait_unshard(u)              # never free under an in-flight gather
+        u._set_storage(u.flat_param, False)
+        u.is_sharded = True
+
+    def _pre_forward(self, u: ShardedUnit) -> None:
+        self.unshard(u)
+        self.wait_unshard(u)
+        if not u.in_backward:
+            if u not in self._forward_order:
+                self._forward_order.append(u)
+            nxt = self._next_in_order(u, +1)
+            if nxt is not None:
+                self.unshard(nxt)         # prefetch: its gather runs under this unit's compute
+
+    def _next_in_order(self, u: ShardedUnit, step: int) -> ShardedUnit | None:
+        order = self._last_forward_order if getattr(self, '_last_forward_order', None) else None
+        if not order or u not in order:
+            return None
+        k = order.index(u) + step
+        return order[k] if 0 <= k < len(order) else None
+
+    def _post_forward(self, units: list[ShardedUnit], output: Any) -> None:
+        if any(u.in_backward for u in units):
+            return                        # activation recompute inside backward: parameters are needed right after
+        if torch.is_grad_enabled():
+            outs = output if isinstance(output, (tuple, list)) else (output,)
+            for t in outs:
+                if torch.is_tensor(t) and t.requires_grad:
+                    t.register_hook(lambda g, units=units: self._pre_backward(units))
+        for u in units:
+            self.reshard_unit(u)
+
+    def _pre_backward(self, units: list[ShardedUnit]) -> None:
+        self._last_forward_order = list(self._forward_order) or getattr(self, '_last_forward_order', [])
+        for u in units:
+            if u.in_backward:
+                continue
+            u.in_backward = True
+            self.unshard(u)
+            self.wait_unshard(u)
+            self._alloc_grad(u)
+            prev = self._next_in_order(u, -1)
+            if prev is not None and not prev.in_backward:
+                self.unshard(prev)        # prefetch for the unit whose backward runs next
+        return None
+
+    def _alloc_grad(self, u: ShardedUnit) -> None:
+        if not u.grad_live:
+            u._set_storage(u.flat_grad, True)
+            u.flat_grad.zero_()
+            u.grad_live = True
+            u.grad_zeroed = True
+
+    def _after_unit_backward(self, u: ShardedUnit) -> None:
+        """The unit's gradients were handed to the reduce-scatter: drop its full parameter and gradient buffers."""
+        if not u.hook_seen:
+            return                        # un-hooked units are dropped in finish_backward
+        self.reshard_unit(u)
+        self._free_grad(u)
+
+    def _free_grad(self, u: ShardedUnit) -> None:
+        if u.grad_live and self.require_sync and self.world > 1:
+            if self._comm_stream is not None:
+                u.flat_grad.record_stream(self._comm_stream)     # the reduce-scatter may still be reading it
+            u._set_storage(u.flat_grad, False)
+            u.grad_live = False
+
+    def wait_unit(self, u: ShardedUnit) -> None:
+        if u.ready_pending:
+            torch.cuda.current_stream(self.device).wait_event(u.ready_event)
+            u.ready_pending = False
+
+    def synchronize_optimizer(self) -> None:
+        """Current stream waits for every in-flight unit update (checkpointing, evaluation, timing boundaries)."""
+        for u in self.units:
+            self.wait_unit(u)
 
     def zero_grad(self) -> None:
         for u in self.units:
-            u.flat_grad.zero_()
+            if not u.grad_live:           # ZeRO-3: no storage until the unit's next backward allocates + clears it
+                continue
+            if not u.grad_zeroed:
+                self.wait_unit(u)
+                u.flat_grad.zero_()
             for (_, p), o in zip(u.params, u.offsets):   # something may have replaced .grad (set_to_none)
                 if p.grad is None or p.grad.data_ptr() != u.flat_grad.data_ptr() + o * u.flat_grad.element_size():
                     p.grad = u.flat_grad[o:o + p.numel()].view(p.shape)
@@ -228,7 +451,7 @@ class FlatParamEngine:
         """Device scalar: squared L2 norm of the (already reduced) gradient, summed over the dp axis
         (and any extra axes the parameters are sharded over).  No host sync."""
         from ..ops.adamw_op import sumsq
-        if self.nvlink:
+        if self.nvlink_grads:
             # per-unit partial norms were accumulated by the reduce-scatter kernels; one tiny all-reduce is left
             self._norm_accumulating = False
             self._discount_tp_replicas()
@@ -259,9 +482,20 @@ class FlatParamEngine:
                     self._norm_sq -= g[start:start + length].float().pow(2).sum()
 
     # ------------------------------------------------------------------ parameters
+    def gather_unit(self, u: ShardedUnit) -> None:
+        """Rebuild ONE unit's full buffer from the updated slices (used by the overlapped optimizer step)."""
+        if self.world == 1 or self.reshard:       # ZeRO-3: the next use gathers
+            return
+        if self.nvlink:
+            esize = self.param_arena.tensor.element_size()
+            self.comm.allgather_pull(self.param_arena, u.arena_offset * esize, u.shard_numel * esize)
+            self.comm.barrier()
+            return
+        self.comm.all_gather_into(u.flat_param, u.param_shard)
+
     def gather_params(self) -> None:
         """After the optimizer updated every rank's slice: rebuild the full bf16 buffers in place."""
-        if self.world == 1:
+        if self.world == 1 or self.reshard:
             return
         if self.nvlink:
             esize = self.param_arena.tensor.element_size()
@@ -275,6 +509,46 @@ class FlatParamEngine:
     def broadcast_params(self, src_index: int = 0) -> None:
         for u in self.units:
             self.comm.broadcast(u.flat_param, src_index)
+        self.sync_shards_from_full()
+
+    # ------------------------------------------------------------------ ZeRO-3: whole-model access
+    def sync_shards_from_full(self) -> None:
+        """After something wrote the FULL parameters directly (weight loading, checkpoint restore, init
+        broadcast): refresh the persistent owned slices.  No-op in resident mode."""
+        if not self.reshard:
+            return
+        for u in self.units:
+            if not u.is_sharded:
+                s = u.shard_numel
+                u._shard.copy_(u.flat_param[self.rank * s:(self.rank + 1) * s])
+
+    def unshard_all(self) -> None:
+        for u in self.units:
+            self.wait_unit(u)
+            if self.reshard:
+                self.unshard(u)
+                self.wait_unshard(u)
+
+    def reshard_all(self) -> None:
+        if self.reshard:
+            for u in self.units:
+                self.reshard_unit(u)
+
+    def unsharded(self, writeback: bool = False):
+        """Context manager: every parameter is whole inside (state_dict, export, evaluation helpers); with
+        ``writeback`` the owned slices are refreshed from whatever was written."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def ctx():
+            self.unshard_all()
+            try:
+                yield self
+            finally:
+                if writeback:
+                    self.sync_shards_from_full()
+                self.reshard_all()
+        return ctx()
 
     def num_parameters(self) -> int:
         return sum(u.numel for u in self.units)
@@ -306,12 +580,31 @@ def _collect_units(model: nn.Module, only_trainable: bool = True
     return groups
 
 
-def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_after_forward: bool | int = True,
+def _resolve_reshard(mode: Any, units: list, dp_mesh: MeshAxis | None, device: torch.device) -> bool:
+    """``True`` / an int -> ZeRO-3 (full buffers only around a unit's use), ``False`` -> resident parameters
+    (ZeRO-2), ``'auto'`` (our default) -> resident unless bf16 parameters + gradients would take more than 40% of
+    the device.  ``LLMT_RESHARD=0|1`` overrides.  The reference's default is ``True``
+    (fsdp2_strategy.py:56); at 180 GB per GPU resident is faster whenever it fits."""
+    import os
+    if dp_mesh is None or dp_mesh.size() <= 1:
+        return False
+    env = os.environ.get('LLMT_RESHARD')
+    if env in ('0', '1'):
+        return env == '1'
+    if isinstance(mode, str) or mode is None:
+        if device.type != 'cuda':
+            return False
+        need = 2 * sum(p.numel() * p.element_size() for _, ps in units for _, p in ps)
+        return need > 0.4 * torch.cuda.get_device_properties(device).total_memory
+    return bool(mode)
+
+
+def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_after_forward: bool | int | str = 'auto',
                         mp_policy: Any = None, offload_policy: Any = None, device: torch.device | None = None,
                         comm: Comm | None = None, **_: Any) -> FlatParamEngine:
     """Build the flat-parameter engine for ``model`` over the data-parallel axis and attach it as
-    ``model._flat_engine``.  ``reshard_after_forward`` / ``offload_policy`` are accepted for API parity;
-    parameters stay resident (see module docstring)."""
+    ``model._flat_engine``.  ``reshard_after_forward`` selects ZeRO-3 vs resident parameters (see
+    ``_resolve_reshard``); ``offload_policy`` is accepted for API parity."""
     if getattr(model, '_flat_engine', None) is not None:
         return model._flat_engine
     if device is None:
@@ -320,8 +613,11 @@ def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_afte
     # gradients are reduced in the parameter dtype (bf16 for `bf16-true`, like the reference's default
     # MixedPrecisionPolicy, fsdp2_precision.py:72-76); `.grad` must match the parameter dtype anyway
     tp_axis = getattr(getattr(model, 'tp_context', None), 'axis', None)
-    engine = FlatParamEngine(_collect_units(model), dp_mesh, device, comm=comm, tp_axis=tp_axis)
+    units = _collect_units(model)
+    engine = FlatParamEngine(units, dp_mesh, device, comm=comm, tp_axis=tp_axis,
+                             reshard=_resolve_reshard(reshard_after_forward, units, dp_mesh, device))
     model._flat_engine = engine
+    engine.attach_module_hooks(model)
     if offload_policy is not None and getattr(offload_policy, 'pin_memory', None) is not None \
             and type(offload_policy).__name__ == 'CPUOffloadPolicy':
         logger.warning('CPU offload requested: not needed at 180 GB/GPU, parameters stay on device')

@@ -28,12 +28,13 @@ def _loss(model, ids):
     return torch.nn.functional.cross_entropy(logits[:, :-1].flatten(0, 1), ids[:, 1:].flatten())
 
 
-def _dp_worker(rank: int, world: int, steps: int, accum: int):
+def _dp_worker(rank: int, world: int, steps: int, accum: int, reshard: bool = False):
     from llm_training_b200.optim import ShardedOptimizer
     from llm_training_b200.parallel import apply_fully_sharded, init_mesh
     mesh = init_mesh(world, 1)
     model = _make_model()
-    engine = apply_fully_sharded(model, mesh.dp)
+    engine = apply_fully_sharded(model, mesh.dp, reshard_after_forward=reshard)
+    assert engine.reshard == reshard
     opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1), [engine],
                            max_grad_norm=1.0)
     losses = []
@@ -49,13 +50,20 @@ def _dp_worker(rank: int, world: int, steps: int, accum: int):
                 engine._rearm()
             losses.append(loss.item())
         opt.step()
-    return {n: p.detach().clone() for n, p in model.named_parameters()}, losses, float(opt.last_grad_norm)
+        if reshard:      # ZeRO-3: between steps no unit keeps its full parameter or gradient buffer
+            assert all(u.is_sharded and not u.grad_live for u in engine.units), \
+                [(u.name, u.is_sharded, u.grad_live) for u in engine.units]
+    with engine.unsharded():
+        params = {n: p.detach().clone() for n, p in model.named_parameters()}
+    return params, losses, float(opt.last_grad_norm)
 
 
-@pytest.mark.parametrize('accum', [1, 2])
-def test_sharded_data_parallel_matches_single_process(accum):
+@pytest.mark.parametrize('accum,reshard', [(1, False), (2, False), (1, True), (2, True)])
+def test_sharded_data_parallel_matches_single_process(accum, reshard):
+    """Resident (ZeRO-2) and resharding (ZeRO-3: gather before use, drop after use) engines both reproduce the
+    single-process run."""
     steps = 3
-    results = run_distributed(_dp_worker, world=2, args=(steps, accum))
+    results = run_distributed(_dp_worker, world=2, args=(steps, accum, reshard))
     ref = _make_model()
     ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2, weight_decay=0.1)
     for step in range(steps):

@@ -354,3 +354,41 @@ def test_direct_wgrad_accumulation_matches_autograd_path():
     assert all(u.pending_grads <= 0 for u in ea.units)          # every parameter reported in
     for ua, ub in zip(ea.units, eb.units):
         _close(ua.flat_grad, ub.flat_grad, rtol=2e-2, atol=2e-3)
+
+
+def test_overlapped_optimizer_step_is_bit_identical():
+    """AdamW of step k on the side stream under the forward of step k+1 (engine events + forward pre-hooks)
+    gives exactly the losses and parameters of the serial schedule."""
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=3,
+                      num_attention_heads=4, num_key_value_heads=2)
+    results = []
+    for overlap in (False, True):
+        torch.manual_seed(0)
+        with torch.device(DEV):
+            model = Llama(cfg).to(torch.bfloat16)
+        engine = apply_fully_sharded(model, None, device=torch.device(DEV))
+        engine.overlap_optimizer = overlap
+        opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
+                               max_grad_norm=1.0)
+        losses = []
+        for step in range(5):
+            ids = torch.randint(0, 512, (2, 256), generator=torch.Generator().manual_seed(step)).to(DEV)
+            opt.zero_grad()
+            out = model(input_ids=ids, skip_logits=True)
+            loss = fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                              shift_labels(ids).flatten())
+            loss.backward()
+            opt.step()
+            losses.append(loss.detach())
+        opt.synchronize()
+        torch.cuda.synchronize()
+        if overlap:
+            assert any(u.hook_seen for u in engine.units)
+        results.append(([float(x) for x in losses], [p.detach().clone() for p in model.parameters()]))
+    assert results[0][0] == results[1][0], (results[0][0], results[1][0])
+    for a, b in zip(results[0][1], results[1][1]):
+        assert torch.equal(a, b)

@@ -18,6 +18,9 @@ def _free_port() -> int:
 
 def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
     try:
+        flags = comm_kind.split('+')[1:]
+        overlap, reshard = 'overlap' in flags, 'reshard' in flags
+        comm_kind = comm_kind.split('+')[0]
         os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
                           MASTER_PORT=str(port), LLMT_COMM=comm_kind)
         import torch.distributed as dist
@@ -33,8 +36,10 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
                           num_attention_heads=4, num_key_value_heads=2)
         with torch.device('cuda'):
             model = Llama(cfg).to(torch.bfloat16)
-        engine = apply_fully_sharded(model, mesh.dp, device=torch.device('cuda', rank))
-        assert engine.nvlink == (comm_kind == 'nvlink')
+        engine = apply_fully_sharded(model, mesh.dp, device=torch.device('cuda', rank), reshard_after_forward=reshard)
+        assert engine.nvlink == (comm_kind == 'nvlink') and engine.reshard == reshard
+        assert (engine.shard_arena is not None) == (reshard and comm_kind == 'nvlink')
+        engine.overlap_optimizer = overlap          # optimizer of step k under the forward of step k+1
         opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
                                max_grad_norm=1.0)
         losses, norms = [], []
@@ -49,8 +54,12 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
             opt.step()
             losses.append(float(loss))
             norms.append(float(opt.last_grad_norm))
+        opt.synchronize()
         torch.cuda.synchronize()
-        checksum = [float(p.float().sum()) for p in model.parameters()]
+        if reshard:
+            assert all(u.is_sharded and not u.grad_live for u in engine.units)
+        with engine.unsharded():
+            checksum = [float(p.float().sum()) for p in model.parameters()]
         queue.put((rank, 'ok', (losses, norms, checksum)))
         dist.barrier()
         dist.destroy_process_group()
@@ -91,6 +100,27 @@ def test_nvlink_engine_matches_nccl_engine():
             assert abs(a - b) <= 2e-2 * max(1.0, abs(a)), (a, b)
     # every rank ends with the same parameters
     assert all(abs(a - b) < 1e-6 * max(1.0, abs(a)) for a, b in zip(got[0][2], got[1][2]))
+    # the overlapped optimizer step (per-unit update + push + barrier on the side stream, first use waits on the
+    # unit's event) must not change a single bit, on either backend
+    for kind, base in (('nvlink+overlap', got), ('torch+overlap', ref)):
+        ov = _run(kind)
+        for rank in (0, 1):
+            assert ov[rank][0] == base[rank][0], (kind, ov[rank][0], base[rank][0])
+            assert ov[rank][2] == base[rank][2], kind
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
+def test_zero3_resharding_engine_matches_resident_engine():
+    """ZeRO-3 mode (persistent slices only; full buffers gathered before a unit's use and dropped after it) with the
+    NCCL gather and with the NVLink pull from the symmetric shard arena, with and without the overlapped
+    optimizer, against the resident NCCL engine."""
+    ref = _run('torch')
+    for kind in ('torch+reshard', 'nvlink+reshard', 'nvlink+reshard+overlap'):
+        got = _run(kind)
+        for rank in (0, 1):
+            assert got[rank][0] == ref[rank][0], (kind, got[rank][0], ref[rank][0])
+            for a, b in zip(ref[rank][2], got[rank][2]):
+                assert abs(a - b) <= 1e-3 * max(1.0, abs(a)), (kind, a, b)
 
 
 def _tp_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
