@@ -195,12 +195,20 @@ class FlatParamEngine:
     def _reset_pending(self) -> None:
         for u in self.units:
             u.pending_grads = sum(1 for _, p in u.params if p.requires_grad)
+            u.ready_ids = set()
             u.reduced = False
             u.work = None
 
     def _on_grad_ready(self, param: nn.Parameter) -> None:
+        """One notification per parameter and backward pass.  A parameter can report twice — the wgrad GEMM that
+        accumulated straight into the flat buffer reports it, and autograd's AccumulateGrad node still runs its
+        post-accumulate hook for the ``None`` gradient the op returned — so readiness is tracked per parameter,
+        not by counting calls."""
         u = self._param_to_unit[id(param)]
         u.grad_zeroed = False
+        if id(param) in u.ready_ids:
+            return
+        u.ready_ids.add(id(param))
         u.pending_grads -= 1
         if u.pending_grads == 0 and self.require_sync:
             self._launch_reduce(u)
@@ -277,6 +285,7 @@ class FlatParamEngine:
     def _rearm(self) -> None:
         for u in self.units:
             u.pending_grads = sum(1 for _, p in u.params if p.requires_grad)
+            u.ready_ids = set()
             if self.reshard:              # non-boundary micro-batch: keep the partial gradients, drop the parameters
                 u.in_backward = False
                 self.reshard_unit(u)

@@ -19,7 +19,7 @@ def _free_port() -> int:
 def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
     try:
         flags = comm_kind.split('+')[1:]
-        overlap, reshard = 'overlap' in flags, 'reshard' in flags
+        overlap, reshard, direct = 'overlap' in flags, 'reshard' in flags, 'direct' in flags
         comm_kind = comm_kind.split('+')[0]
         os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
                           MASTER_PORT=str(port), LLMT_COMM=comm_kind)
@@ -40,6 +40,7 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
         assert engine.nvlink == (comm_kind == 'nvlink') and engine.reshard == reshard
         assert (engine.shard_arena is not None) == (reshard and comm_kind == 'nvlink')
         engine.overlap_optimizer = overlap          # optimizer of step k under the forward of step k+1
+        engine.enable_direct_grad_accumulation(direct)   # wgrad GEMMs accumulate straight into the flat grads
         opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
                                max_grad_norm=1.0)
         losses, norms = [], []
@@ -107,6 +108,17 @@ def test_nvlink_engine_matches_nccl_engine():
         for rank in (0, 1):
             assert ov[rank][0] == base[rank][0], (kind, ov[rank][0], base[rank][0])
             assert ov[rank][2] == base[rank][2], kind
+    # direct wgrad accumulation into the flat gradient buffers: every parameter's gradient must be in the buffer
+    # BEFORE the unit's reduce-scatter starts (the accumulate order differs, so compare with a tolerance)
+    for kind, base in (('nvlink+direct', got), ('torch+direct', ref)):
+        dr = _run(kind)
+        for rank in (0, 1):
+            for a, b in zip(base[rank][0], dr[rank][0]):
+                assert abs(a - b) < 5e-3, (kind, base[rank][0], dr[rank][0])
+            for a, b in zip(base[rank][1], dr[rank][1]):
+                assert abs(a - b) < 5e-3 * max(1.0, a), (kind, base[rank][1], dr[rank][1])
+            for a, b in zip(base[rank][2], dr[rank][2]):
+                assert abs(a - b) <= 5e-3 * max(1.0, abs(a)), (kind, a, b)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
@@ -115,7 +127,7 @@ def test_zero3_resharding_engine_matches_resident_engine():
     NCCL gather and with the NVLink pull from the symmetric shard arena, with and without the overlapped
     optimizer, against the resident NCCL engine."""
     ref = _run('torch')
-    for kind in ('torch+reshard', 'nvlink+reshard', 'nvlink+reshard+overlap'):
+    for kind in ('torch+reshard', 'nvlink+reshard', 'nvlink+reshard+overlap+direct'):
         got = _run(kind)
         for rank in (0, 1):
             assert got[rank][0] == ref[rank][0], (kind, got[rank][0], ref[rank][0])
