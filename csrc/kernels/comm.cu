@@ -97,6 +97,19 @@ gather_shards_kernel(Peers shards, uint4* __restrict__ dst, int rank, int world,
   }
 }
 
+// Same for the 16-byte vectors [lo, hi) of the unit's flat buffer EXCEPT [skip_lo, skip_hi): the skipped range is
+// gathered by its first consumer (the weight-gathering GEMM, csrc/kernels/gemm.cu kDistA == 3).
+__global__ void __launch_bounds__(512)
+gather_range_kernel(Peers shards, uint4* __restrict__ dst, int64_t shard_vec16, int64_t lo, int64_t hi,
+                    int64_t skip_lo, int64_t skip_hi) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t v = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < hi; v += stride) {
+    if (v >= skip_lo && v < skip_hi) continue;
+    const int64_t owner = v / shard_vec16;
+    dst[v] = ld_peer_16_fresh(reinterpret_cast<const uint4*>(shards.ptr[owner]) + (v - owner * shard_vec16));
+  }
+}
+
 // ---- reduce-scatter (mean) by pulling this rank's slice from every peer + sum of squares of the result
 template <typename T>
 __global__ void __launch_bounds__(512)
@@ -296,6 +309,20 @@ extern "C" int llmt_comm_gather_shards(const void* const* shard_ptrs, void* dst_
   const int64_t nvec = shard_bytes / 16;
   gather_shards_kernel<<<grid_for(nvec, 512, 2), 512, 0, stream>>>(shards, (uint4*)dst_full, rank, world, nvec);
   return check_launch("comm_gather_shards");
+}
+
+// dst_full bytes [lo, hi) minus [skip_lo, skip_hi) <- the owners' slices (all offsets in bytes, multiples of 16).
+extern "C" int llmt_comm_gather_range(const void* const* shard_ptrs, void* dst_full, int world, int64_t shard_bytes,
+                                      int64_t lo, int64_t hi, int64_t skip_lo, int64_t skip_hi, cudaStream_t stream) {
+  LLMT_REQUIRE(shard_bytes % 16 == 0 && lo % 16 == 0 && hi % 16 == 0 && skip_lo % 16 == 0 && skip_hi % 16 == 0 &&
+                   (uintptr_t)dst_full % 16 == 0, "gather_range: 16-byte alignment required");
+  LLMT_REQUIRE(lo >= 0 && hi <= shard_bytes * world, "gather_range: range exceeds the unit");
+  Peers shards;
+  if (fill_peers(&shards, shard_ptrs, world)) return 1;
+  if (hi <= lo) return 0;
+  gather_range_kernel<<<grid_for((hi - lo) / 16, 512, 2), 512, 0, stream>>>(
+      shards, (uint4*)dst_full, shard_bytes / 16, lo / 16, hi / 16, skip_lo / 16, skip_hi / 16);
+  return check_launch("comm_gather_range");
 }
 
 extern "C" int llmt_comm_rs_num_partials() { return num_sms() * 2; }

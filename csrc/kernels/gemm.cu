@@ -71,6 +71,10 @@ struct Params {
 //               rank+2, ...), and bump a per-block arrival counter; the TMA producer waits on the counter of a
 //               remote block before its first load.  Every byte crosses NVLink once, the copy hides under the
 //               MMAs of the earlier blocks, and the gathered activation is left behind for the backward pass.
+//            3: "weight gather" (ZeRO-3 parameter all-gather -> first consumer GEMM): B = W[N, K] is a row range of
+//               a unit's flat parameter buffer whose slices live on their owner ranks (symmetric shard arena).
+//               The pull warps land W in the local full buffer n-block by n-block; tiles are walked n-major so
+//               the producer of n-block j only waits for the bytes of block j.
 //   kDistC : the [M, N] result is reduce-scattered by rows; each tile is TMA-reduce-ADDED into the owner rank's
 //            [rows_per_rank, N] buffer (GEMM -> reduce-scatter)
 constexpr int kMaxDistRanks = 8;
@@ -84,6 +88,9 @@ struct DistMaps {
                                       // delivered), zero on entry
   int64_t lda, ld_full;
   int rank, world;
+  // weight gather (kDistA == 3): a_raw[r] = rank r's slice of the unit, a_full = the unit's full buffer;
+  // W starts w_off elements into the flat buffer, every slice holds shard_numel elements
+  int64_t w_off, shard_numel;
 };
 struct NoDist {};
 constexpr int kPullUnroll = 8;                  // 16-byte loads in flight per lane of a pull warp
@@ -103,11 +110,12 @@ __device__ __forceinline__ void tile_coords(int tile, int num_m, int num_n, int&
 }
 
 template <int kCtaGroup, bool kAMn, bool kBMn, typename OutT, int kDistA = 0, bool kDistC = false>
-__global__ void __launch_bounds__((kDistA == 2 ? 2 : 1) * kThreads, 1)
+__global__ void __launch_bounds__((kDistA >= 2 ? 2 : 1) * kThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmC, const __grid_constant__ CUtensorMap tmR, Params p,
                  const __grid_constant__ typename std::conditional<(kDistA != 0 || kDistC), DistMaps, NoDist>::type dist) {
-  static_assert(!(kDistA != 0 && kAMn), "gathered A must be K-major");
+  static_assert(!(kDistA != 0 && kDistA != 3 && kAMn), "gathered A must be K-major");
+  static_assert(!(kDistA == 3 && kBMn), "gathered weights are K-major ([N, K] rows)");
   using C = Cfg<kCtaGroup>;
   constexpr int kOutChunkCols = 128 / (int)sizeof(OutT);  // columns per 128-byte staging row: 64 bf16 / 32 fp32
   constexpr int kNumChunks = BN / kOutChunkCols;
@@ -142,6 +150,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if constexpr (kDistA == 2) {
       tm += p.tm_rot;
       if (tm >= num_m) tm -= num_m;
+    }
+    if constexpr (kDistA == 3) {          // n-major: all m-tiles of weight block 0, then block 1, ... (arrival order)
+      tm = tile % num_m;
+      tn = tile / num_m;
     }
   };
 
@@ -188,7 +200,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int n0 = tn * BN + (int)cta_rank * C::kBRows;
         [[maybe_unused]] const CUtensorMap* mapA = &tmA;
         [[maybe_unused]] int m_local = m0;
-        if constexpr (kDistA != 0) {                   // A tile lives on rank m0 / rows_per_rank
+        if constexpr (kDistA == 3) {
+          // weight rows of this n-block come from the landing buffer once every piece of the block has arrived
+          const int rows_here = min(BN, p.N - tn * BN);
+          const int target = (int)(((int64_t)rows_here * (p.K >> 3) + kPieceVecs - 1) / kPieceVecs);
+          const int* flag = dist.flags + tn;
+          uint32_t spins = 0;
+          while (ld_acquire_gpu_s32(flag) < target) {
+            if (++spins > (1u << 26)) __trap();
+          }
+          fence_proxy_async_all();
+        }
+        if constexpr (kDistA == 1 || kDistA == 2) {    // A tile lives on rank m0 / rows_per_rank
           const int owner = min(m0 / p.rows_per_rank, kMaxDistRanks - 1);
           if (kDistA == 1 || owner == dist.rank) {
             mapA = &dist.a[owner];
@@ -212,7 +235,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int k0 = kb * BK;
           if (kCtaGroup == 1 || is_leader) mbar_arrive_expect_tx(full_bar(stage), C::kStageBytes * kCtaGroup);
           if constexpr (kCtaGroup == 1) {
-            if constexpr (kDistA != 0) tma_load_2d(sa, mapA, fb, k0, m_local);
+            if constexpr (kDistA == 1 || kDistA == 2) tma_load_2d(sa, mapA, fb, k0, m_local);
             else if constexpr (!kAMn) tma_load_2d(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
@@ -224,7 +247,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               for (int j = 0; j < C::kBRows / 64; ++j) tma_load_2d(sb + j * (BK * 128), &tmB, fb, n0 + j * 64, k0);
             }
           } else {
-            if constexpr (kDistA != 0) tma_load_2d_cg2(sa, mapA, fb, k0, m_local);
+            if constexpr (kDistA == 1 || kDistA == 2) tma_load_2d_cg2(sa, mapA, fb, k0, m_local);
             else if constexpr (!kAMn) tma_load_2d_cg2(sa, &tmA, fb, k0, m0);
             else {
 #pragma unroll
@@ -275,6 +298,40 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if constexpr (kCtaGroup == 1) umma_commit(tmem_full_bar(acc));
         else umma_commit_cg2_mcast(tmem_full_bar(acc), 0b11);
         if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (kDistA == 3 && warp >= kThreads / 32) {
+    // ===== pull warps (weight gather): W's flat element range, 4 KB pieces dealt round-robin to every pull warp =====
+    if constexpr (kDistA == 3) {
+      constexpr int kPullWarps = kThreads / 32;
+      const int pw = warp - kThreads / 32;
+      const int64_t gw = (int64_t)blockIdx.x * kPullWarps + pw, GW = (int64_t)gridDim.x * kPullWarps;
+      const int64_t total_vecs = (int64_t)p.N * (p.K >> 3);
+      const int64_t vecs_per_blk = (int64_t)BN * (p.K >> 3);               // multiple of kPieceVecs
+      const int64_t pieces = (total_vecs + kPieceVecs - 1) / kPieceVecs;
+      __nv_bfloat16* full = reinterpret_cast<__nv_bfloat16*>(dist.a_full);
+      for (int64_t piece = gw; piece < pieces; piece += GW) {
+        uint4 r[kPullUnroll];
+        int64_t e[kPullUnroll];
+#pragma unroll
+        for (int u = 0; u < kPullUnroll; ++u) {
+          const int64_t v = piece * kPieceVecs + u * 32 + lane;
+          e[u] = -1;
+          if (v < total_vecs) {
+            e[u] = dist.w_off + (v << 3);                                   // element index in the flat buffer
+            const int64_t owner = e[u] / dist.shard_numel;
+            const int64_t local = e[u] - owner * dist.shard_numel;
+            r[u] = ld_relaxed_sys_16(reinterpret_cast<const __nv_bfloat16*>(dist.a_raw[owner]) + local);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kPullUnroll; ++u)
+          if (e[u] >= 0) *reinterpret_cast<uint4*>(full + e[u]) = r[u];
+        __syncwarp();
+        if (lane == 0) {
+          __threadfence();
+          red_release_gpu_add_s32(dist.flags + (int)((piece * kPieceVecs) / vecs_per_blk), 1);
+        }
       }
     }
   } else if (kDistA == 2 && warp >= kThreads / 32) {
@@ -500,7 +557,7 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
   if (workers > cap) workers = cap;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(workers * kCtaGroup);
-  cfg.blockDim = dim3((kDistA == 2 ? 2 : 1) * kThreads);
+  cfg.blockDim = dim3((kDistA >= 2 ? 2 : 1) * kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -700,4 +757,55 @@ extern "C" int llmt_gemm_bf16_ag(const void* const* a_ptrs, void* a_full, const 
   }
   if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
   return launch<2, false, false, __nv_bfloat16, 2, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+}
+
+// ZeRO-3 parameter all-gather -> first consumer GEMM:  C[M, N] = A[M, K] * W[N, K]^T where W is the element range
+// [w_off, w_off + N*K) of a sharding unit's flat parameter buffer.  shard_ptrs[r] (HOST array) is rank r's slice of
+// that unit in the symmetric shard arena (shard_numel elements each); full_base is the unit's local full buffer,
+// whose W range this kernel fills while it computes.  flags: int32 [ceil(N / 256)], reset here on `stream`.
+// A cross-rank barrier must separate the last write of any slice from this call.
+extern "C" int llmt_gemm_bf16_wgather(const void* A, const void* const* shard_ptrs, void* full_base, int64_t w_off,
+                                      int64_t shard_numel, void* Cout, int* flags, int rank, int world, int M, int N,
+                                      int K, int64_t lda, int64_t ldc, int cta_group, int max_ctas,
+                                      cudaStream_t stream) {
+  LLMT_REQUIRE(world >= 1 && world <= kMaxDistRanks && rank >= 0 && rank < world,
+               "gemm_wgather: rank %d / world %d not supported (max %d ranks)", rank, world, kMaxDistRanks);
+  LLMT_REQUIRE(cta_group == 1 || cta_group == 2, "gemm_wgather: cta_group must be 1 or 2");
+  LLMT_REQUIRE(K % 8 == 0 && lda % 8 == 0 && ldc % 8 == 0 && w_off % 8 == 0 && shard_numel % 8 == 0 && shard_numel > 0,
+               "gemm_wgather: K, leading dimensions, w_off and shard_numel must be multiples of 8");
+  LLMT_REQUIRE(w_off >= 0 && w_off + (int64_t)N * K <= shard_numel * world, "gemm_wgather: W exceeds the unit");
+  LLMT_REQUIRE((uintptr_t)full_base % 16 == 0 && (uintptr_t)A % 16 == 0 && (uintptr_t)Cout % 16 == 0,
+               "gemm_wgather: misaligned buffers");
+  if (max_ctas <= 0) max_ctas = num_sms();
+  if (max_ctas > num_sms()) max_ctas = num_sms();
+  static DistMaps maps;
+  CUtensorMap ta, tb, tc;
+  int rc;
+  const int b_rows = BN / cta_group;
+  void* w_local = reinterpret_cast<__nv_bfloat16*>(full_base) + w_off;
+  rc = make_tmap_2d(&ta, A, 2, M, K, lda, BK, BM);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tb, w_local, 2, N, K, K, BK, b_rows);
+  if (rc) return rc;
+  rc = make_tmap_2d(&tc, Cout, 2, M, N, ldc, 64, BM);
+  if (rc) return rc;
+  for (int r = 0; r < kMaxDistRanks; ++r) {
+    maps.a[r] = ta;
+    maps.c[r] = tc;
+    maps.a_raw[r] = shard_ptrs[r < world ? r : world - 1];
+    LLMT_REQUIRE((uintptr_t)maps.a_raw[r] % 16 == 0, "gemm_wgather: misaligned slice");
+  }
+  maps.a_full = full_base;
+  maps.flags = flags;
+  maps.lda = lda;
+  maps.ld_full = K;
+  maps.rank = rank;
+  maps.world = world;
+  maps.w_off = w_off;
+  maps.shard_numel = shard_numel;
+  cudaError_t e = cudaMemsetAsync(flags, 0, sizeof(int) * (size_t)((N + BN - 1) / BN), stream);
+  LLMT_REQUIRE(e == cudaSuccess, "gemm_wgather: flag reset failed: %s", cudaGetErrorString(e));
+  Params p{M, N, K, 0, 0, 0};
+  if (cta_group == 1) return launch<1, false, false, __nv_bfloat16, 3, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
+  return launch<2, false, false, __nv_bfloat16, 3, false>(ta, tb, tc, tc, p, max_ctas, stream, &maps);
 }

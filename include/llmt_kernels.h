@@ -51,6 +51,16 @@ int llmt_gemm_bf16_ag(const void* const* a_ptrs, void* a_full, const void* B, vo
                       int world, int rows_per_rank, int M, int N, int K, int64_t lda, int64_t ld_full, int64_t ldb,
                       int64_t ldc, int b_mn_major, int cta_group, int max_ctas, cudaStream_t stream);
 
+/* ZeRO-3 parameter all-gather -> first consumer GEMM: C = A * W^T with W = elements [w_off, w_off + N*K) of a
+ * sharding unit's flat parameter buffer whose slices live on their owners (shard_ptrs: HOST array of `world`
+ * pointers into the symmetric shard arena, shard_numel elements each).  Extra warps of the GEMM pull W over NVLink
+ * into full_base + w_off n-block by n-block; tiles are walked n-major and the TMA producer of an n-block waits for
+ * that block's arrival counter (flags: int32 [ceil(N/256)], reset by the call).  Replaces FSDP2's all-gather before
+ * the layer's first linear (src/llm_training/models/llama/llama_model.py:263-268). */
+int llmt_gemm_bf16_wgather(const void* A, const void* const* shard_ptrs, void* full_base, int64_t w_off,
+                           int64_t shard_numel, void* C, int* flags, int rank, int world, int M, int N, int K,
+                           int64_t lda, int64_t ldc, int cta_group, int max_ctas, cudaStream_t stream);
+
 /* ---- NVLink collectives for the sharding engine (csrc/kernels/comm.cu); replace NCCL all-gather /
  *      reduce-scatter issued by FSDP2 / ZeRO (llama_model.py:263-268, deepspeed_strategy.py:39-44) ------------ */
 int llmt_comm_barrier(const void* const* signal_pads, int rank, int world, int slot_base, uint32_t epoch,
@@ -60,6 +70,8 @@ int llmt_comm_allgather_pull(const void* const* full_ptrs, int rank, int world, 
 /* ZeRO-3 parameter gather: full[r * shard_bytes ..] <- rank r's slice, pulled from the symmetric shard arena */
 int llmt_comm_gather_shards(const void* const* shard_ptrs, void* dst_full, int rank, int world, int64_t shard_bytes,
                             cudaStream_t stream);
+int llmt_comm_gather_range(const void* const* shard_ptrs, void* dst_full, int world, int64_t shard_bytes, int64_t lo,
+                           int64_t hi, int64_t skip_lo, int64_t skip_hi, cudaStream_t stream);
 int llmt_comm_rs_num_partials(void);
 int llmt_comm_rs_sumsq(const void* const* grad_ptrs, int rank, int world, int64_t shard_elems, int is_fp32,
                        void* out_shard, float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream);

@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 from .gemm_op import gemm
-from .linear_op import _adjacent_rows_view, _as_2d, linear, multi_linear, wgrad
+from .linear_op import _adjacent_rows_view, _as_2d, complete_lazy_gather, linear, multi_linear, wgrad
 from .rms_norm_op import rms_norm, rmsnorm_bwd_raw, rmsnorm_fwd_raw
 from .swiglu_op import silu_mul_bwd_raw, silu_mul_fused, silu_mul_fwd_raw
 
@@ -28,9 +28,16 @@ class _NormMultiLinearFn(torch.autograd.Function):
         nw = norm_weight if norm_weight.dtype == torch.bfloat16 else norm_weight.to(torch.bfloat16)
         xn, rstd = rmsnorm_fwd_raw(x2, nw, eps)
         fused = _adjacent_rows_view(weights)
-        if fused is None:
-            fused = torch.cat([w.detach() for w in weights], dim=0)
-        y = gemm(xn, fused)
+        lazy = getattr(weights[0], '_llmt_lazy_unit', None)
+        if fused is not None and lazy is not None and lazy[1].head_pending \
+                and lazy[1].head[1] == fused.shape[0] and x2.shape[0] % 128 == 0:
+            # ZeRO-3 on NVLink: this GEMM is the first consumer of the layer's q|k|v rows and gathers them itself
+            y = lazy[0].first_gemm(xn, lazy[1])
+        else:
+            complete_lazy_gather(weights)
+            if fused is None:
+                fused = torch.cat([w.detach() for w in weights], dim=0)
+            y = gemm(xn, fused)
         ctx.save_for_backward(x2, nw, rstd, fused)
         ctx.eps = eps
         ctx.x_shape = x.shape
@@ -59,7 +66,7 @@ def norm_multi_linear(x: torch.Tensor, norm_weight: torch.Tensor, eps: float, we
     if (_lib.use_kernels(x) and all(w.dtype == torch.bfloat16 for w in weights) and x.shape[-1] % 8 == 0
             and x.shape[-1] <= 16384):
         return _NormMultiLinearFn.apply(x, norm_weight, eps, *weights)
-    return multi_linear(rms_norm(x, norm_weight, eps), weights)
+    return multi_linear(rms_norm(x, norm_weight, eps), weights)     # completes a pending lazy gather itself
 
 
 class _SwiGLUDownFn(torch.autograd.Function):

@@ -19,6 +19,15 @@ def _as_2d(t: torch.Tensor) -> torch.Tensor:
     return t2
 
 
+def complete_lazy_gather(weights) -> None:
+    """ZeRO-3 on NVLink leaves a layer's q|k|v rows to be gathered by the GEMM that consumes them
+    (``FlatParamEngine.first_gemm``); any other consumer calls this first."""
+    for w in weights:
+        lazy = getattr(w, '_llmt_lazy_unit', None)
+        if lazy is not None and lazy[1].head_pending:
+            lazy[0].complete_head(lazy[1])
+
+
 def wgrad(dy2: torch.Tensor, x2: torch.Tensor, weights: tuple[torch.Tensor, ...]) -> list:
     """dW_i = dY_i^T X for row-stacked weights.  When the sharding engine has given every weight a gradient view
     inside its flat buffer and marked it ``_llmt_direct_grad`` (weights used once per step), the GEMM epilogue
@@ -65,6 +74,7 @@ class _LinearFn(torch.autograd.Function):
 
 def linear(x: torch.Tensor, weight: torch.Tensor, bias: torch.Tensor | None = None,
            residual: torch.Tensor | None = None) -> torch.Tensor:
+    complete_lazy_gather((weight,))
     if _lib.use_kernels(x) and weight.dtype == torch.bfloat16 and x.shape[-1] % 8 == 0 and weight.shape[0] % 8 == 0:
         y = _LinearFn.apply(x, weight, residual)
         if bias is not None:
@@ -122,6 +132,7 @@ class _MultiLinearFn(torch.autograd.Function):
 def multi_linear(x: torch.Tensor, weights: list[torch.Tensor], biases: list[torch.Tensor | None] | None = None
                  ) -> torch.Tensor:
     """``concat_i(x @ W_i^T (+ b_i))`` along the last dim, computed as a single GEMM on CUDA."""
+    complete_lazy_gather(weights)
     if _lib.use_kernels(x) and all(w.dtype == torch.bfloat16 for w in weights) and x.shape[-1] % 8 == 0:
         y = _MultiLinearFn.apply(x, *weights)
     else:

@@ -86,6 +86,10 @@ class ShardedUnit:
         self.in_backward = False
         self.gather_event: Any = None
         self.gather_pending = False
+        # ZeRO-3 on NVLink: (element offset, rows, cols) of the row-stacked weights the unit's FIRST GEMM consumes
+        # (q|k|v); in forward that GEMM gathers them itself, the side-stream gather covers the rest of the unit
+        self.head: tuple[int, int, int] | None = None
+        self.head_pending = False
 
     @property
     def param_shard(self) -> torch.Tensor:
@@ -168,6 +172,8 @@ class FlatParamEngine:
                 self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype))
         # `nvlink` = parameters travel through our kernels; `nvlink_grads` = gradients do too (resident mode only)
         self.nvlink_grads = self.nvlink and not self.reshard
+        import os
+        self.fused_first_gemm = os.environ.get('LLMT_FUSED_FIRST_GEMM', '1') != '0'
         self._forward_order: list[ShardedUnit] = []      # hooked units in the order the last forward used them
         self._norm_accumulating = False
         self.require_sync = True
@@ -334,12 +340,66 @@ class FlatParamEngine:
         model.register_forward_pre_hook(root_hook)
 
     # ------------------------------------------------------------------ ZeRO-3: gather before use, drop after use
-    def unshard(self, u: ShardedUnit) -> None:
-        """Give ``flat_param`` storage and start gathering every rank's slice into it on the side stream."""
+    def enable_fused_first_gemm(self, model: nn.Module) -> None:
+        """ZeRO-3 + NVLink: let the first GEMM of every decoder layer (q|k|v projection) pull its own weights from
+        the owners' slices while it runs (``NVLinkComm.gemm_weight_gather``) instead of waiting for a gather."""
+        if self.shard_arena is None or not hasattr(model, 'sharding_units'):
+            return
+        for _, module in model.sharding_units():
+            attn = getattr(module, 'self_attn', None)
+            if attn is None:
+                continue
+            if all(hasattr(attn, n) for n in ('q_proj', 'k_proj', 'v_proj')):
+                ws = [attn.q_proj.weight, attn.k_proj.weight, attn.v_proj.weight]
+            elif hasattr(attn, 'qkv_proj'):
+                ws = [attn.qkv_proj.weight]
+            else:
+                continue
+            u = self._param_to_unit.get(id(ws[0]))
+            if u is None or any(self._param_to_unit.get(id(w)) is not u for w in ws):
+                continue
+            offs = {id(p): o for (_, p), o in zip(u.params, u.offsets)}
+            k = ws[0].shape[1]
+            ok, expect = True, offs[id(ws[0])]
+            for w in ws:
+                ok &= w.dim() == 2 and w.shape[1] == k and w.dtype == torch.bfloat16 and offs[id(w)] == expect
+                expect += w.numel()
+            if not ok or k % 8:
+                continue
+            u.head = (offs[id(ws[0])], sum(w.shape[0] for w in ws), k)
+            for w in ws:
+                w._llmt_lazy_unit = (self, u)
+        n_max = max((u.head[1] for u in self.units if u.head is not None), default=0)
+        if n_max:
+            self._head_flags = torch.zeros(n_max // 256 + 2, dtype=torch.int32, device=self.device)
+
+    def first_gemm(self, x: torch.Tensor, u: ShardedUnit) -> torch.Tensor:
+        """``x @ head(u)^T`` while the head weights are gathered by the GEMM itself."""
+        off, n, _ = u.head
+        esize = u.flat_param.element_size()
+        y = self.comm.gemm_weight_gather(x, self.shard_arena, u.arena_offset * esize, u.flat_param, off,
+                                         u.shard_numel, n, self._head_flags)
+        u.head_pending = False
+        return y
+
+    def complete_head(self, u: ShardedUnit) -> None:
+        """Some other consumer needs the head weights first: gather them now on the current stream."""
+        if u.head_pending:
+            off, n, k = u.head
+            esize = u.flat_param.element_size()
+            self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
+                                   off * esize, (off + n * k) * esize, barrier=False)
+            u.head_pending = False
+
+    def unshard(self, u: ShardedUnit, lazy_head: bool = False) -> None:
+        """Give ``flat_param`` storage and start gathering every rank's slice into it on the side stream.  With
+        ``lazy_head`` (forward pass) the q|k|v rows are left to the GEMM that consumes them."""
         if not u.is_sharded:
             return
         u._set_storage(u.flat_param, True)
         u.is_sharded = False
+        u.head_pending = bool(lazy_head and u.head is not None and self._comm_stream is not None
+                              and self.fused_first_gemm)
         main = torch.cuda.current_stream(self.device) if self._comm_stream is not None else None
         if self._comm_stream is not None:
             self._comm_stream.wait_stream(main)        # the slice may have just been written by the optimizer
@@ -355,31 +415,40 @@ class FlatParamEngine:
     def _gather_into_full(self, u: ShardedUnit) -> None:
         if self.shard_arena is not None:
             esize = u.flat_param.element_size()
+            if u.head_pending:
+                off, n, k = u.head
+                self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
+                                       0, u.padded_numel * esize, off * esize, (off + n * k) * esize)
+                return
             self.comm.gather_shards(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param)
         else:
             self.comm.all_gather_into(u.flat_param, u.param_shard)
 
-    def wait_unshard(self, u: ShardedUnit) -> None:
+    def wait_unshard(self, u: ShardedUnit, keep_lazy_head: bool = False) -> None:
         if u.gather_pending:
             torch.cuda.current_stream(self.device).wait_event(u.gather_event)
             u.gather_pending = False
+        if u.head_pending and not keep_lazy_head:
+            self.complete_head(u)
 
     def reshard_unit(self, u: ShardedUnit) -> None:
         if u.is_sharded or not self.reshard:
             return
-        self.wait_unshard(u)              # never free under an in-flight gather
+        self.wait_unshard(u, keep_lazy_head=True)     # never free under an in-flight gather
+        u.head_pending = False
         u._set_storage(u.flat_param, False)
         u.is_sharded = True
 
     def _pre_forward(self, u: ShardedUnit) -> None:
-        self.unshard(u)
-        self.wait_unshard(u)
-        if not u.in_backward:
+        fwd = not u.in_backward
+        self.unshard(u, lazy_head=fwd)
+        self.wait_unshard(u, keep_lazy_head=fwd)      # the q|k|v GEMM finishes the gather itself
+        if fwd:
             if u not in self._forward_order:
                 self._forward_order.append(u)
             nxt = self._next_in_order(u, +1)
             if nxt is not None:
-                self.unshard(nxt)         # prefetch: its gather runs under this unit's compute
+                self.unshard(nxt, lazy_head=True)     # prefetch: its gather runs under this unit's compute
 
     def _next_in_order(self, u: ShardedUnit, step: int) -> ShardedUnit | None:
         order = self._last_forward_order if getattr(self, '_last_forward_order', None) else None
@@ -627,6 +696,8 @@ def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_afte
                              reshard=_resolve_reshard(reshard_after_forward, units, dp_mesh, device))
     model._flat_engine = engine
     engine.attach_module_hooks(model)
+    if engine.reshard:
+        engine.enable_fused_first_gemm(model)
     if offload_policy is not None and getattr(offload_policy, 'pin_memory', None) is not None \
             and type(offload_policy).__name__ == 'CPUOffloadPolicy':
         logger.warning('CPU offload requested: not needed at 180 GB/GPU, parameters stay on device')

@@ -114,6 +114,30 @@ class NVLinkComm(Comm):
                                                      _lib.c_int(self.rank), _lib.c_int(self.size),
                                                      _lib.c_i64(shard_bytes), _lib.stream()), 'comm_gather_shards')
 
+    def gather_range(self, arena: SymmetricBuffer, byte_offset: int, shard_bytes: int, full: torch.Tensor,
+                     lo: int, hi: int, skip_lo: int = 0, skip_hi: int = 0, barrier: bool = True) -> None:
+        """Like ``gather_shards`` for the byte range [lo, hi) of the unit minus [skip_lo, skip_hi)."""
+        if barrier:
+            self.barrier()
+        _lib.check(self._lib.llmt_comm_gather_range(arena.peer_ptrs_at(byte_offset), _lib.ptr(full),
+                                                    _lib.c_int(self.size), _lib.c_i64(shard_bytes), _lib.c_i64(lo),
+                                                    _lib.c_i64(hi), _lib.c_i64(skip_lo), _lib.c_i64(skip_hi),
+                                                    _lib.stream()), 'comm_gather_range')
+
+    def gemm_weight_gather(self, x: torch.Tensor, arena: SymmetricBuffer, byte_offset: int, full: torch.Tensor,
+                           w_off: int, shard_numel: int, n: int, flags: torch.Tensor) -> torch.Tensor:
+        """``x @ W^T`` where W = elements [w_off, w_off + n*k) of the unit: the GEMM's pull warps land W in ``full``
+        while the tensor cores work (csrc/kernels/gemm.cu, kDistA == 3).  No barrier here: the caller has already
+        waited for one that follows the last write of every slice."""
+        m, k = x.shape
+        y = torch.empty((m, n), dtype=x.dtype, device=x.device)
+        _lib.check(self._lib.llmt_gemm_bf16_wgather(
+            _lib.ptr(x), arena.peer_ptrs_at(byte_offset), _lib.ptr(full), _lib.c_i64(w_off), _lib.c_i64(shard_numel),
+            _lib.ptr(y), _lib.ptr(flags), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_int(m), _lib.c_int(n),
+            _lib.c_int(k), _lib.c_i64(x.stride(0)), _lib.c_i64(n), _lib.c_int(2), _lib.c_int(0), _lib.stream()),
+            'gemm_bf16_wgather')
+        return y
+
     def reduce_scatter_sumsq(self, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, out_shard: torch.Tensor,
                              norm_sq: torch.Tensor, accumulate_norm: bool) -> None:
         self.barrier()                                           # every rank finished writing this unit's grads
