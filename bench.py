@@ -30,6 +30,10 @@ MODELS = {
     'llama-3-8b': dict(vocab_size=128256, hidden_size=4096, intermediate_size=14336, num_hidden_layers=32,
                        num_attention_heads=32, num_key_value_heads=8, max_position_embeddings=8192,
                        rope_theta=500000.0, rms_norm_eps=1e-5, bos_token_id=128000, eos_token_id=128001),
+    # BASELINE config 5 (run with --tp 8 --recompute full|selective)
+    'llama-3.1-70b': dict(vocab_size=128256, hidden_size=8192, intermediate_size=28672, num_hidden_layers=80,
+                          num_attention_heads=64, num_key_value_heads=8, max_position_embeddings=131072,
+                          rope_theta=500000.0, rms_norm_eps=1e-5, bos_token_id=128000, eos_token_id=128001),
     # for smoke runs on small memory / CPU
     'llama-tiny': dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
                        num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=8192),
