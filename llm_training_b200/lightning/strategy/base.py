@@ -286,7 +286,9 @@ class Strategy:
 
     # ---------------------------------------------------------------- checkpoint I/O (see checkpoint_io.py)
     save_distributed_checkpoint: bool = False
-    overlap_optimizer_step: bool = os.environ.get('LLMT_OVERLAP_OPT', '1') != '0'
+    # measured on 1, 2 and 8 B200s (profiles/bench_8gpu*_r1_final.log): no gain beyond noise, the step is power /
+    # HBM bound and the push is already short; available with LLMT_OVERLAP_OPT=1 or by setting the attribute
+    overlap_optimizer_step: bool = os.environ.get('LLMT_OVERLAP_OPT', '0') == '1'
 
     def save_checkpoint(self, checkpoint: dict[str, Any], filepath: str) -> None:
         from ..checkpoint_io import save_checkpoint
