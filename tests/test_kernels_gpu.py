@@ -392,3 +392,98 @@ def test_overlapped_optimizer_step_is_bit_identical():
     assert results[0][0] == results[1][0], (results[0][0], results[1][0])
     for a, b in zip(results[0][1], results[1][1]):
         assert torch.equal(a, b)
+
+
+# ---------------------------------------------------------------------------------------------------
+# fused compute + collective GEMMs, emulated on ONE GPU: the "peers" are separate buffers of the same device and
+# every rank's launch is issued in turn.  Each launch only READS its peers (arrival counters are intra-kernel), so
+# nothing waits on another launch; the multi-GPU versions of these checks are in tests/test_multi_gpu.py.
+# ---------------------------------------------------------------------------------------------------
+def _ptr_array(tensors):
+    import ctypes
+    return (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+@pytest.mark.parametrize('cta_group,rows,k,n,b_mn', [(2, 512, 512, 768, False), (1, 384, 256, 320, False),
+                                                     (2, 256, 384, 512, True)])
+def test_all_gather_gemm_land_once_emulated_ranks(cta_group, rows, k, n, b_mn):
+    from llm_training_b200.ops import _lib
+    world = 4
+    g = torch.Generator(device=DEV).manual_seed(3)
+    blocks = [torch.randn(rows, k, device=DEV, generator=g).bfloat16() for _ in range(world)]
+    w = (torch.randn((k, n) if b_mn else (n, k), device=DEV, generator=g) * 0.05).bfloat16()
+    full = torch.cat(blocks)
+    want = full.float() @ (w.float() if b_mn else w.float().t())
+    flags = torch.zeros(64, dtype=torch.int32, device=DEV)
+    for rank in range(world):
+        landed = torch.zeros_like(full)
+        out = torch.empty(rows * world, n, dtype=torch.bfloat16, device=DEV)
+        _lib.check(_lib.lib().llmt_gemm_bf16_ag(
+            _ptr_array(blocks), _lib.ptr(landed), _lib.ptr(w), _lib.ptr(out), _lib.ptr(flags), _lib.c_int(rank),
+            _lib.c_int(world), _lib.c_int(rows), _lib.c_int(rows * world), _lib.c_int(n), _lib.c_int(k), _lib.c_i64(k),
+            _lib.c_i64(k), _lib.c_i64(w.stride(0)), _lib.c_i64(n), _lib.c_int(b_mn), _lib.c_int(cta_group),
+            _lib.c_int(0), _lib.stream()), 'gemm_bf16_ag')
+        assert torch.equal(landed, full), f'rank {rank}: gathered operand differs'
+        _close(out, want)
+
+
+def test_weight_gather_gemm_emulated_ranks():
+    """ZeRO-3 first-consumer GEMM: W is a row range of a flat unit whose slices sit in four separate buffers."""
+    from llm_training_b200.ops import _lib
+    world, n, k, m, w_off = 4, 1280, 512, 768, 4096 + 8
+    g = torch.Generator(device=DEV).manual_seed(5)
+    unit_numel = w_off + n * k + 1000
+    shard_numel = -(-unit_numel // (8 * world)) * 8
+    flat = torch.zeros(shard_numel * world, dtype=torch.bfloat16, device=DEV)
+    flat[:unit_numel] = (torch.randn(unit_numel, device=DEV, generator=g) * 0.05).bfloat16()
+    shards = [flat[r * shard_numel:(r + 1) * shard_numel].clone() for r in range(world)]
+    x = torch.randn(m, k, device=DEV, generator=g).bfloat16()
+    w = flat[w_off:w_off + n * k].view(n, k)
+    want = x.float() @ w.float().t()
+    flags = torch.zeros(64, dtype=torch.int32, device=DEV)
+    for rank in range(world):
+        full = torch.zeros_like(flat)
+        y = torch.empty(m, n, dtype=torch.bfloat16, device=DEV)
+        _lib.check(_lib.lib().llmt_gemm_bf16_wgather(
+            _lib.ptr(x), _ptr_array(shards), _lib.ptr(full), _lib.c_i64(w_off), _lib.c_i64(shard_numel), _lib.ptr(y),
+            _lib.ptr(flags), _lib.c_int(rank), _lib.c_int(world), _lib.c_int(m), _lib.c_int(n), _lib.c_int(k),
+            _lib.c_i64(k), _lib.c_i64(n), _lib.c_int(2), _lib.c_int(0), _lib.stream()), 'gemm_bf16_wgather')
+        assert torch.equal(full[w_off:w_off + n * k], flat[w_off:w_off + n * k]), 'landed weights differ'
+        assert float(full[:w_off].abs().max()) == 0 and float(full[w_off + n * k:].abs().max()) == 0
+        _close(y, want)
+    # the side-stream range gather fills everything EXCEPT the head the GEMM pulled
+    full = torch.zeros_like(flat)
+    lo, hi = w_off * 2, (w_off + n * k) * 2
+    _lib.check(_lib.lib().llmt_comm_gather_range(_ptr_array(shards), _lib.ptr(full), _lib.c_int(world),
+                                                 _lib.c_i64(shard_numel * 2), _lib.c_i64(0),
+                                                 _lib.c_i64(flat.numel() * 2), _lib.c_i64(lo), _lib.c_i64(hi),
+                                                 _lib.stream()), 'gather_range')
+    expect = flat.clone()
+    expect[w_off:w_off + n * k] = 0
+    assert torch.equal(full, expect)
+    full.zero_()
+    _lib.check(_lib.lib().llmt_comm_gather_shards(_ptr_array(shards), _lib.ptr(full), _lib.c_int(1), _lib.c_int(world),
+                                                  _lib.c_i64(shard_numel * 2), _lib.stream()), 'gather_shards')
+    assert torch.equal(full, flat)
+
+
+def test_gemm_reduce_scatter_emulated_ranks():
+    """Row-parallel GEMM -> reduce-scatter: every rank's launch TMA-reduce-adds its tiles into the owners' buffers."""
+    import ctypes
+    from llm_training_b200.ops import _lib
+    world, rows, n, k = 4, 256, 512, 384
+    g = torch.Generator(device=DEV).manual_seed(9)
+    xs = [torch.randn(rows * world, k, device=DEV, generator=g).bfloat16() * 0.5 for _ in range(world)]
+    ws = [(torch.randn(n, k, device=DEV, generator=g) * 0.05).bfloat16() for _ in range(world)]
+    residual = [torch.randn(rows, n, device=DEV, generator=g).bfloat16() for _ in range(world)]
+    targets = [r.clone() for r in residual]
+    null = (ctypes.c_void_p * 1)(0)
+    for rank in range(world):
+        _lib.check(_lib.lib().llmt_gemm_bf16_dist(
+            _lib.c_int(2), _lib.ptr(xs[rank]), null, _lib.ptr(ws[rank]), _lib.ptr(None), _ptr_array(targets),
+            _lib.c_int(world), _lib.c_int(rows), _lib.c_int(rows * world), _lib.c_int(n), _lib.c_int(k), _lib.c_i64(k),
+            _lib.c_i64(k), _lib.c_i64(n), _lib.c_int(0), _lib.c_int(2), _lib.c_int(0), _lib.stream()),
+            'gemm_bf16_dist')
+    total = sum(x.float() @ w.float().t() for x, w in zip(xs, ws))
+    for r in range(world):
+        _close(targets[r], residual[r].float() + total[r * rows:(r + 1) * rows], rtol=3e-2, atol=6e-2)
