@@ -132,7 +132,7 @@ class Strategy:
         self.mesh = init_mesh(dp, tp, self.world_size, self.global_rank)
 
     # ---------------------------------------------------------------- model + optimizers
-    reshard_after_forward: bool | int = True
+    reshard_after_forward: bool | int | str = 'auto'
     use_master_weights: bool = True
 
     @property
@@ -193,7 +193,8 @@ class Strategy:
                 continue
             engine = getattr(model, '_flat_engine', None)
             if engine is None:
-                engine = apply_fully_sharded(model, self.dp_mesh, device=self.root_device)
+                engine = apply_fully_sharded(model, self.dp_mesh, device=self.root_device,
+                                             reshard_after_forward=self.reshard_after_forward)
             engines.append(engine)
         claimed = {id(p) for e in engines for u in e.units for _, p in u.params}
         rest = [(n, p) for n, p in module.named_parameters() if p.requires_grad and id(p) not in claimed]

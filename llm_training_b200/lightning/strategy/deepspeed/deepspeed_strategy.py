@@ -4,10 +4,11 @@ The reference wraps Lightning's DeepSpeed strategy (src/llm_training/lightning/s
 deepspeed_strategy.py:16-156); six of its eight example configs use ``stage: 2``.  DeepSpeed is not a
 dependency here — the constructor accepts the same arguments and maps them onto the flat-parameter engine:
 
-  stage 0/1/2/3 -> optimizer state and fp32 master weights sharded over all ranks (ZeRO-1), gradients
-                   reduce-scattered per unit during backward (ZeRO-2), bf16 parameters all-gathered in place
-                   after the step; at 180 GB/GPU parameters stay resident, so stage 3's parameter partitioning
-                   is a memory option, not a different code path
+  stage 0/1/2   -> optimizer state and fp32 master weights sharded over all ranks (ZeRO-1), gradients
+                   reduce-scattered per unit during backward (ZeRO-2), bf16 parameters resident and refreshed in
+                   place by the optimizer kernel after the step
+  stage 3       -> the engine's resharding mode (``reshard_after_forward=True``): parameters and gradients exist
+                   whole only around a unit's forward / backward (parallel/fsdp.py)
   offload_* / nvme / bucket sizes / hpZ / quantised comm -> accepted, not needed on this hardware (logged)
   loss scaling knobs -> fp16 GradScaler configuration
 """
@@ -47,6 +48,7 @@ class DeepSpeedStrategy(Strategy):
         if stage not in (0, 1, 2, 3):
             raise ValueError(f'ZeRO stage must be 0..3, got {stage}')
         self.stage = stage
+        self.reshard_after_forward = True if stage == 3 else False
         self.zero_optimization = zero_optimization
         self.exclude_frozen_parameters = exclude_frozen_parameters
         self.raise_error_at_min_scale = raise_error_at_min_scale
