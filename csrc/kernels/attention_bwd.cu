@@ -12,7 +12,16 @@
 //   dV  += P^T  dO          (M=128 kv, N=D,     K=64 q) A=P^T  K-major, B=dO MN-major
 //   dK  += dS^T Q           (M=128 kv, N=D,     K=64 q) A=dS^T K-major, B=Q  MN-major
 //   dQ^T = K^T dS^T         (M=D,      N=64 q,  K=128)  A=K  MN-major,  B=dS^T MN-major   -> red.add to dq_acc
-// TMEM: S^T @0 (64) | dP^T @64 (64) | dQ^T @128 (64) | dK @256 (128) | dV @384 (128)  = 512 columns, 1 CTA / SM.
+// Eight compute warps: warp w owns TMEM lanes / kv rows 32*(w%4)..+32 and the q-column half w/4 of every 64-column
+// step, so each SM sub-partition interleaves two warps' exp2 / convert / smem-store streams (one warp per scheduler
+// left the MUFU and TMEM-load latencies exposed: 25% tensor-pipe activity in ncu).
+// TMEM: S^T @0 (64) | dP^T @64 (64) | dQ^T @128, @192 (2 x 64, double-buffered so its drain runs under the next
+// step's MMAs) | dK @256 (128) | dV @384 (128)  = 512 columns, 1 CTA / SM.
+// Measured (B200, 8192 tokens, 32/8 heads, d=128): 2.22 ms per backward = 2.05x flash-attn 2.8.  Switching off the
+// dQ reduce or the exp2 does not move the time: per 128x64 step the five MMAs read 213 KB of operands from shared
+// memory and the P^T / dS^T / dQ staging / TMA traffic adds ~128 KB, i.e. ~2700 cycles at 128 B/clk against a
+// 1280-cycle tensor floor — the kernel is shared-memory-bandwidth bound (next step: P^T as a TMEM A-operand,
+// 128-column q steps).
 // The head dimension is always padded to 128 here (TMA zero-fills the out-of-range columns).
 #include <cuda.h>
 
@@ -31,7 +40,9 @@ int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, int64_t rows, int64_t co
 constexpr int kBwdKV = 128;   // kv rows per CTA
 constexpr int kBwdQ = 64;     // q rows per step
 constexpr int kBwdD = 128;    // padded head dim
-constexpr int kBwdThreads = 192;
+constexpr int kBwdThreads = 320;   // 8 compute warps (2 per TMEM lane quarter: q columns 0-31 / 32-63) + MMA + TMA
+constexpr int kBwdComputeThreads = 256;
+constexpr int kBwdMmaWarp = 8, kBwdTmaWarp = 9;
 
 struct BwdCfg {
   static constexpr int kKBytes = kBwdKV * kBwdD * 2;        // 32 KB : 2 boxes [128][64]
@@ -48,10 +59,10 @@ struct BwdCfg {
   static constexpr int kMetaOff = kDQOff + kDQBytes;        // 3 x {L[64], delta[64], seg_start[64]}
   static constexpr int kMetaBytes = 3 * 3 * 64 * 4;      // 3-deep ring
   static constexpr int kBarOff = kMetaOff + kMetaBytes;
-  // kv_full, qdo_full[2], qdo_empty[2], st_full, st_empty, pds_full, pds_empty, dq_full, dq_empty, acc_done
-  static constexpr int kNumBars = 12;
+  // kv_full, qdo_full[2], qdo_empty[2], st_full, st_empty, pds_full, pds_empty, dq_full[2], dq_empty[2], acc_done
+  static constexpr int kNumBars = 14;
   static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
-  static constexpr int kColST = 0, kColDPT = 64, kColDQT = 128, kColDK = 256, kColDV = 384;
+  static constexpr int kColST = 0, kColDPT = 64, kColDQT = 128 /* two buffers: 128, 192 */, kColDK = 256, kColDV = 384;
 };
 
 struct BwdParams {
@@ -129,10 +140,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
   auto qdo_empty = [&](int s) { return bars + 8u * (3 + s); };
   const uint32_t st_full = bars + 8u * 5, st_empty = bars + 8u * 6;
   const uint32_t pds_full = bars + 8u * 7, pds_empty = bars + 8u * 8;
-  const uint32_t dq_full = bars + 8u * 9, dq_empty = bars + 8u * 10;
-  const uint32_t acc_done = bars + 8u * 11;
-  const uint32_t tmem_ptr_smem = bars + 8u * 12;
-  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 12);
+  auto dq_full = [&](int b) { return bars + 8u * (9 + b); };
+  auto dq_empty = [&](int b) { return bars + 8u * (11 + b); };
+  const uint32_t acc_done = bars + 8u * 13;
+  const uint32_t tmem_ptr_smem = bars + 8u * 14;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // launch order = longest job first: blockIdx.x (fast axis) walks the kv heads, blockIdx.y the kv tiles, so the
@@ -149,22 +161,24 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
   const int nq = q_hi / kBwdQ - i_lo + 1;
   const int n_total = G * nq;
 
-  if (warp == 4 && lane == 0) {
+  if (warp == kBwdMmaWarp && lane == 0) {
     mbar_init(kv_full, 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(qdo_full(s), 1);
       mbar_init(qdo_empty(s), 1);
     }
     mbar_init(st_full, 1);
-    mbar_init(st_empty, 128);
-    mbar_init(pds_full, 128);
+    mbar_init(st_empty, kBwdComputeThreads);
+    mbar_init(pds_full, kBwdComputeThreads);
     mbar_init(pds_empty, 1);
-    mbar_init(dq_full, 1);
-    mbar_init(dq_empty, 128);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(dq_full(b), 1);
+      mbar_init(dq_empty(b), kBwdComputeThreads);
+    }
     mbar_init(acc_done, 1);
     fence_barrier_init();
   }
-  if (warp == 5) {
+  if (warp == kBwdTmaWarp) {
     if (lane == 0) {
       tma_prefetch_desc(&tmKV);
       tma_prefetch_desc(&tmQ);
@@ -180,7 +194,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_gen;
 
-  if (warp == 5) {
+  if (warp == kBwdTmaWarp) {
     // ===== TMA producer =====
     if (lane == 0) {
       mbar_arrive_expect_tx(kv_full, 2 * C::kKBytes);
@@ -202,7 +216,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
         }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == kBwdMmaWarp) {
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc_st = make_idesc_bf16(kBwdKV, kBwdQ, false, false);   // S^T, dP^T
@@ -241,7 +255,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
           issue_st(it + 1);
         }
         mbar_wait(pds_full, it & 1);
-        mbar_wait(dq_empty, (it & 1) ^ 1);
+        mbar_wait(dq_empty(it & 1), ((it >> 1) & 1) ^ 1);   // dQ^T(it-2) has left this TMEM buffer
         tc_fence_after();
         const int st = it & 1;
         const uint32_t qa = sbase + C::kQOff + st * C::kQBytes, doa = sbase + C::kDOOff + st * C::kQBytes;
@@ -257,20 +271,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
         }
 #pragma unroll
         for (int kk = 0; kk < kBwdKV / 16; ++kk) {  // dQ^T = K^T dS^T
-          umma_f16<1>(tmem_base + C::kColDQT, make_smem_desc(ka + kk * 2048, kBwdKV * 128, 1024),
+          umma_f16<1>(tmem_base + C::kColDQT + (it & 1) * 64, make_smem_desc(ka + kk * 2048, kBwdKV * 128, 1024),
                       make_smem_desc(dsa + kk * 2048, kBwdKV * 128, 1024), idesc_dq, kk != 0);
         }
         umma_commit(qdo_empty(st));
         umma_commit(pds_empty);
-        umma_commit(dq_full);
+        umma_commit(dq_full(it & 1));
       }
       umma_commit(acc_done);
     }
   } else {
-    // ===== compute warps: thread <-> kv row =====
-    const int r = warp * 32 + lane;
+    // ===== compute warps: thread <-> kv row r, q-column half hf =====
+    const int r = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const int c_base = hf * 32;                          // first q column of this thread's half
     const int kvi = k0 + r;
-    const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
+    const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     uint8_t* p_row = smem + C::kPOff + r * 128;
     uint8_t* ds_row = smem + C::kDSOff + r * 128;
 
@@ -279,6 +295,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
     auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 192; };
     float pre0 = 0.f, pre1 = 0.f;                       // prefetched values (r < 64: L, delta; r >= 64: seg_start)
     auto meta_fetch = [&](int it) {
+      if (hf != 0) return;                               // warps 0-3 fetch for everybody
       const int h = g * G + it / nq;
       const int q = (i_lo + it % nq) * kBwdQ + (r & 63);
       const bool ok = q < p.tokens;
@@ -290,12 +307,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       }
     };
     auto meta_store = [&](int it) {
+      if (hf != 0) return;
       float* m = meta(it);
       if (r < 64) { m[r] = pre0; m[64 + r] = pre1; }
       else        { m[128 + (r - 64)] = pre0; }
     };
     // P^T of step `it` from S^T in TMEM -> registers (fp32 bit patterns in sv)
-    uint32_t sv[64];
+    uint32_t sv[32];
     auto compute_p = [&](int it) {
       const int q0 = (i_lo + it % nq) * kBwdQ;
       const float* mL = meta(it);
@@ -303,22 +321,45 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       const bool need_mask = (q0 < k0 + kBwdKV - 1) || (mS[63] > k0) || (p.window > 0);
       mbar_wait(st_full, it & 1);
       tc_fence_after();
-      {
-        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[0]);
-        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&sv[32]);
-        tmem_ld_32x32b_x32(t_lane + C::kColST, a);
-        tmem_ld_32x32b_x32(t_lane + C::kColST + 32, b);
-      }
+      tmem_ld_32x32b_x32(t_lane + C::kColST + c_base, sv);
       tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < 64; ++c) {
-        float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c]));
+      for (int c = 0; c < 32; ++c) {
+        float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c_base + c]));
         if (need_mask) {
-          const int q = q0 + c;
-          const bool valid = (mS[c] <= kvi) && (kvi <= q) && (p.window == 0 || q - kvi < p.window);
+          const int q = q0 + c_base + c;
+          const bool valid = (mS[c_base + c] <= kvi) && (kvi <= q) && (p.window == 0 || q - kvi < p.window);
           pv = valid ? pv : 0.f;
         }
         sv[c] = __float_as_uint(pv);
+      }
+    };
+
+    auto drain_dq = [&](int j, int meta_it) {
+      uint32_t dq[32];
+      if (j >= 0) {
+        mbar_wait(dq_full(j & 1), (j >> 1) & 1);
+        tc_fence_after();
+        tmem_ld_32x32b_x32(t_lane + C::kColDQT + (j & 1) * 64 + c_base, dq);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(dq_empty(j & 1));
+        if (threadIdx.x == 0) tma_store_wait_read<0>();   // previous reduce has finished reading the staging tile
+      }
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (j >= 0) {
+        float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) stage[(c_base + c) * kBwdD + r] = __uint_as_float(dq[c]);
+      }
+      if (meta_it < n_total) meta_store(meta_it);         // ring slot meta_it % 3 was last read two steps ago
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 2, 256;" ::: "memory");      // also publishes the metadata stored above
+      if (j >= 0 && threadIdx.x == 0) {
+        const int hj = g * G + j / nq;
+        const int qj = (i_lo + j % nq) * kBwdQ;
+        tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, hj * p.head_dim, qj);
+        tma_store_commit();
       }
     };
 
@@ -326,7 +367,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
     meta_fetch(0);
     meta_store(0);
     if (n_total > 1) { meta_fetch(1); meta_store(1); }
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     compute_p(0);
 
     for (int it = 0; it < n_total; ++it) {
@@ -338,73 +379,48 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       // ---- P^T(it) (registers) -> smem, dS^T(it) from dP^T -> smem
       mbar_wait(pds_empty, (it & 1) ^ 1);                 // dV/dK/dQ MMAs of the previous step have read the tiles
 #pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
+      for (int ch = 0; ch < 4; ++ch) {
         float f[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(sv[ch * 8 + e]);
-        *reinterpret_cast<bf16x8*>(p_row + ((ch ^ (r & 7)) << 4)) = pack8(f);
+        *reinterpret_cast<bf16x8*>(p_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) = pack8(f);
       }
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
+      {
         uint32_t dp[32];
-        tmem_ld_32x32b_x32(t_lane + C::kColDPT + half * 32, dp);
+        tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
         tmem_ld_wait();
-        if (half == 1) {
-          tc_fence_before();
-          mbar_arrive(st_empty);                          // S^T and dP^T of this step are fully in registers
-        }
+        tc_fence_before();
+        mbar_arrive(st_empty);                            // this thread's S^T and dP^T columns are in registers
 #pragma unroll
         for (int ch = 0; ch < 4; ++ch) {
           float f[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            const int c = half * 32 + ch * 8 + e;
-            f[e] = __uint_as_float(sv[c]) * (__uint_as_float(dp[ch * 8 + e]) - mD[c]) * p.scale;
+            const int c = ch * 8 + e;
+            f[e] = __uint_as_float(sv[c]) * (__uint_as_float(dp[c]) - mD[c_base + c]) * p.scale;
           }
-          *reinterpret_cast<bf16x8*>(ds_row + (((half * 4 + ch) ^ (r & 7)) << 4)) = pack8(f);
+          *reinterpret_cast<bf16x8*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) = pack8(f);
         }
       }
       fence_proxy_async_smem();
       mbar_arrive(pds_full);
 
-      // ---- overlap: while the tensor cores run S^T/dP^T(it+1) and dV/dK/dQ^T(it), build P^T(it+1)
-      if (it + 1 < n_total) compute_p(it + 1);
+      // ---- dQ^T(it-1): TMEM [lane = d][col = q] -> smem [q][d] fp32 -> one TMA reduce-add into dq_acc.  dQ^T is
+      //      double-buffered in TMEM, so this drain (and its two CTA barriers) runs UNDER the MMAs of step it
+      //      instead of between them; the barriers also publish the metadata of step it+2.
+      drain_dq(it - 1, it + 2);
 
-      // ---- dQ^T(it): TMEM [lane = d][col = q] -> smem [q][d] fp32 -> one TMA reduce-add into dq_acc
-      mbar_wait(dq_full, it & 1);
-      tc_fence_after();
-      uint32_t dq[64];
-      {
-        uint32_t (&a)[32] = *reinterpret_cast<uint32_t (*)[32]>(&dq[0]);
-        uint32_t (&b)[32] = *reinterpret_cast<uint32_t (*)[32]>(&dq[32]);
-        tmem_ld_32x32b_x32(t_lane + C::kColDQT, a);
-        tmem_ld_32x32b_x32(t_lane + C::kColDQT + 32, b);
-      }
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(dq_empty);
-      if (threadIdx.x == 0) tma_store_wait_read<0>();     // previous reduce has finished reading the staging tile
-      asm volatile("bar.sync 2, 128;" ::: "memory");
-      {
-        float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
-#pragma unroll
-        for (int c = 0; c < 64; ++c) stage[c * kBwdD + r] = __uint_as_float(dq[c]);
-      }
-      if (it + 2 < n_total) meta_store(it + 2);           // ring slot (it+2)%3 == (it-1)%3 is no longer read
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 2, 128;" ::: "memory");      // also publishes the metadata stored above
-      if (threadIdx.x == 0) {
-        tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, h * p.head_dim, q0);
-        tma_store_commit();
-      }
+      // ---- while the tensor cores run S^T/dP^T(it+1) and dV/dK/dQ^T(it), build P^T(it+1)
+      if (it + 1 < n_total) compute_p(it + 1);
     }
+    drain_dq(n_total - 1, n_total + 2);
     if (threadIdx.x == 0) tma_store_wait<0>();
 
     // ---- dK / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
     mbar_wait(acc_done, 0);
     tc_fence_after();
-#pragma unroll
-    for (int which = 0; which < 2; ++which) {
+    {
+      const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
       uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
       const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
 #pragma unroll
@@ -424,7 +440,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
       }
     }
     fence_proxy_async_smem();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     if (threadIdx.x == 0) {
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
@@ -438,7 +454,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) tmem_dealloc<1>(tmem_base, 512);
+  if (warp == kBwdTmaWarp) tmem_dealloc<1>(tmem_base, 512);
 }
 
 }  // namespace attn
