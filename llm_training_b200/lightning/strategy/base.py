@@ -163,6 +163,10 @@ class Strategy:
             for e in self.engines:
                 e.overlap_optimizer = True
         trainer.optimizers, trainer.lr_scheduler_configs = self._setup_optimizers(trainer, module)
+        from ...utils.profiling import enable_nvtx, nvtx_requested
+        if nvtx_requested() and self.root_device.type == 'cuda':
+            for model in self._sharded_models(module):
+                enable_nvtx(model)
 
     def _materialize(self, module: nn.Module) -> None:
         device = self.root_device

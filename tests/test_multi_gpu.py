@@ -218,3 +218,66 @@ def test_fused_tensor_parallel_kernels_match_nccl_path():
         for a, b in zip(ref[rank][1], got[rank][1]):
             assert abs(a - b) <= 5e-2 * max(1e-3, abs(a)), (a, b)
         assert got[rank][2] is not None and got[rank][2] < 5e-2
+
+
+def _flag_stress_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
+    try:
+        os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
+                          MASTER_PORT=str(port), LLMT_COMM='nvlink')
+        import torch.distributed as dist
+        torch.cuda.set_device(rank)
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+        from llm_training_b200.parallel import init_mesh
+        from llm_training_b200.parallel.comm import get_comm
+        mesh = init_mesh(world, 1)
+        comm = get_comm(mesh.dp)
+        assert getattr(comm, 'is_nvlink', False)
+        n = 1 << 16
+        slice_n = n // world
+        buf = comm.alloc(n, torch.float32)
+        bad = 0
+        val = torch.zeros(4, dtype=torch.float32, device='cuda')
+        for i in range(1500):
+            # every rank stamps ITS slice with the round number (the rest with -1), then pulls the peers' slices
+            # through the mapped pointers (barrier + pull kernel): a stale stamp means the flag barrier let a reader
+            # through before the writer's data was visible, or let a writer of round i+1 overtake a reader of round i
+            buf.tensor.fill_(-1.0)
+            buf.tensor[rank * slice_n:(rank + 1) * slice_n].fill_(float(i))
+            if (i + rank) % 3 == 0:
+                torch.cuda._sleep(200_000)              # skew the ranks
+            comm.allgather_pull(buf, 0, slice_n * 4)
+            peer = (rank + 1) % world
+            stamps = buf.tensor[peer * slice_n:(peer + 1) * slice_n]
+            if float(stamps.min()) != float(i) or float(stamps.max()) != float(i):
+                bad += 1
+            comm.barrier()                              # nobody overwrites before everyone has read
+            val.fill_(float(rank + i))
+            comm.all_reduce(val)
+            expect = sum(r + i for r in range(world))
+            if abs(float(val[0]) - expect) > 1e-3:
+                bad += 1
+        torch.cuda.synchronize()
+        queue.put((rank, 'ok', bad))
+        dist.barrier()
+        dist.destroy_process_group()
+    except Exception:  # noqa: BLE001
+        queue.put((rank, 'error', traceback.format_exc()))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
+def test_symmetric_memory_flag_protocol_stress():
+    """1500 rounds of write -> flag barrier -> peer read -> barrier -> one-shot all-reduce with skewed ranks: the
+    epoch flags must never let a reader run ahead of a writer."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    queue = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_flag_stress_worker, args=(r, 2, port, 'nvlink', queue)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for _ in range(2):
+        rank, status, payload = queue.get(timeout=300)
+        assert status == 'ok', f'rank {rank}:\n{payload}'
+        assert payload == 0, f'rank {rank}: {payload} stale reads / wrong sums'
+    for p in procs:
+        p.join(timeout=60)
