@@ -56,13 +56,16 @@ def packed_attention(qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.
 
     ``qkv`` is ``[T, (Hq + 2*Hkv) * D]`` laid out ``q heads | k heads | v heads`` per row (the output
     of the fused QKV projection, RoPE already applied).  Token ``t`` attends keys ``j`` with
-    ``seg_start[t] <= j <= t`` (and ``j > t - window`` if a sliding window is set).  Returns ``[T, Hq*D]``.
+    ``seg_start[t] <= j <= t`` (and ``j >= t - window`` if a sliding window is set: ``window`` keys back plus the
+    token itself, the meaning of flash-attn's ``window_size=(window, window)`` and of the reference's eager mask,
+    attention_op.py:160-161,588).  Returns ``[T, Hq*D]``.
     """
     scale = (1.0 / math.sqrt(head_dim)) if scale is None else scale
     w = int(window) if window else 0
     if _lib.use_kernels(qkv):
+        # the kernels count the visible keys INCLUDING the query's own position
         return _PackedAttentionFn.apply(qkv.contiguous(), seg_start, seg_end, num_heads, num_kv_heads, head_dim,
-                                        scale, w)
+                                        scale, w + 1 if w else 0)
     t = qkv.shape[0]
     q, k, v = qkv.split([num_heads * head_dim, num_kv_heads * head_dim, num_kv_heads * head_dim], dim=-1)
     o = attention_ref(q.reshape(t, num_heads, head_dim), k.reshape(t, num_kv_heads, head_dim),
@@ -87,7 +90,7 @@ def prepare_4d_causal_attention_mask(attention_mask: torch.Tensor | None, input_
     idx = torch.arange(seq, device=device)
     allowed = (idx[None, None, :] <= idx[None, :, None]) & (idx[None, None, :] >= start[:, :, None])
     if sliding_window:
-        allowed &= idx[None, None, :] > (idx[None, :, None] - sliding_window)
+        allowed &= idx[None, None, :] >= (idx[None, :, None] - sliding_window)
     if attention_mask is not None:
         allowed &= attention_mask.to(device).bool()[:, None, :]
         # fully masked (pad) query rows attend to themselves so softmax stays finite

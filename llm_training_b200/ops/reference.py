@@ -68,7 +68,7 @@ def attention_mask_from_bounds(seg_start: torch.Tensor, window: int | None = Non
     idx = torch.arange(t, device=seg_start.device)
     allowed = (idx[None, :] <= idx[:, None]) & (idx[None, :] >= seg_start[:, None])
     if window is not None and window > 0:
-        allowed &= idx[None, :] > (idx[:, None] - window)
+        allowed &= idx[None, :] >= (idx[:, None] - window)      # `window` keys back + the token itself (HF / flash-attn)
     return allowed
 
 
