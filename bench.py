@@ -120,6 +120,7 @@ def main() -> None:
     ap.add_argument('--micro-batch', type=int, default=1)
     ap.add_argument('--recompute', default='auto', choices=['auto', 'none', 'full', 'selective'])
     ap.add_argument('--tp', type=int, default=1)
+    ap.add_argument('--phases', action='store_true', help='also report forward / backward / optimizer device time')
     args = ap.parse_args()
     if args.impl == 'reference':
         reference_arm(args)
@@ -230,14 +231,27 @@ def main() -> None:
              'position_ids': torch.arange(args.seq_len).unsqueeze(0).to(device), 'labels': ids.to(device)}
     optimizer = trainer.optimizers[0]
 
+    phase_events: list = []
+
     def step() -> None:
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(4)] if (args.phases and cuda) else None
+        if marks:
+            marks[0].record()
         loss = trainer.strategy.training_step(batch, 0)
+        if marks:
+            marks[1].record()
         trainer.strategy.backward(loss)
+        if marks:
+            marks[2].record()
         trainer.strategy.optimizer_step(optimizer)
         optimizer.zero_grad()
+        if marks:
+            marks[3].record()
+            phase_events.append(marks)
 
     for _ in range(args.warmup):
         step()
+    phase_events.clear()
     sampler = ClockSampler(local_rank)
     have_lib = cuda and _lib.kernels_available()
     if have_lib:
@@ -281,6 +295,13 @@ def main() -> None:
         pass
     value = tokens_per_step / (ms / 1e3)
     e2e_value = tokens_per_step / (e2e_ms / 1e3)
+    phases = None
+    if phase_events:
+        fwd = sum(m[0].elapsed_time(m[1]) for m in phase_events) / len(phase_events)
+        bwd = sum(m[1].elapsed_time(m[2]) for m in phase_events) / len(phase_events)
+        opt = sum(m[2].elapsed_time(m[3]) for m in phase_events) / len(phase_events)
+        phases = {'forward_ms': reduce_max(fwd), 'backward_ms': reduce_max(bwd), 'optimizer_ms': reduce_max(opt)}
+    zero3 = any(getattr(e, 'reshard', False) for e in trainer.strategy.engines)
     if rank == 0:
         mfu = (value * flops_per_token / 1e12 / (peak * world)) if peak else None
         print(json.dumps({
@@ -289,7 +310,8 @@ def main() -> None:
             'vs_baseline': None, 'dtype': 'bf16' if cuda else 'fp32', 'data': 'synthetic', 'impl': 'ours',
             'config': {'model': args.model if args.layers <= 0 else f'{args.model}-{args.layers}layers', 'global_batch': args.micro_batch * dp, 'seq_len': args.seq_len,
                        'parallelism': f'dp{dp}' + (f'xtp{args.tp}' if args.tp > 1 else ''),
-                       'sharding': 'flat-param ZeRO (optimizer+grad sharded, params resident)',
+                       'sharding': ('flat-param ZeRO-3 (params, grads and optimizer state sharded)' if zero3 else
+                                    'flat-param ZeRO (optimizer+grad sharded, params resident)'),
                        'optimizer': 'AdamW fp32 master, grad clip 1.0', 'recompute': recompute,
                        'l2': 'working set (16 GB bf16 weights) >> 126 MB L2, no flush needed'},
             'mfu_of_measured_sustained_peak': mfu, 'model_tflops_per_gpu': value * flops_per_token / 1e12 / world,
@@ -298,6 +320,7 @@ def main() -> None:
                     'h2d_bytes_per_step': timer.h2d, 'd2h_bytes_per_step': timer.d2h,
                     'api': 'Trainer.fit(CLM, DummyDataModule)'},
             'gpu_launches': int(launches), 'last_loss': getattr(timer, 'last_loss', None),
+            **({'phases': phases} if phases else {}),
         }))
     if dist.is_initialized():
         dist.barrier()

@@ -207,8 +207,8 @@ struct AdamWArgs {
 template <typename GradT>
 __global__ void __launch_bounds__(256)
 adamw_push_kernel(float* __restrict__ master, float* __restrict__ m, float* __restrict__ v,
-                  const GradT* __restrict__ grad, Peers params, int rank, int world, int64_t shard_elems,
-                  AdamWArgs a, const float* __restrict__ norm_sq) {
+                  const GradT* __restrict__ grad, Peers params, uint4* __restrict__ mc_params, int rank, int world,
+                  int64_t shard_elems, AdamWArgs a, const float* __restrict__ norm_sq) {
   float gscale = a.grad_scale;
   if (norm_sq != nullptr && a.max_norm > 0.f) {
     const float norm = sqrtf(*norm_sq) * fabsf(a.grad_scale);
@@ -248,10 +248,18 @@ adamw_push_kernel(float* __restrict__ master, float* __restrict__ m, float* __re
     reinterpret_cast<float4*>(v)[2 * i + 1] = *reinterpret_cast<float4*>(&vv[4]);
     const bf16x8 packed = pack8(p);
     const uint4 raw = *reinterpret_cast<const uint4*>(&packed);
+    if (mc_params != nullptr) {
+      // NVSwitch multicast: ONE 16-byte store leaves this GPU, the switch replicates it into every rank's arena
+      // (this rank's included) -> outbound traffic is shard bytes instead of (world - 1) x shard bytes
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_params + base + i),
+                   "f"(__uint_as_float(raw.x)), "f"(__uint_as_float(raw.y)), "f"(__uint_as_float(raw.z)),
+                   "f"(__uint_as_float(raw.w)) : "memory");
+    } else {
 #pragma unroll 1
-    for (int q = 0; q < world; ++q) {
-      const int dst_rank = (rank + q) % world;
-      st_peer_16(reinterpret_cast<uint4*>(params.ptr[dst_rank]) + base + i, raw);
+      for (int q = 0; q < world; ++q) {
+        const int dst_rank = (rank + q) % world;
+        st_peer_16(reinterpret_cast<uint4*>(params.ptr[dst_rank]) + base + i, raw);
+      }
     }
   }
 }
@@ -364,13 +372,15 @@ extern "C" int llmt_comm_allreduce_f32(const void* const* buf_ptrs, const void* 
   return check_launch("comm_allreduce_f32");
 }
 
-extern "C" int llmt_comm_adamw_push(float* master, float* m, float* v, const void* grad_shard,
-                                    const void* const* param_ptrs, int rank, int world, int64_t shard_elems,
-                                    int grad_is_fp32, float lr, float beta1, float beta2, float eps,
-                                    float weight_decay, int step, float grad_scale, float max_norm,
-                                    const float* norm_sq, cudaStream_t stream) {
+// mc_params: multicast (NVSwitch) address of the same arena range, or NULL -> one unicast store per peer.
+extern "C" int llmt_comm_adamw_push_mc(float* master, float* m, float* v, const void* grad_shard,
+                                       const void* const* param_ptrs, void* mc_params, int rank, int world,
+                                       int64_t shard_elems, int grad_is_fp32, float lr, float beta1, float beta2,
+                                       float eps, float weight_decay, int step, float grad_scale, float max_norm,
+                                       const float* norm_sq, cudaStream_t stream) {
   LLMT_REQUIRE(step >= 1, "adamw_push: step must be >= 1");
   LLMT_REQUIRE(shard_elems % 8 == 0, "adamw_push: shard must be a multiple of 8 elements");
+  LLMT_REQUIRE((uintptr_t)mc_params % 16 == 0, "adamw_push: multicast pointer must be 16-byte aligned");
   Peers params;
   if (fill_peers(&params, param_ptrs, world)) return 1;
   if (shard_elems == 0) return 0;
@@ -381,10 +391,21 @@ extern "C" int llmt_comm_adamw_push(float* master, float* m, float* v, const voi
   a.grad_scale = grad_scale; a.max_norm = max_norm;
   const int grid = grid_for(shard_elems / 8, 256, update_ctas_per_sm());
   if (grad_is_fp32)
-    adamw_push_kernel<float><<<grid, 256, 0, stream>>>(master, m, v, (const float*)grad_shard, params, rank, world,
-                                                       shard_elems, a, norm_sq);
+    adamw_push_kernel<float><<<grid, 256, 0, stream>>>(master, m, v, (const float*)grad_shard, params,
+                                                       (uint4*)mc_params, rank, world, shard_elems, a, norm_sq);
   else
     adamw_push_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(master, m, v, (const __nv_bfloat16*)grad_shard, params,
-                                                               rank, world, shard_elems, a, norm_sq);
+                                                               (uint4*)mc_params, rank, world, shard_elems, a,
+                                                               norm_sq);
   return check_launch("comm_adamw_push");
+}
+
+extern "C" int llmt_comm_adamw_push(float* master, float* m, float* v, const void* grad_shard,
+                                    const void* const* param_ptrs, int rank, int world, int64_t shard_elems,
+                                    int grad_is_fp32, float lr, float beta1, float beta2, float eps,
+                                    float weight_decay, int step, float grad_scale, float max_norm,
+                                    const float* norm_sq, cudaStream_t stream) {
+  return llmt_comm_adamw_push_mc(master, m, v, grad_shard, param_ptrs, nullptr, rank, world, shard_elems,
+                                 grad_is_fp32, lr, beta1, beta2, eps, weight_decay, step, grad_scale, max_norm,
+                                 norm_sq, stream);
 }

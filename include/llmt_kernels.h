@@ -82,6 +82,13 @@ int llmt_comm_adamw_push(float* master, float* m, float* v, const void* grad_sha
                          float beta2, float eps, float weight_decay, int step, float grad_scale, float max_norm,
                          const float* norm_sq, cudaStream_t stream);
 
+/* Same with NVSwitch multicast: mc_params is the multicast address of the arena range (NULL -> unicast stores); one
+ * multimem.st per 16 bytes leaves the GPU and the switch writes every rank's copy. */
+int llmt_comm_adamw_push_mc(float* master, float* m, float* v, const void* grad_shard, const void* const* param_ptrs,
+                            void* mc_params, int rank, int world, int64_t shard_elems, int grad_is_fp32, float lr,
+                            float beta1, float beta2, float eps, float weight_decay, int step, float grad_scale,
+                            float max_norm, const float* norm_sq, cudaStream_t stream);
+
 /* ---- packed causal attention (src/llm_training/ops/attention_op.py:538-654, flash-attn varlen) -----------
  * qkv: bf16 [T, (Hq+2Hkv)*D]; out: bf16 [T, Hq*D]; lse: fp32 [Hq, T] (log2 units); seg_start/seg_end int32 [T].
  * bwd scratch: delta fp32 [Hq, T]; dq_acc fp32 [T, Hq*D], must be zero on entry. */

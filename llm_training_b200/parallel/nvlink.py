@@ -37,6 +37,11 @@ class SymmetricBuffer:
         self.tensor = tensor
         self.handle = handle
         self.peer_ptrs: list[int] = [int(p) for p in handle.buffer_ptrs]
+        # NVSwitch multicast mapping of the same buffer (0 when the fabric / driver does not offer one)
+        try:
+            self.multicast_ptr = int(getattr(handle, 'multicast_ptr', 0) or 0)
+        except Exception:  # noqa: BLE001
+            self.multicast_ptr = 0
 
     def peer_ptrs_at(self, byte_offset: int):
         return _ptr_array([p + byte_offset for p in self.peer_ptrs])
@@ -61,6 +66,8 @@ class NVLinkComm(Comm):
         self._pads = _ptr_array([int(p) for p in self._scalars.handle.signal_pad_ptrs])
         self._barrier_epoch = 0
         self._allreduce_epoch = 0
+        import os
+        self.use_multicast = os.environ.get('LLMT_MULTICAST', '1') != '0'   # NVSwitch multicast stores when mapped
         self._lib = _lib.lib()
         self._rs_partial = torch.empty(self._lib.llmt_comm_rs_num_partials(), dtype=torch.float32, device=self.device)
         dist.barrier(group=self.group, device_ids=[self.device.index])
@@ -150,9 +157,10 @@ class NVLinkComm(Comm):
                    grad_shard: torch.Tensor, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, *,
                    lr: float, beta1: float, beta2: float, eps: float, weight_decay: float, step: int,
                    max_norm: float, norm_sq: torch.Tensor | None) -> None:
-        _lib.check(self._lib.llmt_comm_adamw_push(
+        mc = arena.multicast_ptr + byte_offset if (arena.multicast_ptr and self.use_multicast) else 0
+        _lib.check(self._lib.llmt_comm_adamw_push_mc(
             _lib.ptr(master), _lib.ptr(exp_avg), _lib.ptr(exp_avg_sq), _lib.ptr(grad_shard),
-            arena.peer_ptrs_at(byte_offset), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
+            arena.peer_ptrs_at(byte_offset), ctypes.c_void_p(mc), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
             _lib.c_int(grad_shard.dtype == torch.float32), _lib.c_f32(lr), _lib.c_f32(beta1), _lib.c_f32(beta2),
             _lib.c_f32(eps), _lib.c_f32(weight_decay), _lib.c_int(step), _lib.c_f32(1.0), _lib.c_f32(max_norm),
             _lib.ptr(norm_sq), _lib.stream()), 'comm_adamw_push')
