@@ -85,7 +85,7 @@ def test_sharded_data_parallel_matches_single_process(accum, reshard):
         assert torch.equal(results[0][0][n], results[1][0][n]), n
 
 
-def _fit_worker(rank: int, world: int, tmpdir: str, ckpt_path, max_steps: int):
+def _fit_worker(rank: int, world: int, tmpdir: str, ckpt_path, max_steps: int, reshard: bool = False):
     from llm_training_b200.data import DummyDataModule, DummyDataModuleConfig
     from llm_training_b200.lightning import FSDP2Strategy, ModelCheckpoint, Trainer, seed_everything
     from llm_training_b200.lms import CLM, CLMConfig
@@ -98,13 +98,19 @@ def _fit_worker(rank: int, world: int, tmpdir: str, ckpt_path, max_steps: int):
                    lr_scheduler_kwargs=dict(num_warmup_steps=2, min_lr=1e-4)))))
     dm = DummyDataModule(DummyDataModuleConfig(batch_size=2, vocab_size=128, max_length=16, num_samples=48,
                                                base_seed=5, pin_memory=False))
-    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world), precision='32-true', logger=False,
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world, reshard_after_forward=reshard),
+                      precision='32-true', logger=False,
                       enable_progress_bar=False, max_steps=max_steps, gradient_clip_val=1.0, accelerator='cpu',
                       default_root_dir=tmpdir, max_epochs=1,
                       callbacks=[ModelCheckpoint(dirpath=tmpdir + '/ckpt', every_n_train_steps=4, save_top_k=-1)])
     trainer.fit(lm, dm, ckpt_path=ckpt_path)
-    return ({n: p.detach().clone() for n, p in lm.named_parameters()}, trainer.global_step,
-            int(lm.consumed_samples.compute()))
+    assert all(e.reshard == reshard for e in trainer.strategy.engines)
+    import contextlib
+    with contextlib.ExitStack() as stack:
+        for e in trainer.strategy.engines:
+            stack.enter_context(e.unsharded())               # ZeRO-3: parameters only exist whole inside
+        params = {n: p.detach().clone() for n, p in lm.named_parameters()}
+    return params, trainer.global_step, int(lm.consumed_samples.compute())
 
 
 def test_fit_checkpoint_resume_is_bit_identical(tmp_path):
@@ -119,6 +125,24 @@ def test_fit_checkpoint_resume_is_bit_identical(tmp_path):
     assert resumed[0][2] == full[0][2]                        # consumed-samples metric restored and continued
     for n, p in full[0][0].items():
         assert torch.allclose(resumed[0][0][n], p, atol=1e-6), n
+
+
+def test_zero3_fit_checkpoint_resume_matches_resident_run(tmp_path):
+    """The same Trainer.fit in ZeRO-3 mode (reshard_after_forward=True): identical weights to the resident run, and a
+    sharded checkpoint written from slices-only state resumes to the same result."""
+    resident = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'r'), None, 8, False))
+    zero3 = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'z'), None, 8, True))
+    for n, p in resident[0][0].items():
+        assert torch.allclose(zero3[0][0][n], p, atol=1e-6), n
+    ckpt = str(tmp_path / 'z' / 'ckpt' / 'epoch=0-step=4.ckpt')
+    resumed = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'z2'), ckpt, 8, True))
+    assert resumed[0][1] == 8
+    for n, p in zero3[0][0].items():
+        assert torch.allclose(resumed[0][0][n], p, atol=1e-6), n
+    # and a ZeRO-3 checkpoint loads into a resident engine (same file format)
+    crossed = run_distributed(_fit_worker, world=2, args=(str(tmp_path / 'z3'), ckpt, 8, False))
+    for n, p in zero3[0][0].items():
+        assert torch.allclose(crossed[0][0][n], p, atol=1e-6), n
 
 
 def _tp_worker(rank: int, world: int, model_kind: str, dp: int, tp: int):
