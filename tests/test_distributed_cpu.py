@@ -145,7 +145,7 @@ def test_zero3_fit_checkpoint_resume_matches_resident_run(tmp_path):
         assert torch.allclose(crossed[0][0][n], p, atol=1e-6), n
 
 
-def _tp_worker(rank: int, world: int, model_kind: str, dp: int, tp: int):
+def _tp_worker(rank: int, world: int, model_kind: str, dp: int, tp: int, reshard: bool = False):
     from llm_training_b200.models import Llama, LlamaConfig, Phi3, Phi3Config
     from llm_training_b200.optim import ShardedOptimizer
     from llm_training_b200.parallel import apply_fully_sharded, init_mesh
@@ -159,7 +159,7 @@ def _tp_worker(rank: int, world: int, model_kind: str, dp: int, tp: int):
         model = Phi3(Phi3Config(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
                                 num_attention_heads=4, num_key_value_heads=2, pad_token_id=0,
                                 attn_implementation='sdpa'))
-    model.parallelize(dp_mesh=mesh.dp, tp_mesh=mesh.tp)
+    model.parallelize(dp_mesh=mesh.dp, tp_mesh=mesh.tp, reshard_after_forward=reshard)
     engine = model._flat_engine if getattr(model, '_flat_engine', None) is not None \
         else apply_fully_sharded(model, mesh.dp)
     opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1), [engine],
@@ -176,16 +176,18 @@ def _tp_worker(rank: int, world: int, model_kind: str, dp: int, tp: int):
         opt.step()
         losses.append(loss.item())
     full = {}
-    for n, p in model.named_parameters():
-        info = getattr(p, '_tp_info', None)
-        full[n] = info.gather(p.detach()) if info is not None else p.detach().clone()
+    with engine.unsharded():                          # no-op for the resident engine, gathers under ZeRO-3
+        for n, p in model.named_parameters():
+            info = getattr(p, '_tp_info', None)
+            full[n] = info.gather(p.detach()) if info is not None else p.detach().clone()
     return full, losses, float(opt.last_grad_norm)
 
 
-@pytest.mark.parametrize('model_kind,dp,tp', [('llama', 1, 2), ('phi3', 1, 2), ('llama', 2, 2)])
-def test_tensor_sequence_parallel_matches_single_process(model_kind, dp, tp):
+@pytest.mark.parametrize('model_kind,dp,tp,reshard', [('llama', 1, 2, False), ('phi3', 1, 2, False),
+                                                      ('llama', 2, 2, False), ('llama', 2, 2, True)])
+def test_tensor_sequence_parallel_matches_single_process(model_kind, dp, tp, reshard):
     from llm_training_b200.models import Llama, LlamaConfig, Phi3, Phi3Config
-    results = run_distributed(_tp_worker, world=dp * tp, args=(model_kind, dp, tp), timeout=600)
+    results = run_distributed(_tp_worker, world=dp * tp, args=(model_kind, dp, tp, reshard), timeout=600)
     torch.manual_seed(0)
     if model_kind == 'llama':
         ref = Llama(LlamaConfig(**TINY))
