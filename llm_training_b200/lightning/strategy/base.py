@@ -7,8 +7,7 @@ This is the part of Lightning's ``ParallelStrategy`` + the reference's ``FSDP2St
 import datetime
 import logging
 import os
-import pickle
-from contextlib import contextmanager, nullcontext
+from contextlib import contextmanager
 from typing import Any, ContextManager
 
 import torch

@@ -12,7 +12,6 @@ import os
 import random
 import subprocess
 import sys
-import time
 from typing import Any, Iterable
 
 import numpy as np

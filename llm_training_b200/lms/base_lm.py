@@ -7,7 +7,6 @@ import re
 from typing import Any
 
 import torch
-from torch import nn
 
 from ..lightning.module import LightningModule
 from ..models.base_model import BaseModel

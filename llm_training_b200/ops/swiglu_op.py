@@ -1,7 +1,6 @@
 """SiLU(gate) * up, and the three-matrix SwiGLU MLP
 (reference: src/llm_training/ops/swiglu_op.py:5-29, ops/liger_kernel/swiglu_op.py:6-39)."""
 import torch
-import torch.nn.functional as F
 
 from . import _lib
 from .reference import silu_mul_ref

@@ -21,7 +21,6 @@ engine built around *flat per-unit buffers*:
 Communication goes through :mod:`.comm` (gloo for CPU tests, NCCL or the NVLink kernels on GPUs).
 """
 import logging
-import math
 from typing import Any, Iterable
 
 import torch

@@ -7,7 +7,6 @@ default.
 """
 import contextlib
 import os
-from typing import Any
 
 import torch
 from torch import nn

@@ -1,6 +1,5 @@
 """Multi-process plumbing on CPU/gloo (BASELINE config 1): sharded-vs-single-process parity of the
 flat-parameter engine, gradient accumulation without sync, checkpoint save -> resume."""
-import copy
 
 import pytest
 import torch
