@@ -149,7 +149,9 @@ class _VocabParallelLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int,
-                axis: MeshAxis) -> torch.Tensor:
+                axis: MeshAxis, tp: 'TensorParallelContext | None' = None) -> torch.Tensor:
+        """``tp`` given: ``hidden`` is the LOCAL sequence shard and the logits GEMM gathers it itself (land-once
+        all-gather -> GEMM); backward then reduce-scatters dH inside the dgrad GEMM."""
         v_local = weight.shape[0]
         v0 = axis.rank * v_local
         local_labels = labels - v0
@@ -158,8 +160,12 @@ class _VocabParallelLoss(torch.autograd.Function):
         local_labels = torch.where(in_shard, local_labels, torch.full_like(labels, -1))
         local_labels = torch.where(labels == ignore_index, torch.full_like(labels, ignore_index), local_labels)
         use_k = _lib.use_kernels(hidden) and weight.dtype == torch.bfloat16 and v_local % 8 == 0
+        assert tp is None or use_k, 'fused vocab-parallel loss needs the CUDA kernels'
         if use_k:
-            logits = gemm(hidden.contiguous(), weight)
+            if tp is not None:
+                logits, hidden = _gather_gemm(tp, hidden.contiguous(), weight, b_mn_major=False)
+            else:
+                logits = gemm(hidden.contiguous(), weight)
             rows = logits.shape[0]
             lse_local = torch.empty(rows, dtype=torch.float32, device=hidden.device)
             tgt_local = torch.empty_like(lse_local)
@@ -179,6 +185,7 @@ class _VocabParallelLoss(torch.autograd.Function):
         dist.all_reduce(tgt, group=axis.group)
         ctx.save_for_backward(hidden, weight, logits, local_labels, lse)
         ctx.meta = (ignore_index, use_k, v_local)
+        ctx.tp = tp
         return (lse - tgt) * (labels != ignore_index)
 
     @staticmethod
@@ -192,7 +199,10 @@ class _VocabParallelLoss(torch.autograd.Function):
                                                       _lib.ptr(scale), _lib.c_int(rows), _lib.c_int(v_local),
                                                       _lib.c_i64(logits.stride(0)), _lib.c_i64(ignore_index),
                                                       _lib.c_f32(0.0), _lib.stream()), 'ce_bwd')
-            dh = gemm(logits, weight, b_mn_major=True)
+            if ctx.tp is not None:      # dH partial sums -> sequence shards, reduce-scattered by the dgrad GEMM
+                dh = _fused_linear_reduce_scatter(ctx.tp, logits, weight, None, b_mn_major=True)
+            else:
+                dh = gemm(logits, weight, b_mn_major=True)
             dw = gemm(logits, hidden.contiguous(), a_mn_major=True, b_mn_major=True)
         else:
             probs = torch.exp(logits - lse.unsqueeze(1))
@@ -202,7 +212,7 @@ class _VocabParallelLoss(torch.autograd.Function):
             dlogits = (probs - onehot) * (scale * (local_labels != ignore_index)).unsqueeze(1)
             dh = (dlogits @ weight.float()).to(hidden.dtype)
             dw = (dlogits.t() @ hidden.float()).to(weight.dtype)
-        return dh, dw, None, None, None
+        return dh, dw, None, None, None, None
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -415,6 +425,9 @@ class TensorParallelContext:
 
     def _token_nll(self, normed_local: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int
                    ) -> torch.Tensor:
+        if normed_local.dim() == 2 and weight.shape[0] % 8 == 0 and weight.dtype == torch.bfloat16 \
+                and self._fused_ok(normed_local, weight, normed_local.shape[0]):
+            return _VocabParallelLoss.apply(normed_local, weight, labels.contiguous(), ignore_index, self.axis, self)
         h = self.gather_sequence(normed_local)
         return _VocabParallelLoss.apply(h, weight, labels.contiguous(), ignore_index, self.axis)
 
