@@ -659,7 +659,7 @@ extern "C" int llmt_gemm_bf16_dist(int mode, const void* A, const void* const* a
   LLMT_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && ldc % 8 == 0, "gemm_dist: leading dimensions must be multiples of 8");
   LLMT_REQUIRE(cta_group == 1 || cta_group == 2, "gemm_dist: cta_group must be 1 or 2");
   if (max_ctas <= 0) max_ctas = num_sms();
-  static DistMaps maps;   // filled per call; copied into kernel parameters by the launch
+  static thread_local DistMaps maps;   // filled per call; copied into kernel parameters by the launch
   CUtensorMap ta, tb, tc;
   int rc;
   const int b_rows = BN / cta_group;
@@ -723,7 +723,7 @@ extern "C" int llmt_gemm_bf16_ag(const void* const* a_ptrs, void* a_full, const 
   LLMT_REQUIRE((uintptr_t)a_full % 16 == 0 && (uintptr_t)flags % 4 == 0, "gemm_ag: misaligned buffers");
   if (max_ctas <= 0) max_ctas = num_sms();
   if (max_ctas > num_sms()) max_ctas = num_sms();   // every CTA must be resident: the producers wait on all pullers
-  static DistMaps maps;
+  static thread_local DistMaps maps;
   CUtensorMap ta, tb, tc;
   int rc;
   const int b_rows = BN / cta_group;
@@ -778,7 +778,7 @@ extern "C" int llmt_gemm_bf16_wgather(const void* A, const void* const* shard_pt
                "gemm_wgather: misaligned buffers");
   if (max_ctas <= 0) max_ctas = num_sms();
   if (max_ctas > num_sms()) max_ctas = num_sms();
-  static DistMaps maps;
+  static thread_local DistMaps maps;
   CUtensorMap ta, tb, tc;
   int rc;
   const int b_rows = BN / cta_group;
