@@ -24,7 +24,10 @@ def timeit(fn, iters=10):
 def main():
     dev = 'cuda'
     results = []
-    for tokens, hq, hkv, d in [(8192, 32, 8, 128), (16384, 32, 8, 128), (8192, 32, 32, 96)]:
+    shapes = [(8192, 32, 8, 128), (16384, 32, 8, 128), (8192, 32, 32, 96)]
+    if os.environ.get('ATTN_SHAPES'):       # e.g. ATTN_SHAPES=131072,4,1,128 (one rank's heads of the 128k TP=8 config)
+        shapes = [tuple(int(v) for v in s.split(',')) for s in os.environ['ATTN_SHAPES'].split(';')]
+    for tokens, hq, hkv, d in shapes:
         torch.manual_seed(0)
         qkv = (torch.randn(tokens, (hq + 2 * hkv) * d, device=dev) * 0.5).bfloat16().requires_grad_()
         start = torch.zeros(tokens, dtype=torch.int32, device=dev)
@@ -47,6 +50,11 @@ def main():
             do2 = dout.view(1, tokens, hq, d)
             r['fa2_bwd_ms'] = timeit(lambda: torch.autograd.grad(o2, (q, k, v), do2, retain_graph=True))
             r['max_diff_vs_fa2'] = (o2.view(tokens, -1).float() - out.float()).abs().max().item()
+            ours = torch.autograd.grad(out, qkv, dout, retain_graph=True)[0]
+            theirs = torch.cat([t.reshape(tokens, -1) for t in torch.autograd.grad(o2, (q, k, v), do2, retain_graph=True)],
+                               dim=-1)
+            r['max_grad_diff_vs_fa2'] = (ours.float() - theirs.float()).abs().max().item()
+            r['grad_abs_max'] = theirs.float().abs().max().item()
         except Exception as ex:  # flash-attn missing or failing on this box
             r['fa2_error'] = repr(ex)[:200]
         results.append(r)
