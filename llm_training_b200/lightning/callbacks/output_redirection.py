@@ -26,8 +26,14 @@ class _Tee:
 
 
 class OutputRedirection(Callback):
+    LOG_FILE_SUFFIX = '.log'
+
     def __init__(self, log_file_name: str | None = None, redirect_stdout: bool = True, redirect_stderr: bool = True,
-                 redirect_loggers: bool = True, rank_zero_only: bool = True) -> None:
+                 redirect_loggers: bool = True, rank_zero_only: bool = True, enabled: bool = True) -> None:
+        """``log_file_name`` may contain ``{index}`` (number of logs already in the directory) and ``{version}``
+        (logger version), like the reference's default ``'{index}-{version}'``; ``enabled=False`` turns the callback
+        into a no-op (reference: output_redirection.py:16-33)."""
+        self.enabled = enabled
         self.log_file_name = log_file_name
         self.redirect_stdout, self.redirect_stderr = redirect_stdout, redirect_stderr
         self.redirect_loggers = redirect_loggers
@@ -39,14 +45,18 @@ class OutputRedirection(Callback):
     def _path(self, trainer) -> str:
         log_dir = trainer.log_dir
         os.makedirs(log_dir, exist_ok=True)
-        if self.log_file_name:
-            return os.path.join(log_dir, self.log_file_name)
-        existing = [f for f in os.listdir(log_dir) if f.endswith('.log')]
+        existing = [f for f in os.listdir(log_dir) if f.endswith(self.LOG_FILE_SUFFIX)]
         version = getattr(trainer.logger, 'version', None) or 'run'
-        return os.path.join(log_dir, f'{len(existing)}-{version}.log')
+        if self.log_file_name:
+            name = self.log_file_name.format(index=len(existing), version=version) \
+                if '{' in self.log_file_name else self.log_file_name
+            if not name.endswith(self.LOG_FILE_SUFFIX) and '{' in self.log_file_name:
+                name += self.LOG_FILE_SUFFIX
+            return os.path.join(log_dir, name)
+        return os.path.join(log_dir, f'{len(existing)}-{version}{self.LOG_FILE_SUFFIX}')
 
     def setup(self, trainer, pl_module, stage: str) -> None:
-        if self._file is not None or (self.rank_zero_only and not trainer.is_global_zero):
+        if not self.enabled or self._file is not None or (self.rank_zero_only and not trainer.is_global_zero):
             return
         path = trainer.strategy.broadcast(self._path(trainer)) if not self.rank_zero_only else self._path(trainer)
         if not trainer.is_global_zero:

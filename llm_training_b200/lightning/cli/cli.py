@@ -21,9 +21,23 @@ SUBCOMMANDS = ('fit', 'validate')
 
 
 class LightningCLI:
-    def __init__(self, args: list[str] | None = None, run: bool = True, trainer_class: type[Trainer] = Trainer,
+    def __init__(self, model_class: Any | None = None, datamodule_class: Any | None = None,
                  save_config_callback: type[SaveConfigCallback] | None = SaveConfigCallback,
-                 trainer_defaults: dict[str, Any] | None = None) -> None:
+                 save_config_kwargs: dict[str, Any] | None = None, trainer_class: type[Trainer] = Trainer,
+                 trainer_defaults: dict[str, Any] | None = None, seed_everything_default: bool | int = True,
+                 parser_kwargs: dict[str, Any] | None = None, subclass_mode_model: bool = False,
+                 subclass_mode_data: bool = False, args: list[str] | None = None, run: bool = True,
+                 auto_configure_optimizers: bool = True) -> None:
+        """Same keyword arguments as the reference's ``LightningCLI`` (lightning/cli/cli.py:18-33).  ``model_class`` /
+        ``datamodule_class`` fix the class when the YAML section has no ``class_path``; ``seed_everything_default``
+        is used when the config has no ``seed_everything``; ``save_config_kwargs`` go to the save-config callback;
+        ``parser_kwargs`` / ``subclass_mode_*`` / ``auto_configure_optimizers`` are jsonargparse-specific and
+        accepted for compatibility (every section is already resolved in subclass mode here)."""
+        if isinstance(model_class, (list, tuple)):      # LightningCLI(argv): argument list passed positionally
+            args, model_class = list(model_class), None
+        self.model_class, self.datamodule_class = model_class, datamodule_class
+        self.save_config_kwargs = save_config_kwargs or {}
+        self.seed_everything_default = seed_everything_default
         argv = list(sys.argv[1:] if args is None else args)
         configs, overrides, positional = parse_overrides(argv)
         self.subcommand = positional[0] if positional and positional[0] in SUBCOMMANDS else None
@@ -39,14 +53,29 @@ class LightningCLI:
         self.trainer_defaults = trainer_defaults or {}
 
         self.seed = None
-        if self.config.get('seed_everything') not in (None, False):
-            seed = self.config['seed_everything']
+        seed = self.config.get('seed_everything', self.seed_everything_default)
+        if seed not in (None, False):
             self.seed = seed_everything(None if seed is True else int(seed))
-        self.model = instantiate(self.config['model'])
-        self.datamodule = instantiate(self.config['data']) if self.config.get('data') else None
+        self.model = self._instantiate_section('model', self.model_class)
+        self.datamodule = self._instantiate_section('data', self.datamodule_class) if self.config.get('data') else None
         self.trainer = self._instantiate_trainer()
         if run:
             self.run()
+
+    def _instantiate_section(self, key: str, fixed_class: Any | None) -> Any:
+        """A section is ``{class_path, init_args}``; with a fixed class (``model_class`` / ``datamodule_class``) it may
+        also be the bare ``init_args`` mapping, as in Lightning's non-subclass mode."""
+        spec = self.config[key]
+        if fixed_class is not None and 'class_path' not in spec:
+            from .config import instantiate_nested as _nested
+            return fixed_class(**_nested(spec.get('init_args', spec)))
+        return instantiate(spec)
+
+    def add_arguments_to_parser(self, parser: Any = None) -> None:
+        """Hook of the reference's jsonargparse-based CLI (cli.py:52-77) where it registers ``--float32-matmul-
+        precision``, ``--logging-level`` and the ``output_redirection`` / ``tqdm_progress`` argument groups.  The YAML
+        loader of this CLI reads those keys directly, so there is nothing to register; subclasses may still override
+        this to post-process ``self.config`` before the trainer is built."""
 
     def _instantiate_trainer(self) -> Trainer:
         cfg = dict(self.trainer_defaults)
@@ -65,8 +94,9 @@ class LightningCLI:
         progress = self.config.get('tqdm_progress')
         if progress is not None or kwargs.get('enable_progress_bar', True):
             callbacks.append(TQDMProgressBar(**(progress or {})))
+        self.add_arguments_to_parser(None)
         if self.save_config_callback is not None:
-            callbacks.append(self.save_config_callback(config=self.config))
+            callbacks.append(self.save_config_callback(config=self.config, **self.save_config_kwargs))
         return self.trainer_class(callbacks=callbacks, **kwargs)
 
     def run(self) -> None:

@@ -256,7 +256,7 @@ class Strategy:
                 e.set_requires_gradient_sync(True)
 
     def optimizer_step(self, optimizer: Optimizer, closure=None) -> Any:
-        out = optimizer.step(closure) if closure is not None else optimizer.step()
+        out = self.precision_plugin.optimizer_step(optimizer, self.lightning_module, closure)
         self._grad_norm = getattr(optimizer, 'last_grad_norm', None)
         if self.lightning_module is not None:
             self.lightning_module._grad_norm = self._grad_norm
@@ -310,6 +310,60 @@ class Strategy:
                 shutil.rmtree(filepath, ignore_errors=True)
             elif os.path.exists(filepath):
                 os.remove(filepath)
+
+    # ---------------------------------------------------------------- Lightning strategy interface (names the
+    # reference's FSDP2Strategy exposes, fsdp2_strategy.py:140-167, 241-263, 315-360, 422-428)
+    @property
+    def num_processes(self) -> int:
+        """Processes (GPUs) of this node."""
+        return max(1, self.world_size // max(1, self.num_nodes))
+
+    @property
+    def is_distributed(self) -> bool:
+        return True
+
+    @property
+    def process_group_backend(self) -> str | None:
+        return self._process_group_backend
+
+    @property
+    def restore_checkpoint_after_setup(self) -> bool:
+        return True                      # weights are loaded into the flat buffers the engine builds in setup()
+
+    @property
+    def lightning_restore_optimizer(self) -> bool:
+        return False                     # optimizer slices are restored by `load_checkpoint`, not by the trainer
+
+    def setup_optimizers(self, trainer) -> None:
+        trainer.optimizers, trainer.lr_scheduler_configs = self._setup_optimizers(trainer, trainer.lightning_module)
+
+    def model_to_device(self) -> None:
+        if self.lightning_module is not None:
+            self._materialize(self.lightning_module)
+
+    def tensor_init_context(self, empty_init: bool | None = None) -> ContextManager:
+        """Dtype (and, with ``empty_init``, meta-device) context for building modules; materialisation is ``setup``."""
+        cms = [self.precision_plugin.tensor_init_context()]
+        if empty_init:
+            cms.append(torch.device('meta'))
+        return _Stack(*cms)
+
+    def lightning_module_state_dict(self) -> dict[str, Any]:
+        """Full-shape CPU state dict (ZeRO-3 units are gathered, TP shards are gathered over the tp axis)."""
+        from ..checkpoint_io import module_state_dict
+        return module_state_dict(self, balanced=False)
+
+    def load_model_state_dict(self, checkpoint: Any, strict: bool = True) -> None:
+        """Nothing to do: ``load_checkpoint`` already wrote the weights into the flat buffers."""
+
+    def optimizer_state(self, optimizer: Optimizer) -> dict[str, Any]:
+        return optimizer.state_dict()
+
+    def load_optimizer_state_dict(self, checkpoint: Any) -> None:
+        """Nothing to do: ``load_checkpoint`` already restored this rank's optimizer slices."""
+
+    def set_world_ranks(self) -> None:
+        """Ranks come from the launcher's environment (RANK / LOCAL_RANK / WORLD_SIZE); nothing to assign."""
 
     def synchronize_optimizer(self) -> None:
         """The current stream waits for in-flight (overlapped) optimizer work; call before touching parameters or

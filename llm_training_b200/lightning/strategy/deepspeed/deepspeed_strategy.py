@@ -76,6 +76,19 @@ class DeepSpeedStrategy(Strategy):
     def zero_stage_3(self) -> bool:
         return self.stage == 3
 
+    @property
+    def is_fp16(self) -> bool:
+        """fp16 with dynamic loss scaling (reference: deepspeed_strategy.py:104-108)."""
+        return self.precision_plugin.precision in ('16-mixed', '16-true')
+
+    @property
+    def skipped_steps(self) -> int:
+        """Optimizer steps skipped because the fp16 gradients overflowed (shown in the progress bar upstream)."""
+        return int(getattr(self.precision_plugin, 'skipped_steps', 0))
+
+    def init_deepspeed(self) -> None:
+        """DeepSpeed builds its engine here; the native engine is built in ``setup`` — kept for API parity."""
+
     def _mesh_sizes(self) -> tuple[int, int]:
         return self.world_size, 1
 
@@ -87,4 +100,7 @@ class DeepSpeedStrategy(Strategy):
                 self.precision_plugin.scaler = torch.amp.GradScaler(
                     self.root_device.type, init_scale=2.0 ** cfg['initial_scale_power'],
                     growth_interval=cfg['loss_scale_window'])
+            self.precision_plugin.growth_interval = int(cfg['loss_scale_window'])
+            self.precision_plugin.min_scale = float(cfg['min_loss_scale'])
+            self.precision_plugin.raise_error_at_min_scale = bool(self.raise_error_at_min_scale)
         super().setup(trainer)

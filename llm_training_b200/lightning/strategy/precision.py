@@ -34,15 +34,19 @@ class CPUOffloadPolicy(OffloadPolicy):
 
 
 class FSDP2Precision:
-    def __init__(self, precision: str | int = '32-true', scaler: Any | None = None) -> None:
+    def __init__(self, precision: str | int = '32-true', device: str | None = None, scaler: Any | None = None
+                 ) -> None:
+        """Same arguments as the reference (fsdp2_precision.py:25-30); ``device`` only selects the GradScaler /
+        autocast device type and defaults to CUDA when available."""
         precision = _ALIASES.get(precision, precision)
+        self.device = device or ('cuda' if torch.cuda.is_available() else 'cpu')
         supported = ('32-true', '16-true', 'bf16-true', '16-mixed', 'bf16-mixed')
         if precision not in supported:
             raise ValueError(f'`precision={precision!r}` is not supported; choose from {supported}')
         self.precision: str = precision
         self.scaler = scaler
         if precision == '16-mixed' and scaler is None:
-            self.scaler = torch.amp.GradScaler('cuda' if torch.cuda.is_available() else 'cpu')
+            self.scaler = torch.amp.GradScaler(self.device)
         table = {
             '32-true': (torch.float32, None),
             '16-true': (torch.float16, None),
@@ -76,6 +80,50 @@ class FSDP2Precision:
 
     def pre_backward(self, loss: torch.Tensor) -> torch.Tensor:
         return self.scaler.scale(loss) if self.scaler is not None else loss
+
+    def tensor_init_context(self) -> ContextManager:
+        """Default dtype while modules are built (reference: fsdp2_precision.py:104-106)."""
+        return self.module_init_context()
+
+    # ---- optimizer step with dynamic loss scaling (fp16-mixed).  The reference delegates to torch's GradScaler
+    #      (fsdp2_precision.py:130-163); the sharded optimizer unscales inside its fused update instead, so the only
+    #      host work is reading the norm's finiteness.
+    growth_factor, backoff_factor, growth_interval = 2.0, 0.5, 2000
+    min_scale: float = 1.0
+    raise_error_at_min_scale: bool = False
+
+    def optimizer_step(self, optimizer: Any, model: Any = None, closure: Any = None, **kwargs: Any) -> Any:
+        if closure is not None:
+            closure()
+        if self.scaler is None:
+            return optimizer.step(**kwargs)
+        scale = float(self.scaler.get_scale())
+        optimizer.grad_scale, optimizer.skip_nonfinite = 1.0 / scale, True
+        out = optimizer.step(**kwargs)
+        if getattr(optimizer, 'last_step_skipped', False):
+            self.skipped_steps = getattr(self, 'skipped_steps', 0) + 1
+            self._good_steps = 0
+            new_scale = scale * self.backoff_factor
+            if new_scale < self.min_scale:
+                if self.raise_error_at_min_scale:
+                    raise RuntimeError(f'fp16 loss scale fell below the minimum ({self.min_scale}): the gradients '
+                                       'overflow even at the smallest scale')
+                new_scale = self.min_scale
+        else:
+            self._good_steps = getattr(self, '_good_steps', 0) + 1
+            new_scale = scale * self.growth_factor if self._good_steps % self.growth_interval == 0 else scale
+        self.scaler.update(new_scale)
+        return out
+
+    def clip_grad_by_norm(self, optimizer: Any, clip_val: float) -> None:
+        """The clip runs inside the fused optimizer kernel from the device-side global norm; this only sets it."""
+        optimizer.max_grad_norm = float(clip_val) if clip_val else None
+
+    def clip_gradients(self, optimizer: Any, clip_val: int | float = 0.0, gradient_clip_algorithm: Any = 'norm'
+                       ) -> None:
+        if str(getattr(gradient_clip_algorithm, 'value', gradient_clip_algorithm)).lower() not in ('norm', 'none'):
+            raise ValueError('only gradient clipping by global norm is supported (the reference clips by norm)')
+        self.clip_grad_by_norm(optimizer, clip_val)
 
     def state_dict(self) -> dict:
         return self.scaler.state_dict() if self.scaler is not None else {}

@@ -61,6 +61,13 @@ class CLM(BaseLightningModule):
         else:                                                        # generic models: forward hook
             self.model.get_input_embeddings().register_forward_hook(self._neftune_hook)
 
+    # names of the reference's hooks (lms/clm/clm.py:45-82)
+    def register_neftune_hook(self) -> None:
+        self.register_neftune()
+
+    def neftune_forward_hook(self, module, input, output):     # noqa: A002 -- reference signature
+        return self._neftune_hook(module, input, output)
+
     def _neftune_hook(self, module, inputs, output):
         if not module.training:
             return output

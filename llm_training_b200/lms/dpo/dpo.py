@@ -99,6 +99,16 @@ class DPO(BaseLightningModule):
                 out[f'reference_{side}_logps'], _ = sequence_logps(self.ref_model, *args)
         return out
 
+    def get_logps(self, model: BaseModel, input_ids: torch.Tensor, attention_mask: torch.Tensor | None,
+                  position_ids: torch.Tensor | None, labels: torch.Tensor) -> torch.Tensor:
+        """Per-sequence SUM of label log-probabilities (``labels`` already shifted), same contract as the
+        reference (lms/dpo/dpo.py:73-114) — computed by the fused linear + log-prob path, so no ``[B, T, V]``
+        log-softmax is materialised (vocab-parallel under TP)."""
+        return sequence_logps(model, input_ids, attention_mask, position_ids, labels, self.config.ignore_index)[0]
+
+    def add_suffix_to_metrics(self, metrics: dict[str, torch.Tensor], suffix: str) -> dict[str, torch.Tensor]:
+        return {k + suffix: v for k, v in metrics.items()}
+
     def compute_loss(self, policy_chosen_logps: torch.Tensor, policy_rejected_logps: torch.Tensor,
                      reference_chosen_logps: torch.Tensor, reference_rejected_logps: torch.Tensor,
                      metrics: dict[str, torch.Tensor]) -> torch.Tensor:

@@ -57,6 +57,18 @@ class ORPO(BaseLightningModule):
             out[f'{side}_mean_logit'] = self._mean_logit(model_out)
         return out
 
+    def get_logps(self, logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Length-normalised label log-probabilities from materialised logits (``labels`` already shifted), the
+        reference's helper (lms/orpo/orpo.py:61-93).  The training path does not call it: ``forward_batch`` uses the
+        fused linear + log-prob op on the hidden states instead."""
+        mask = labels != self.config.ignore_index
+        logp = torch.log_softmax(logits.float(), dim=-1)
+        picked = logp.gather(-1, labels.clamp_min(0).unsqueeze(-1)).squeeze(-1) * mask
+        return picked.sum(-1) / mask.sum(-1).clamp_min(1)
+
+    def add_suffix_to_metrics(self, metrics: dict[str, torch.Tensor], suffix: str) -> dict[str, torch.Tensor]:
+        return {k + suffix: v for k, v in metrics.items()}
+
     def _mean_logit(self, model_out) -> torch.Tensor:
         if model_out.logits is not None:
             return model_out.logits.detach().float().mean()

@@ -165,3 +165,12 @@ def attention_core(qkv: torch.Tensor, ctx: PackedContext, *, num_heads: int, num
     if selective_recompute and training and torch.is_grad_enabled():
         return torch.utils.checkpoint.checkpoint(core, qkv, use_reentrant=False)
     return core(qkv)
+
+
+def repeat_kv(hidden_states: torch.Tensor, n_rep: int) -> torch.Tensor:
+    """``[B, Hkv, S, D] -> [B, Hkv * n_rep, S, D]`` (reference: llama_model.py:430-431).  Only the eager / SDPA
+    fallbacks need it; the packed attention kernels read each KV head once for its whole query group."""
+    if n_rep == 1:
+        return hidden_states
+    b, h, s, d = hidden_states.shape
+    return hidden_states[:, :, None].expand(b, h, n_rep, s, d).reshape(b, h * n_rep, s, d)

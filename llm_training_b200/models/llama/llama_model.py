@@ -21,7 +21,8 @@ from torch import nn
 
 from ...ops import (embedding, linear, multi_linear, neftune_noise_scale, norm_multi_linear, silu_mul_fused,
                     swiglu_down_linear)
-from ..decoder import PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context
+from ..decoder import (PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context,
+                       repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
 from .llama_config import LlamaConfig

@@ -14,7 +14,8 @@ import torch.utils.checkpoint
 from torch import nn
 
 from ...ops import embedding, linear, neftune_noise_scale, silu_mul_fused
-from ..decoder import PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context
+from ..decoder import (PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context,
+                       repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
 from .phi3_config import Phi3Config

@@ -115,6 +115,67 @@ def get_unpad_data(attention_mask: torch.Tensor) -> tuple[torch.Tensor, torch.Te
     return indices, cu, int(lengths.max().item()) if lengths.numel() else 0
 
 
+# ---------------------------------------------------------------------------------------------------
+# helpers of the reference's public surface (attention_op.py:286-314, 375-385, 488-536), vectorised
+# ---------------------------------------------------------------------------------------------------
+def get_sequence_indices(attention_mask: torch.Tensor) -> list[tuple[int, int, int]]:
+    """``(row, first, last)`` (inclusive) of every run of equal segment ids, row by row, in order of appearance.
+    One pass of tensor ops instead of the reference's Python loop over every token."""
+    mask = attention_mask if attention_mask.dim() == 2 else attention_mask.view(1, -1)
+    rows, seq = mask.shape
+    if seq == 0:
+        return []
+    change = torch.ones((rows, seq), dtype=torch.bool, device=mask.device)
+    change[:, 1:] = mask[:, 1:] != mask[:, :-1]
+    starts = change.nonzero()                                    # sorted by (row, column)
+    r, first = starts[:, 0], starts[:, 1]
+    last = torch.empty_like(first)
+    last[:-1] = first[1:] - 1
+    last[-1] = seq - 1
+    row_end = torch.ones_like(r, dtype=torch.bool)
+    row_end[:-1] = r[1:] != r[:-1]
+    last[row_end] = seq - 1
+    return [(int(a), int(b), int(c)) for a, b, c in zip(r.tolist(), first.tolist(), last.tolist())]
+
+
+def update_4d_causal_mask_for_packed_sequence(causal_mask: torch.Tensor,
+                                              sequence_indices: list[tuple[int, int, int]],
+                                              inplace: bool = False) -> torch.Tensor:
+    """Block everything a document's queries could see before the document's first token."""
+    causal_mask = causal_mask if inplace else causal_mask.clone()
+    min_dtype = torch.finfo(causal_mask.dtype).min
+    for i, s, e in sequence_indices:
+        causal_mask[i, :, s:e + 1, :s] = min_dtype
+    return causal_mask
+
+
+def get_max_seqlen_in_batch(attention_mask: torch.Tensor) -> torch.Tensor:
+    """Lengths (int32) of the documents of a segment-id mask, ordered by row then by segment id; padding (id 0) is
+    not a document.  Same result as the reference's loop over ``max(segment id)`` without the per-id reductions."""
+    mask = attention_mask if attention_mask.dim() == 2 else attention_mask.view(1, -1)
+    n_ids = int(mask.max()) if mask.numel() else 0
+    if n_ids <= 0:
+        return torch.zeros(0, dtype=torch.int32, device=mask.device)
+    ids = torch.arange(1, n_ids + 1, device=mask.device)
+    counts = (mask.unsqueeze(-1) == ids).sum(dim=1).flatten()    # [rows, n_ids] -> row-major
+    return counts[counts > 0].to(torch.int32)
+
+
+def prepare_fa2_from_position_ids(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                  position_ids: torch.Tensor):
+    """Flatten ``[B, S, H, D]`` q / k / v and derive ``cu_seqlens`` from the places where ``position_ids`` restart at
+    0 (every document of a pack restarts its positions).  Returns ``(q, k, v, indices_q, (cu_q, cu_k),
+    (max_q, max_k))`` like the reference, for callers that drive a varlen attention kernel themselves."""
+    query = query.reshape(-1, query.size(-2), query.size(-1))
+    key = key.reshape(-1, key.size(-2), key.size(-1))
+    value = value.reshape(-1, value.size(-2), value.size(-1))
+    flat = position_ids.flatten()
+    indices_q = torch.arange(flat.size(0), device=flat.device, dtype=torch.int32)
+    cu = torch.cat((indices_q[flat == 0], torch.tensor([flat.size(0)], device=flat.device, dtype=torch.int32)))
+    max_len = flat.max() + 1
+    return query, key, value, indices_q, (cu, cu), (max_len, max_len)
+
+
 def flash_attention_forward(query_states: torch.Tensor, key_states: torch.Tensor, value_states: torch.Tensor,
                             attention_mask: torch.Tensor | None, query_length: int, is_causal: bool = True,
                             dropout: float = 0.0, softmax_scale: float | None = None,

@@ -55,6 +55,11 @@ class ShardedOptimizer(Optimizer):
         if not self.fused:
             self._build_generic()
         self.last_grad_norm: torch.Tensor | None = None
+        # fp16 loss scaling (set by the precision plugin before every step): gradients are multiplied by
+        # `grad_scale` (= 1 / loss scale) INSIDE the fused update; a non-finite gradient norm skips the step
+        self.grad_scale: float = 1.0
+        self.skip_nonfinite: bool = False
+        self.last_step_skipped: bool = False
 
     # -- the user's optimizer stays the source of truth for hyper-parameters ---------------------------
     @property
@@ -124,23 +129,27 @@ class ShardedOptimizer(Optimizer):
         for e in self.engines:
             ns = e.grad_norm_sq(self.norm_extra_axes)
             norm_sq = ns if norm_sq is None else norm_sq.add_(ns)
-        self.last_grad_norm = norm_sq.sqrt() if norm_sq is not None else None
+        self.last_grad_norm = norm_sq.sqrt() * abs(self.grad_scale) if norm_sq is not None else None
+        self.last_step_skipped = False
+        if self.skip_nonfinite and norm_sq is not None and not bool(torch.isfinite(norm_sq).all()):
+            self.last_step_skipped = True          # overflow under fp16 loss scaling: leave weights and state alone
+            return loss
         self.step_count += 1
         max_norm = float(self.max_grad_norm) if self.max_grad_norm else 0.0
         if self.fused:
             g = self._optimizer.param_groups[0]
             hyper = dict(lr=g['lr'], beta1=g.get('betas', (0.9, 0.999))[0], beta2=g.get('betas', (0.9, 0.999))[1],
                          eps=g.get('eps', 1e-8), weight_decay=g.get('weight_decay', 0.0), step=self.step_count,
-                         max_norm=max_norm, norm_sq=norm_sq)
+                         max_norm=max_norm, norm_sq=norm_sq, grad_scale=self.grad_scale)
             if self._overlap_enabled():
                 self._step_overlapped(hyper)
                 return loss
             for e, u, st in self._units():
                 self._update_unit(e, u, st, hyper)
         else:
-            clip = 1.0
+            clip = self.grad_scale
             if max_norm > 0 and norm_sq is not None:
-                clip = torch.clamp(max_norm / (norm_sq.sqrt() + 1e-6), max=1.0)
+                clip = self.grad_scale * torch.clamp(max_norm / (norm_sq.sqrt() * abs(self.grad_scale) + 1e-6), max=1.0)
             for group, src in zip(self._generic.param_groups, self._optimizer.param_groups):
                 for k, v in src.items():
                     if k != 'params':

@@ -156,11 +156,11 @@ class NVLinkComm(Comm):
     def adamw_push(self, master: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor,
                    grad_shard: torch.Tensor, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, *,
                    lr: float, beta1: float, beta2: float, eps: float, weight_decay: float, step: int,
-                   max_norm: float, norm_sq: torch.Tensor | None) -> None:
+                   max_norm: float, norm_sq: torch.Tensor | None, grad_scale: float = 1.0) -> None:
         mc = arena.multicast_ptr + byte_offset if (arena.multicast_ptr and self.use_multicast) else 0
         _lib.check(self._lib.llmt_comm_adamw_push_mc(
             _lib.ptr(master), _lib.ptr(exp_avg), _lib.ptr(exp_avg_sq), _lib.ptr(grad_shard),
             arena.peer_ptrs_at(byte_offset), ctypes.c_void_p(mc), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
             _lib.c_int(grad_shard.dtype == torch.float32), _lib.c_f32(lr), _lib.c_f32(beta1), _lib.c_f32(beta2),
-            _lib.c_f32(eps), _lib.c_f32(weight_decay), _lib.c_int(step), _lib.c_f32(1.0), _lib.c_f32(max_norm),
+            _lib.c_f32(eps), _lib.c_f32(weight_decay), _lib.c_int(step), _lib.c_f32(grad_scale), _lib.c_f32(max_norm),
             _lib.ptr(norm_sq), _lib.stream()), 'comm_adamw_push')

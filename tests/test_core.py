@@ -370,3 +370,43 @@ data:
     trained = cli.model.model
     assert torch.allclose(hf.model.layers[1].mlp.down_proj.weight, trained.layers[1].mlp.down_proj.weight.detach())
     assert torch.allclose(hf.lm_head.weight, trained.lm_head.weight.detach())
+
+
+def test_fp16_mixed_dynamic_loss_scaling_skips_overflow_steps():
+    """`16-mixed`: the loss is scaled, the fused optimizer unscales inside its update, a non-finite gradient norm skips
+    the step and halves the scale (reference: GradScaler path of FSDP2Precision, fsdp2_precision.py:130-163; its
+    scaler is never created because of SURVEY B7)."""
+    from llm_training_b200.lightning import FSDP2Strategy, Trainer
+    from llm_training_b200.lms import CLM, CLMConfig
+    torch.manual_seed(0)
+    lm = CLM(CLMConfig.model_validate(dict(init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama', model_config=dict(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2, attn_implementation='sdpa')),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=1e-2)))))
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=1), precision='16-mixed', logger=False, enable_progress_bar=False, enable_checkpointing=False, gradient_clip_val=1.0, accelerator='cpu')
+    lm.trainer = trainer
+    trainer.lightning_module = lm
+    trainer.strategy.setup_environment(trainer)
+    with trainer.strategy.model_init_context():
+        lm.configure_model()
+    trainer.strategy.setup(trainer)
+    pp = trainer.strategy.precision_plugin
+    assert pp.scaler is not None and pp.scaler.get_scale() == 65536.0
+    ids = torch.randint(0, 128, (2, 32))
+    batch = dict(input_ids=ids, attention_mask=torch.ones_like(ids), position_ids=torch.arange(32)[None].expand(2, -1), labels=ids)
+    opt = trainer.optimizers[0]
+    losses = []
+    for i in range(8):
+        loss = trainer.strategy.training_step(batch, 0)
+        trainer.strategy.backward(loss)
+        if i == 3:   # inject an overflow
+            for e in trainer.strategy.engines:
+                e.units[0].flat_grad[0] = float('inf')
+        trainer.strategy.optimizer_step(opt)
+        opt.zero_grad()
+        losses.append(round(float(loss.detach()), 4))
+        if i == 3:
+            assert opt.last_step_skipped and pp.scaler.get_scale() == 32768.0 and pp.skipped_steps == 1
+        else:
+            assert not opt.last_step_skipped and float(opt.last_grad_norm) < 100      # norm is reported UNscaled
+    assert losses[4] == losses[3]          # the skipped step left the weights untouched
+    assert losses[-1] < losses[0]
