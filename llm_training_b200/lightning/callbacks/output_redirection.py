@@ -69,10 +69,15 @@ class OutputRedirection(Callback):
         if self.redirect_stderr:
             sys.stderr = _Tee(sys.stderr, self._file)
         if self.redirect_loggers:
-            self._handler = logging.StreamHandler(self._file)
-            self._handler.setFormatter(logging.Formatter('[%(asctime)s][%(levelname)s][%(name)s] %(message)s'))
-            for name in ('llm_training_b200', 'llm_training'):
-                logging.getLogger(name).addHandler(self._handler)
+            self._redirect_loggers()
+
+    def _redirect_loggers(self) -> None:
+        """Attach a handler writing to the log file to the package loggers (reference: ``redirect_loggers``,
+        output_redirection.py:60-73)."""
+        self._handler = logging.StreamHandler(self._file)
+        self._handler.setFormatter(logging.Formatter('[%(asctime)s][%(levelname)s][%(name)s] %(message)s'))
+        for name in ('llm_training_b200', 'llm_training'):
+            logging.getLogger(name).addHandler(self._handler)
 
     def teardown(self, trainer, pl_module, stage: str) -> None:
         if self._file is None:

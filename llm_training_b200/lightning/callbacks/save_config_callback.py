@@ -30,6 +30,10 @@ class SaveConfigCallback(Callback):
             self.yaml_config['slurm_job_name'] = os.environ.get('SLURM_JOB_NAME')
             self.yaml_config['slurm_num_nodes'] = os.environ.get('SLURM_NNODES')
             self.yaml_config['slurm_ntasks'] = os.environ.get('SLURM_NTASKS')
+        self.save_config(trainer, pl_module, stage)
+
+    def save_config(self, trainer, pl_module, stage: str) -> None:
+        """Write the YAML next to the logs and hand it to the logger (reference: save_config_callback.py:20-46)."""
         if trainer.is_global_zero and self.save_to_log_dir:
             logger = trainer.logger
             save_dir = getattr(logger, 'save_dir', None) or trainer.log_dir

@@ -49,6 +49,9 @@ class TrainingTimeEstimator(Callback):
         seconds = float(trainer.strategy.reduce(torch.tensor(self.end_time - self.start_time), reduce_op='max'))
         if seconds <= 0:
             return
+        self.print_estimated_training_time(trainer, seconds)
+
+    def print_estimated_training_time(self, trainer, seconds: float) -> None:
         steps = self.num_test_steps - self.num_warmup_steps
         self.steps_per_second = steps / seconds
         total_steps = trainer.estimated_stepping_batches

@@ -56,6 +56,48 @@ class BaseLightningModule(LightningModule):
     def grad_norm(self):
         return self._grad_norm
 
+    # ---- names of the reference's strategy queries / contexts (lms/base_lm.py:48-57, 91-93, 102-114, 195-222).
+    #      Both strategies run on the same native engine here, so the queries describe the sharding MODE.
+    @property
+    def is_using_ds_z3(self) -> bool:
+        from ..lightning.strategy import DeepSpeedStrategy
+        return isinstance(self.strategy, DeepSpeedStrategy) and self.strategy.zero_stage_3
+
+    @property
+    def is_using_fsdp(self) -> bool:
+        from ..lightning.strategy import FSDP2Strategy
+        return isinstance(self.strategy, FSDP2Strategy)
+
+    @property
+    def should_sync_weights(self) -> bool:
+        return self.should_load_pre_trained_weights or self.should_initialize_weights
+
+    @staticmethod
+    def shutdown_ds_init_context():
+        """DeepSpeed's ZeRO-3 init context has no counterpart: parameters are built whole and sharded in ``setup``."""
+        import contextlib
+        return contextlib.nullcontext()
+
+    def get_pre_trained_weights_context(self):
+        from ..utils.context_managers import ContextManagers
+        return ContextManagers([])
+
+    def configure_model_context(self):
+        """Context ``configure_model`` runs in: weight-init switch (+ the strategy's device / dtype context, which
+        the trainer enters around it)."""
+        return BaseModel.init_weights_context(self.should_initialize_weights)
+
+    def fsdp_parallelize_context(self):
+        """Records tied weights before parallelisation and re-ties them afterwards (reference :203-222)."""
+        import contextlib
+
+        @contextlib.contextmanager
+        def ctx():
+            tied = self._record_tied_weights()
+            yield
+            self._retie(tied)
+        return ctx()
+
     def get_model(self) -> BaseModel:
         raise NotImplementedError
 

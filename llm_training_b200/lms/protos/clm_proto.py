@@ -16,3 +16,7 @@ class CausalLMProto(Protocol):
     def get_input_embeddings(self) -> nn.Embedding: ...
 
     def get_output_embeddings(self) -> nn.Linear: ...
+
+    def set_input_embeddings(self, embed_tokens: nn.Embedding) -> None: ...
+
+    def set_output_embeddings(self, linear_module: nn.Linear) -> None: ...

@@ -149,6 +149,26 @@ def _eager_or_sdpa_attention(qkv: torch.Tensor, ctx: PackedContext, hq: int, hkv
     return o.transpose(1, 2).reshape(b * s, hq * d)
 
 
+def dense_core_attention(query_states: torch.Tensor, key_states: torch.Tensor, value_states: torch.Tensor,
+                         attention_mask: torch.Tensor | None, dropout_p: float = 0.0, training: bool = False,
+                         impl: str = 'eager') -> torch.Tensor:
+    """``[B, H, S, D]`` q / k / v (KV heads already repeated) + additive ``[B, 1, S, S]`` mask -> ``[B, S, H*D]``: the
+    contract of the reference's ``core_attention_forward`` (llama_model.py:506-537, phi3_model.py:436-480).  The
+    training path of this repository never materialises these tensors (``attention_core`` below)."""
+    p = dropout_p if training else 0.0
+    if impl == 'sdpa':
+        o = F.scaled_dot_product_attention(query_states, key_states, value_states, attn_mask=attention_mask, dropout_p=p)
+    else:
+        w = torch.matmul(query_states, key_states.transpose(2, 3)) / math.sqrt(query_states.shape[-1])
+        if attention_mask is not None:
+            w = w + attention_mask
+        w = F.softmax(w, dim=-1, dtype=torch.float32).to(value_states.dtype)
+        w = F.dropout(w, p=p, training=training)
+        o = torch.matmul(w, value_states)
+    b, h, s, d = o.shape
+    return o.transpose(1, 2).reshape(b, s, h * d)
+
+
 def attention_core(qkv: torch.Tensor, ctx: PackedContext, *, num_heads: int, num_kv_heads: int, head_dim: int,
                    impl: str, window: int | None = None, dropout_p: float = 0.0, training: bool = False,
                    selective_recompute: bool = False) -> torch.Tensor:

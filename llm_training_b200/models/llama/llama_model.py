@@ -22,7 +22,7 @@ from torch import nn
 from ...ops import (embedding, linear, multi_linear, neftune_noise_scale, norm_multi_linear, silu_mul_fused,
                     swiglu_down_linear)
 from ..decoder import (PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context,
-                       repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
+                       dense_core_attention, repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
 from .llama_config import LlamaConfig
@@ -90,6 +90,14 @@ class LlamaAttention(nn.Module):
         self.k_proj = nn.Linear(self.hidden_size, self.num_key_value_heads * self.head_dim, bias=bias)
         self.v_proj = nn.Linear(self.hidden_size, self.num_key_value_heads * self.head_dim, bias=bias)
         self.o_proj = nn.Linear(self.num_heads * self.head_dim, self.hidden_size, bias=bias)
+
+    def core_attention_forward(self, query_states: torch.Tensor, key_states: torch.Tensor,
+                               value_states: torch.Tensor, attention_mask: torch.Tensor | None) -> torch.Tensor:
+        """Dense attention on ``[B, H, S, D]`` tensors with a 4-D additive mask (the reference's method of the same
+        name); ``forward`` uses the packed kernels instead."""
+        impl = 'sdpa' if self.config._attn_implementation == 'sdpa' else 'eager'
+        return dense_core_attention(query_states, key_states, value_states, attention_mask,
+                                    getattr(self, 'attention_dropout', 0.0), self.training, impl)
 
     def forward(self, hidden_states: torch.Tensor, ctx: PackedContext, residual: torch.Tensor | None = None,
                 pre_norm: nn.Module | None = None) -> torch.Tensor:

@@ -15,7 +15,7 @@ from torch import nn
 
 from ...ops import embedding, linear, neftune_noise_scale, silu_mul_fused
 from ..decoder import (PackedContext, RMSNorm, RotaryEmbedding, attention_core, build_packed_context,
-                       repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
+                       dense_core_attention, repeat_kv)  # noqa: F401  (repeat_kv: public name of the reference's model modules)
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
 from .phi3_config import Phi3Config
@@ -52,6 +52,13 @@ class Phi3MLP(nn.Module):
         return linear(act, self.down_proj.weight, residual=residual)
 
 
+def fused_core_attention_forward(query_states: torch.Tensor, key_states: torch.Tensor, value_states: torch.Tensor,
+                                 attention_mask: torch.Tensor | None, dropout_p: float = 0.0,
+                                 training: bool = False) -> torch.Tensor:
+    """Name of the reference's ``torch.jit.script`` eager attention (phi3_model.py:436-480)."""
+    return dense_core_attention(query_states, key_states, value_states, attention_mask, dropout_p, training)
+
+
 class Phi3Attention(nn.Module):
     def __init__(self, config: Phi3Config, layer_idx: int | None = None) -> None:
         super().__init__()
@@ -69,6 +76,14 @@ class Phi3Attention(nn.Module):
         op_size = (self.num_heads + 2 * self.num_key_value_heads) * self.head_dim
         self.qkv_proj = nn.Linear(self.hidden_size, op_size, bias=False)
         self.o_proj = nn.Linear(self.num_heads * self.head_dim, self.hidden_size, bias=False)
+
+    def core_attention_forward(self, query_states: torch.Tensor, key_states: torch.Tensor,
+                               value_states: torch.Tensor, attention_mask: torch.Tensor | None) -> torch.Tensor:
+        """Dense attention on ``[B, H, S, D]`` tensors with a 4-D additive mask (the reference's method of the same
+        name); ``forward`` uses the packed kernels instead."""
+        impl = 'sdpa' if self.config._attn_implementation == 'sdpa' else 'eager'
+        return dense_core_attention(query_states, key_states, value_states, attention_mask,
+                                    getattr(self, 'attention_dropout', 0.0), self.training, impl)
 
     def forward(self, hidden_states: torch.Tensor, ctx: PackedContext, residual: torch.Tensor | None = None,
                 resid_pdrop: float = 0.0) -> torch.Tensor:

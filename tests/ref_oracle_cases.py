@@ -9,7 +9,9 @@ import torch
 def build_cases() -> dict:
     from llm_training.lr_schedulers import ConstantWarmupLR, LinearWarmupLR
     from llm_training.ops import apply_rope, rms_norm, shift_labels, swiglu
-    from llm_training.ops.attention_op import prepare_4d_causal_attention_mask
+    from llm_training.ops.attention_op import (get_max_seqlen_in_batch, get_sequence_indices,
+                                               prepare_4d_causal_attention_mask,
+                                               update_4d_causal_mask_for_packed_sequence)
     from llm_training.ops.rope_utils import ROPE_INIT_FUNCTIONS, RoPEConfig
 
     out: dict = {}
@@ -65,6 +67,12 @@ def build_cases() -> dict:
     # finfo.min), this repository lets a padding token see itself; their outputs never reach a loss
     m = prepare_4d_causal_attention_mask(seg, (2, 8), emb, 0)
     out['mask4d_packed_allowed'] = (m > -1.0).float() * (seg != 0)[:, None, :, None]
+    seg3 = torch.tensor([[1, 1, 1, 2, 2, 3, 0, 0], [1, 1, 1, 1, 1, 1, 1, 1], [2, 2, 1, 1, 0, 0, 0, 3]])
+    idx = get_sequence_indices(seg3)
+    out['sequence_indices'] = torch.tensor(idx)
+    out['doc_lengths'] = get_max_seqlen_in_batch(seg3)
+    base = torch.zeros(3, 1, 8, 8)
+    out['packed_mask_update'] = (update_4d_causal_mask_for_packed_sequence(base, idx) < -1.0).float()
     pad = torch.tensor([[1, 1, 1, 1, 1, 0, 0, 0], [1, 1, 1, 1, 1, 1, 1, 1]])
     m = prepare_4d_causal_attention_mask(pad, (2, 8), emb, 0)
     out['mask4d_padded_allowed'] = (m > -1.0).float() * (pad != 0)[:, None, :, None]
