@@ -109,6 +109,8 @@ def reference_arm(args) -> None:
 
 
 def main() -> None:
+    if os.environ.get('NCCL_DEBUG', '').upper() == 'VERSION':
+        os.environ['NCCL_DEBUG'] = 'WARN'      # keep stdout to the ONE JSON line (NCCL prints its version there)
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=5)
