@@ -160,6 +160,16 @@ def _load_optimizer_states(strategy, entries: dict[str, torch.Tensor], metas: li
 
 def load_checkpoint(strategy, filepath: str) -> dict[str, Any]:
     filepath = strategy.broadcast(filepath)
+    if os.path.isdir(filepath) and (os.path.exists(os.path.join(filepath, 'latest'))
+                                    or os.path.isdir(os.path.join(filepath, 'checkpoint'))):
+        # a checkpoint the reference wrote under DeepSpeed (stage <= 2): weights and loop state are restored, the
+        # optimizer state (DeepSpeed's own partition files) is rebuilt from the weights
+        state, rest = _read_deepspeed_checkpoint(filepath)
+        _load_module_state(strategy, state)
+        logger.warning('resuming from a DeepSpeed checkpoint: optimizer state is rebuilt (fp32 masters from the '
+                       'loaded weights, zero moments)')
+        _load_optimizer_states(strategy, {}, [])
+        return rest
     if os.path.isdir(filepath):
         dcp = _dcp()
         meta = torch.load(os.path.join(filepath, 'meta.pt'), map_location='cpu', weights_only=False)
@@ -189,14 +199,40 @@ def load_checkpoint(strategy, filepath: str) -> dict[str, Any]:
     return ckpt
 
 
+def _read_deepspeed_checkpoint(path: str) -> tuple[dict[str, torch.Tensor], dict[str, Any]]:
+    """Checkpoints written by the REFERENCE under its DeepSpeed strategy (six of its eight example configs, stage 2):
+    a directory with ``latest`` (tag) and ``<tag>/mp_rank_00_model_states.pt`` whose ``module`` entry is the full
+    bf16 state dict under the Lightning wrapper prefix ``_forward_module.``; the Lightning client state (loops,
+    callbacks, the embedded ``config``) sits next to it in the same file.  DeepSpeed itself is not needed to read
+    it.  ZeRO-3 checkpoints keep only placeholders in ``module`` (the weights are the fp32 partitions of the optimizer
+    files): convert those with DeepSpeed's ``zero_to_fp32.py`` first."""
+    tag = 'checkpoint'
+    latest = os.path.join(path, 'latest')
+    if os.path.exists(latest):
+        tag = open(latest).read().strip() or tag
+    states = os.path.join(path, tag, 'mp_rank_00_model_states.pt')
+    if not os.path.exists(states):
+        raise FileNotFoundError(f'{path}: DeepSpeed checkpoint without {tag}/mp_rank_00_model_states.pt')
+    blob = torch.load(states, map_location='cpu', weights_only=False)
+    module = blob.pop('module', None)
+    if not module:
+        raise ValueError(f'{states} has no `module` state dict')
+    placeholders = [k for k, v in module.items() if torch.is_tensor(v) and v.numel() == 0]
+    if len(placeholders) > len(module) // 2:
+        raise ValueError(f'{path} is a ZeRO-3 checkpoint (parameters are partitioned into the optimizer files); '
+                         "run DeepSpeed's zero_to_fp32.py on it first")
+    prefix = '_forward_module.'
+    state = {(k[len(prefix):] if k.startswith(prefix) else k): v for k, v in module.items()}
+    return state, blob
+
+
 def read_checkpoint_state_dict(path: str) -> tuple[dict[str, torch.Tensor], dict[str, Any]]:
     """Stand-alone reader for tools (``convert_to_hf.py``): returns (model state dict, rest of checkpoint).
-    Handles a DCP directory with ``meta.pt``, a single file, and a DeepSpeed-style directory is rejected with
-    a clear message (DeepSpeed is not a dependency)."""
+    Handles a DCP directory with ``meta.pt``, a single file, and the DeepSpeed engine directories the reference's
+    ZeRO-1/2 configs write (``<ckpt>/latest`` + ``<tag>/mp_rank_00_model_states.pt``)."""
     if os.path.isdir(path):
         if os.path.exists(os.path.join(path, 'latest')) or os.path.isdir(os.path.join(path, 'checkpoint')):
-            raise ValueError(f'{path} looks like a DeepSpeed engine checkpoint; this framework writes DCP '
-                             'directories or single files (use DeepSpeed\'s zero_to_fp32.py first)')
+            return _read_deepspeed_checkpoint(path)
         dcp = _dcp()
         reader = dcp.FileSystemReader(path)
         md = reader.read_metadata()

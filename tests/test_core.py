@@ -410,3 +410,26 @@ def test_fp16_mixed_dynamic_loss_scaling_skips_overflow_steps():
             assert not opt.last_step_skipped and float(opt.last_grad_norm) < 100      # norm is reported UNscaled
     assert losses[4] == losses[3]          # the skipped step left the weights untouched
     assert losses[-1] < losses[0]
+
+
+def test_reads_reference_deepspeed_zero2_checkpoint_directory(tmp_path):
+    """The directory layout the reference writes under its DeepSpeed strategy (stage <= 2) is readable without
+    DeepSpeed; a ZeRO-3 directory (placeholder tensors in `module`) is rejected with a pointer to zero_to_fp32.py."""
+    import os
+    from llm_training_b200.lightning.checkpoint_io import read_checkpoint_state_dict
+    ckpt = tmp_path / 'epoch=0-step=10.ckpt'
+    os.makedirs(ckpt / 'checkpoint')
+    (ckpt / 'latest').write_text('checkpoint')
+    weights = {'_forward_module.model.embed_tokens.weight': torch.randn(8, 4),
+               '_forward_module.model.norm.weight': torch.ones(4)}
+    torch.save({'module': weights, 'config': {'trainer': {'precision': 'bf16-true'}}, 'global_step': 10},
+               ckpt / 'checkpoint' / 'mp_rank_00_model_states.pt')
+    state, rest = read_checkpoint_state_dict(str(ckpt))
+    assert set(state) == {'model.embed_tokens.weight', 'model.norm.weight'}
+    assert torch.equal(state['model.norm.weight'], torch.ones(4)) and rest['global_step'] == 10 and 'config' in rest
+    z3 = tmp_path / 'z3.ckpt'
+    os.makedirs(z3 / 'checkpoint')
+    (z3 / 'latest').write_text('checkpoint')
+    torch.save({'module': {k: torch.empty(0) for k in weights}}, z3 / 'checkpoint' / 'mp_rank_00_model_states.pt')
+    with pytest.raises(ValueError, match='zero_to_fp32'):
+        read_checkpoint_state_dict(str(z3))
