@@ -213,3 +213,58 @@ def test_tensor_sequence_parallel_matches_single_process(model_kind, dp, tp, res
         diff = (full[n] - p.detach()).abs()
         # Adam turns round-off in near-zero gradients into O(lr) differences for a handful of elements
         assert diff.max().item() < 2e-3 and (diff > 5e-5).float().mean().item() < 1e-3, (n, diff.max().item())
+
+
+# ---------------------------------------------------------------------------------------------------
+# BASELINE config 1: tiny LLaMA (2 layers, d=256) pre-training with best-fit bin packing, CPU/gloo, world_size=2
+# ---------------------------------------------------------------------------------------------------
+def _config1_worker(rank: int, world: int, data_path: str, tmpdir: str):
+    import datasets
+    from llm_training_b200.data import PreTrainingDataModule, PreTrainingDataModuleConfig
+    from llm_training_b200.lightning import FSDP2Strategy, Trainer, seed_everything
+    from llm_training_b200.lms import CLM, CLMConfig
+    from tests.helpers import tiny_tokenizer
+    seed_everything(7)
+
+    class DM(PreTrainingDataModule):
+        def load_data(self):
+            return datasets.DatasetDict({'train': datasets.load_from_disk(data_path)})
+
+    dm = DM(PreTrainingDataModuleConfig(tokenizer=tiny_tokenizer(), max_length=48,
+                                        packing_method='best_fit_bin_packing', batch_size=2, pin_memory=False,
+                                        enable_cache=False, num_workers=0))
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama',
+                   model_config=dict(vocab_size=256, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                                     num_attention_heads=4, num_key_value_heads=2, attn_implementation='sdpa')),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=3e-3)))))
+    losses = []
+
+    class Record:
+        def on_train_batch_end(self, trainer, module, outputs, batch, batch_idx):
+            losses.append(float(outputs.detach()))
+
+    from llm_training_b200.lightning import Callback
+    rec = type('Rec', (Callback,), {'on_train_batch_end': Record.on_train_batch_end})()
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world), precision='32-true', logger=False,
+                      enable_progress_bar=False, enable_checkpointing=False, max_steps=6, gradient_clip_val=1.0,
+                      accelerator='cpu', default_root_dir=tmpdir, callbacks=[rec])
+    trainer.fit(lm, dm)
+    packed = dm.dataset_dict['train']
+    return losses, [len(x) for x in packed['input_ids']], {n: p.detach().clone() for n, p in lm.named_parameters()}
+
+
+def test_baseline_config1_best_fit_packing_pretraining_two_ranks(tmp_path):
+    import datasets
+    texts = [' '.join(f'w{(i * 13 + j) % 200}' for j in range(4 + (i * 5) % 23)) for i in range(96)]
+    data_path = str(tmp_path / 'raw')
+    datasets.Dataset.from_dict({'text': texts}).save_to_disk(data_path)
+    two = run_distributed(_config1_worker, world=2, args=(data_path, str(tmp_path / 'w2')), timeout=600)
+    losses0, rows, params0 = two[0]
+    losses1, _, params1 = two[1]
+    assert max(rows) <= 48 and sum(r > 40 for r in rows) >= len(rows) // 2      # best-fit bins are well filled
+    assert len(losses0) == 6 and losses0[-1] < losses0[0] and losses1[-1] < losses1[0]
+    assert losses0 != losses1                                                    # the ranks saw different rows
+    for n, p in params0.items():                                                 # and hold identical weights
+        assert torch.equal(p, params1[n]), n
