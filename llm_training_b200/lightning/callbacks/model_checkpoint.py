@@ -72,6 +72,13 @@ class ModelCheckpoint(Callback):
         self._last_step_saved = trainer.global_step
         self.last_model_path = path
         self.saved.append(path)
+        if self.save_last:
+            # Lightning's `last.ckpt`: always the most recent state, whatever top-k keeps
+            last = os.path.join(self.dirpath, 'last' + self.FILE_EXTENSION)
+            trainer.strategy.remove_checkpoint(last)
+            trainer.strategy.barrier()
+            trainer.save_checkpoint(last)
+            self.last_model_path = last
         if self.monitor and score is not None:
             self.best_k[path] = score
             pick = min if self.mode == 'min' else max

@@ -433,3 +433,55 @@ def test_reads_reference_deepspeed_zero2_checkpoint_directory(tmp_path):
     torch.save({'module': {k: torch.empty(0) for k in weights}}, z3 / 'checkpoint' / 'mp_rank_00_model_states.pt')
     with pytest.raises(ValueError, match='zero_to_fp32'):
         read_checkpoint_state_dict(str(z3))
+
+
+def test_model_checkpoint_top_k_monitor_and_save_last(tmp_path):
+    """`save_top_k` with and without a monitored metric, `save_last`, Lightning's `epoch=E-step=S.ckpt` naming."""
+    import os
+    from llm_training_b200.lightning import ModelCheckpoint
+
+    class FakeStrategy:
+        def broadcast(self, obj, src=0):
+            return obj
+
+        def barrier(self, name=None):
+            pass
+
+        def remove_checkpoint(self, path):
+            if os.path.exists(path):
+                os.remove(path)
+
+    class FakeTrainer:
+        def __init__(self):
+            self.strategy, self.is_global_zero, self.log_dir = FakeStrategy(), True, str(tmp_path / 'logs')
+            self.current_epoch, self.global_step, self.callback_metrics, self.training = 0, 0, {}, True
+
+        def _resolve(self, v):
+            return float(v)
+
+        def save_checkpoint(self, path):
+            open(path, 'w').write(str(self.global_step))
+
+    trainer = FakeTrainer()
+    plain = ModelCheckpoint(every_n_train_steps=2, save_top_k=2, save_last=True)
+    plain.setup(trainer, None, 'fit')
+    assert plain.dirpath == os.path.join(trainer.log_dir, 'checkpoints')
+    for step in range(1, 9):
+        trainer.global_step = step
+        plain.on_train_batch_end(trainer, None, None, None, step - 1)
+    names = sorted(os.listdir(plain.dirpath))
+    assert names == ['epoch=0-step=6.ckpt', 'epoch=0-step=8.ckpt', 'last.ckpt'], names     # two newest + last
+    assert open(os.path.join(plain.dirpath, 'last.ckpt')).read() == '8'
+
+    best = ModelCheckpoint(dirpath=str(tmp_path / 'best'), monitor='val_loss', mode='min', save_top_k=2,
+                           filename='{step}-{val_loss:.2f}')
+    best.setup(trainer, None, 'fit')
+    trainer.training = False
+    for step, loss in ((10, 3.0), (20, 2.0), (30, 2.5), (40, 4.0), (50, 1.0)):
+        trainer.global_step, trainer.callback_metrics = step, {'val_loss': loss}
+        best.on_validation_end(trainer, None)
+    assert sorted(os.listdir(best.dirpath)) == ['step=20-val_loss=2.00.ckpt', 'step=50-val_loss=1.00.ckpt']
+    assert best.best_model_path.endswith('step=50-val_loss=1.00.ckpt')
+    restored = ModelCheckpoint(dirpath=str(tmp_path / 'best'), monitor='val_loss', save_top_k=2)
+    restored.load_state_dict(best.state_dict())
+    assert restored.best_k == best.best_k and restored.best_model_path == best.best_model_path
