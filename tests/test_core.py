@@ -485,3 +485,19 @@ def test_model_checkpoint_top_k_monitor_and_save_last(tmp_path):
     restored = ModelCheckpoint(dirpath=str(tmp_path / 'best'), monitor='val_loss', save_top_k=2)
     restored.load_state_dict(best.state_dict())
     assert restored.best_k == best.best_k and restored.best_model_path == best.best_model_path
+
+
+def test_wandb_logger_directory_convention_and_local_mirror(tmp_path):
+    """``save_dir == log_dir == <save_dir>/<project>/<name>`` (reference: lightning/loggers/wandb.py:58-72), created
+    lazily; metrics are mirrored to ``metrics.jsonl`` so a run without network still leaves a record."""
+    import json
+    import os
+    from llm_training_b200.lightning.loggers.wandb import WandbLogger, _NullRun
+    lg = WandbLogger(name='run-a', project='proj', save_dir=str(tmp_path), experiment=_NullRun(), prefix='train/')
+    assert not os.path.exists(tmp_path / 'proj')                       # nothing created before first use
+    assert lg.save_dir == lg.log_dir == str(tmp_path / 'proj' / 'run-a') and os.path.isdir(lg.log_dir)
+    lg.log_hyperparams({'lr': 1e-3})
+    lg.log_metrics({'Loss': 2.5}, step=3)
+    lg.finalize('success')
+    rows = [json.loads(l) for l in open(os.path.join(lg.log_dir, 'metrics.jsonl'))]
+    assert rows[0] == {'hparams': {'lr': 1e-3}} and rows[1] == {'step': 3, 'train/Loss': 2.5}
