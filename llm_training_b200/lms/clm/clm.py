@@ -107,7 +107,21 @@ class CLM(BaseLightningModule):
                                                   self.config.ignore_index)
         else:
             loss = self.compute_loss(outputs.logits.float(), labels)
-        return loss, labels
+        return self._normalize_over_data_parallel_ranks(loss, labels), labels
+
+    def _normalize_over_data_parallel_ranks(self, loss: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """``loss_normalization='global_tokens'``: turn the rank-local token mean into this rank's share of the mean
+        over ALL valid tokens of the data-parallel step, so that the gradient average over ranks equals the gradient
+        of the global token mean (ranks with few valid tokens no longer count as much as full ones)."""
+        strategy = self.strategy
+        if self.config.loss_normalization != 'global_tokens' or strategy is None or strategy.dp_size <= 1 \
+                or not torch.is_grad_enabled():
+            return loss
+        import torch.distributed as dist
+        n_local = labels.ne(self.config.ignore_index).sum().to(torch.float32)
+        n_global = n_local.clone()
+        dist.all_reduce(n_global, group=strategy.dp_mesh.get_group())
+        return loss * (n_local * strategy.dp_size / n_global.clamp_min(1.0))
 
     def training_step(self, batch: dict[str, torch.Tensor | Any], batch_idx: int) -> torch.Tensor:
         loss, labels = self._forward_loss(batch)

@@ -268,3 +268,65 @@ def test_baseline_config1_best_fit_packing_pretraining_two_ranks(tmp_path):
     assert losses0 != losses1                                                    # the ranks saw different rows
     for n, p in params0.items():                                                 # and hold identical weights
         assert torch.equal(p, params1[n]), n
+
+
+def _global_tokens_worker(rank: int, world: int, mode: str):
+    from llm_training_b200.lightning import FSDP2Strategy, Trainer, seed_everything
+    from llm_training_b200.lms import CLM, CLMConfig
+    seed_everything(3)
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False, loss_normalization=mode,
+        model=dict(model_class='llm_training.models.Llama', model_config=TINY),
+        optim=dict(optimizer_class='torch.optim.SGD', optimizer_kwargs=dict(lr=0.1)))))
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world), precision='32-true', logger=False,
+                      enable_progress_bar=False, enable_checkpointing=False, accelerator='cpu')
+    lm.trainer = trainer
+    trainer.lightning_module = lm
+    trainer.strategy.setup_environment(trainer)
+    with trainer.strategy.model_init_context():
+        lm.configure_model()
+    trainer.strategy.setup(trainer)
+    ids = _batch(77, rows=2, seq=24)[rank:rank + 1]
+    labels = ids.clone()
+    if rank == 1:
+        labels[:, :20] = -100                       # rank 1 has 4 valid tokens, rank 0 has 24
+    batch = dict(input_ids=ids, attention_mask=torch.ones_like(ids), position_ids=torch.arange(24)[None], labels=labels)
+    loss = trainer.strategy.training_step(batch, 0)
+    trainer.strategy.backward(loss)
+    trainer.strategy.optimizer_step(trainer.optimizers[0])
+    with trainer.strategy.engines[0].unsharded():
+        return {n: p.detach().clone() for n, p in lm.model.named_parameters()}
+
+
+@pytest.mark.parametrize('mode', ['micro_batch', 'global_tokens'])
+def test_loss_normalization_over_data_parallel_ranks(mode):
+    """`micro_batch` reproduces the reference (mean of the ranks' means); `global_tokens` equals the single-process
+    mean over all valid tokens of the step."""
+    from llm_training_b200.lightning import seed_everything
+    from llm_training_b200.ops import shift_labels
+    results = run_distributed(_global_tokens_worker, world=2, args=(mode,))
+    seed_everything(3)
+    ref = _make_model_seeded()
+    ids = _batch(77, rows=2, seq=24)
+    labels = ids.clone()
+    labels[1, :20] = -100
+    logits = ref(input_ids=ids).logits.float()
+    shifted = shift_labels(labels)
+    per_row = [torch.nn.functional.cross_entropy(logits[r], shifted[r], ignore_index=-100, reduction='sum')
+               for r in range(2)]
+    counts = [(shifted[r] != -100).sum() for r in range(2)]
+    if mode == 'micro_batch':
+        loss = (per_row[0] / counts[0] + per_row[1] / counts[1]) / 2
+    else:
+        loss = (per_row[0] + per_row[1]) / (counts[0] + counts[1])
+    loss.backward()
+    with torch.no_grad():
+        for p in ref.parameters():
+            p -= 0.1 * p.grad
+    for n, p in ref.named_parameters():
+        assert torch.allclose(results[0][n], p.detach(), atol=2e-5, rtol=1e-4), (mode, n)
+
+
+def _make_model_seeded():
+    from llm_training_b200.models import Llama, LlamaConfig
+    return Llama(LlamaConfig(**TINY))
