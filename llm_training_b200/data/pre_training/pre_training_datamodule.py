@@ -176,11 +176,21 @@ class PreTrainingDataModule(HFBasedDataModule):
             dataset_dict['train'] = self.sample_data(dataset_dict['train'])
         return dataset_dict
 
-    def token_table(self) -> str:
+    def print_dataset_info(self, file: Any = None) -> None:
+        """Dataset summaries plus the token counts before and after per-source sampling (reference :346-360)."""
+        import shutil
+        super().print_dataset_info(file)
+        print('─' * shutil.get_terminal_size().columns, end='\n\n', file=file)
+        print('Original Tokens:', end='\n\n', file=file)
+        print(self.token_table(self.pre_processed_dataset_dict), end='\n\n', file=file)
+        print('Sampled Tokens:', end='\n\n', file=file)
+        print(self.token_table(self.dataset_dict), file=file)
+
+    def token_table(self, dataset_dict: Any = None) -> str:
         """Per-split / per-source document and token counts (reference :312-360)."""
         from tabulate import tabulate
         rows = []
-        for split, ds in (self.dataset_dict or {}).items():
+        for split, ds in ((dataset_dict if dataset_dict is not None else self.dataset_dict) or {}).items():
             counts: dict[Any, list[int]] = {}
             for source, n in zip(ds['source'], ds['length']):
                 c = counts.setdefault(source, [0, 0])

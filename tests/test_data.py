@@ -187,3 +187,52 @@ def test_dummy_dataset_and_resumable_loader():
     resumed = [b['input_ids'] for b in dm.train_dataloader()]
     assert len(resumed) == len(full) - 3
     assert all(torch.equal(a, b) for a, b in zip(full[3:], resumed))     # same order, first 3 skipped
+
+
+def test_pre_process_data_script_then_training_datamodule_loads_the_result(tmp_path):
+    """scripts/pre_process_data.py (reference: scripts/pre_process_data.py:25-47): tokenise + pack once, store at
+    `pre_processed_data_path` with `info.txt`; a datamodule pointed at that path then skips all pre-processing."""
+    import json
+    import os
+    import subprocess
+    import sys
+    tok_dir = tmp_path / 'tok'
+    tiny_tokenizer().save_pretrained(str(tok_dir))
+    raw = tmp_path / 'raw.jsonl'
+    with open(raw, 'w') as f:
+        for i in range(40):
+            f.write(json.dumps({'text': ' '.join(f'w{(i * 3 + j) % 200}' for j in range(5 + i % 11))}) + '\n')
+    target = tmp_path / 'processed'
+    cfg = tmp_path / 'cfg.yaml'
+    cfg.write_text(f"""
+trainer: {{}}
+model: {{}}
+data:
+  class_path: llm_training.data.PreTrainingDataModule
+  init_args.config:
+    dataset_kwargs:
+      path: json
+      data_files: {raw}
+    pre_processed_data_path: {target}
+    tokenizer:
+      class_path: HFTokenizer
+      init_args:
+        path: {tok_dir}
+    packing_method: best_fit_bin_packing
+    max_length: 32
+    batch_size: 2
+    enable_cache: false
+""")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, HF_DATASETS_OFFLINE='1', HF_HUB_OFFLINE='1')
+    proc = subprocess.run([sys.executable, os.path.join(root, 'scripts', 'pre_process_data.py'), '--config', str(cfg)],
+                          capture_output=True, text=True, timeout=600, env=env)
+    assert proc.returncode == 0, proc.stderr[-2000:]
+    assert (target / 'info.txt').exists() and 'tokens' in (target / 'info.txt').read_text().lower()
+    from llm_training_b200.lightning.cli.config import instantiate, load_config
+    dm = instantiate(load_config([str(cfg)])['data'])
+    dm.load_data = lambda: (_ for _ in ()).throw(AssertionError('raw data must not be read again'))
+    dm.setup()
+    assert max(dm.dataset_dict['train']['length']) <= 32
+    batch = next(iter(dm.train_dataloader()))
+    assert batch['input_ids'].shape[0] == 2
