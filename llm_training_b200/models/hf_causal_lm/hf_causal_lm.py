@@ -44,8 +44,17 @@ class HFCausalLM(HFCompatModel):
     def forward(self, input_ids: torch.Tensor | None = None, attention_mask: torch.Tensor | None = None,
                 position_ids: torch.Tensor | None = None, inputs_embeds: torch.Tensor | None = None,
                 return_last_hidden_states: bool = False, skip_logits: bool = False) -> CausalLMOutput:
-        if attention_mask is not None:
-            attention_mask = attention_mask.clamp_max(1)   # HF modules understand 0/1 masks only
+        if attention_mask is not None and attention_mask.dim() == 2:
+            if bool((attention_mask > 1).any()):
+                # packed batch (segment ids 1, 2, 3, ...): HF modules only know 0/1 masks, so hand them the
+                # block-diagonal causal 4-D mask instead — documents of a pack stay isolated.  The reference gets the
+                # same effect by monkey-patching HF's `_get_unpad_data` for flash-attn (hf_causal_lm.py:40-60).
+                from ...ops import prepare_4d_causal_attention_mask
+                ref = inputs_embeds if inputs_embeds is not None else self.get_input_embeddings().weight
+                attention_mask = prepare_4d_causal_attention_mask(
+                    attention_mask, tuple(attention_mask.shape), torch.empty(0, dtype=ref.dtype, device=ref.device), 0)
+            else:
+                attention_mask = attention_mask.clamp_max(1)
         outputs = self.hf_model(input_ids=input_ids, attention_mask=attention_mask, position_ids=position_ids,
                                 inputs_embeds=inputs_embeds, output_hidden_states=return_last_hidden_states)
         last = outputs.hidden_states[-1] if return_last_hidden_states else None

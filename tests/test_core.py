@@ -501,3 +501,21 @@ def test_wandb_logger_directory_convention_and_local_mirror(tmp_path):
     lg.finalize('success')
     rows = [json.loads(l) for l in open(os.path.join(lg.log_dir, 'metrics.jsonl'))]
     assert rows[0] == {'hparams': {'lr': 1e-3}} and rows[1] == {'step': 3, 'train/Loss': 2.5}
+
+
+def test_hf_causal_lm_keeps_packed_documents_isolated():
+    """Segment-id masks through the HF wrapper: a packed row gives every document the logits it gets alone."""
+    from transformers import LlamaConfig as HFLlamaConfig
+    from llm_training_b200.models import HFCausalLM, HFCausalLMConfig
+    torch.manual_seed(0)
+    model = HFCausalLM(HFCausalLMConfig(hf_config=HFLlamaConfig(
+        vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+        num_key_value_heads=2, attn_implementation='sdpa'))).eval()
+    ids = torch.randint(0, 128, (1, 12))
+    seg = torch.tensor([[1] * 5 + [2] * 4 + [0] * 3])
+    pos = torch.tensor([[0, 1, 2, 3, 4, 0, 1, 2, 3, 0, 0, 0]])
+    with torch.no_grad():
+        packed = model(input_ids=ids, attention_mask=seg, position_ids=pos).logits
+        first = model(input_ids=ids[:, :5], attention_mask=torch.ones(1, 5, dtype=torch.long)).logits
+        second = model(input_ids=ids[:, 5:9], attention_mask=torch.ones(1, 4, dtype=torch.long)).logits
+    assert torch.allclose(packed[:, :5], first, atol=1e-5) and torch.allclose(packed[:, 5:9], second, atol=1e-5)
