@@ -35,6 +35,15 @@ def init_on_device(device: torch.device | str, include_buffers: bool = False):
         if tensor is not None and tensor.device != device:
             module._buffers[name] = module._buffers[name].to(device)
 
+    if device.type == 'meta':
+        # transformers snapshots the torch.nn.init functions when its modelling modules are first imported; make
+        # sure that happens BEFORE they are replaced below, or every later Hugging Face model of the process would
+        # be "initialised" by the no-ops
+        for mod in ('transformers.modeling_utils', 'transformers.initialization'):
+            try:
+                __import__(mod)
+            except Exception:  # noqa: BLE001 -- transformers absent or the module does not exist in this version
+                pass
     saved_inits = {fn: getattr(nn.init, fn) for fn in _INIT_FNS if hasattr(nn.init, fn)}
 
     def _noop(tensor, *args, **kwargs):
