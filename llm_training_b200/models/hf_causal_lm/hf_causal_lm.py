@@ -12,6 +12,38 @@ from ..utils.modeling_outputs import CausalLMOutput
 from .hf_causal_lm_config import HFCausalLMConfig
 
 
+def patch_hf_modules_with_in_tree_kernels(model: nn.Module) -> int:
+    """``enable_liger_kernel`` of the reference patches Hugging Face modules with Liger's Triton kernels
+    (hf_causal_lm.py:62-86).  Here the same switch routes every RMSNorm and every SiLU-gated MLP of the wrapped model
+    through the in-tree ops (sm_100a kernels on GPU, the fp32 restatements on CPU); modules that do not match the
+    expected layout are left untouched.  Returns the number of patched modules."""
+    import types
+
+    from ...ops import linear, rms_norm, silu_mul
+
+    def norm_forward(self, hidden_states):
+        eps = getattr(self, 'variance_epsilon', None)
+        return rms_norm(hidden_states, self.weight, eps if eps is not None else getattr(self, 'eps', 1e-6))
+
+    def mlp_forward(self, x):
+        gate = linear(x, self.gate_proj.weight, self.gate_proj.bias)
+        up = linear(x, self.up_proj.weight, self.up_proj.bias)
+        return linear(silu_mul(gate, up), self.down_proj.weight, self.down_proj.bias)
+
+    patched = 0
+    for module in model.modules():
+        name = type(module).__name__
+        if name.endswith('RMSNorm') and isinstance(getattr(module, 'weight', None), nn.Parameter) \
+                and (hasattr(module, 'variance_epsilon') or hasattr(module, 'eps')) and 'Gemma' not in name:
+            module.forward = types.MethodType(norm_forward, module)      # Gemma scales by (1 + w): not this formula
+            patched += 1
+        elif all(isinstance(getattr(module, n, None), nn.Linear) for n in ('gate_proj', 'up_proj', 'down_proj')) \
+                and type(getattr(module, 'act_fn', None)).__name__ in ('SiLU', 'SiLUActivation'):
+            module.forward = types.MethodType(mlp_forward, module)
+            patched += 1
+    return patched
+
+
 class HFCausalLM(HFCompatModel):
     config: HFCausalLMConfig
     config_class = HFCausalLMConfig
@@ -28,6 +60,8 @@ class HFCausalLM(HFCompatModel):
             self.hf_config = self.config.hf_config
         self.config.hf_config = self.hf_config
         self.hf_model = self.construct_hf_model()
+        if self.config.enable_liger_kernel:
+            self.patched_modules = patch_hf_modules_with_in_tree_kernels(self.hf_model)
         if self.config.enable_gradient_checkpointing:
             self.hf_model.gradient_checkpointing_enable({'use_reentrant': False})
         self.hf_model.tie_weights()

@@ -6,7 +6,7 @@ from ..hf_compat_model import HFCompatModelConfig
 
 class HFCausalLMConfig(HFCompatModelConfig):
     enable_gradient_checkpointing: bool = False
-    enable_liger_kernel: bool = False   # accepted for config compatibility; Liger is not a dependency
+    enable_liger_kernel: bool = False   # route the HF model's RMSNorm / SwiGLU MLP modules through the in-tree ops
 
     hf_config: Any | None = None
 

@@ -519,3 +519,25 @@ def test_hf_causal_lm_keeps_packed_documents_isolated():
         first = model(input_ids=ids[:, :5], attention_mask=torch.ones(1, 5, dtype=torch.long)).logits
         second = model(input_ids=ids[:, 5:9], attention_mask=torch.ones(1, 4, dtype=torch.long)).logits
     assert torch.allclose(packed[:, :5], first, atol=1e-5) and torch.allclose(packed[:, 5:9], second, atol=1e-5)
+
+
+def test_hf_causal_lm_in_tree_kernel_patching_preserves_outputs():
+    """`enable_liger_kernel: true` (reference: Liger patching of HF modules) swaps RMSNorm / SwiGLU MLP forwards for
+    the in-tree ops; logits and gradients are unchanged."""
+    from transformers import LlamaConfig as HFLlamaConfig
+    from llm_training_b200.models import HFCausalLM, HFCausalLMConfig
+    hf_cfg = HFLlamaConfig(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                           num_attention_heads=4, num_key_value_heads=2, attn_implementation='sdpa')
+    torch.manual_seed(0)
+    plain = HFCausalLM(HFCausalLMConfig(hf_config=hf_cfg))
+    torch.manual_seed(0)
+    patched = HFCausalLM(HFCausalLMConfig(hf_config=hf_cfg, enable_liger_kernel=True))
+    assert patched.patched_modules == 2 * 2 + 1 + 2          # two norms + one MLP per layer, the final norm
+    patched.load_state_dict(plain.state_dict())
+    ids = torch.randint(0, 128, (2, 10))
+    a, b = plain(input_ids=ids).logits, patched(input_ids=ids).logits
+    assert torch.allclose(a, b, atol=1e-5)
+    a.float().pow(2).mean().backward()
+    b.float().pow(2).mean().backward()
+    for (n, p), (_, q) in zip(plain.named_parameters(), patched.named_parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-5), n
