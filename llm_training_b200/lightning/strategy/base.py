@@ -220,7 +220,7 @@ class Strategy:
         if self.tp_size > 1:
             extra.append(get_comm(self.tp_mesh, 'torch'))
         wrapped = ShardedOptimizer(optimizer, self.engines, max_grad_norm=trainer.gradient_clip_val,
-                                   norm_extra_axes=extra)
+                                   norm_extra_axes=extra, offload=self.offload_optimizer_state)
         sched_cfgs = []
         if sched is not None:
             cfg = sched if isinstance(sched, dict) else {'scheduler': sched}
@@ -292,6 +292,12 @@ class Strategy:
     save_distributed_checkpoint: bool = False
     # measured on 1, 2 and 8 B200s (profiles/bench_8gpu*_r1_final.log): no gain beyond noise, the step is power /
     # HBM bound and the push is already short; available with LLMT_OVERLAP_OPT=1 or by setting the attribute
+    @property
+    def offload_optimizer_state(self) -> bool:
+        """fp32 masters + Adam moments in host memory (FSDP2 ``CPUOffloadPolicy`` / DeepSpeed ``offload_optimizer``)."""
+        policy = getattr(self, 'offload_policy', None)
+        return type(policy).__name__ == 'CPUOffloadPolicy' or bool(getattr(self, 'offload_optimizer', False))
+
     overlap_optimizer_step: bool = os.environ.get('LLMT_OVERLAP_OPT', '0') == '1'
 
     def save_checkpoint(self, checkpoint: dict[str, Any], filepath: str) -> None:

@@ -9,7 +9,8 @@ dependency here — the constructor accepts the same arguments and maps them ont
                    place by the optimizer kernel after the step
   stage 3       -> the engine's resharding mode (``reshard_after_forward=True``): parameters and gradients exist
                    whole only around a unit's forward / backward (parallel/fsdp.py)
-  offload_* / nvme / bucket sizes / hpZ / quantised comm -> accepted, not needed on this hardware (logged)
+  offload_optimizer -> fp32 masters + Adam moments in pinned host memory, AdamW on the CPU (optim/sharded_optimizer.py)
+  offload_parameters / nvme / bucket sizes / hpZ / quantised comm -> accepted, not needed on this hardware (logged)
   loss scaling knobs -> fp16 GradScaler configuration
 """
 import logging
@@ -48,6 +49,7 @@ class DeepSpeedStrategy(Strategy):
         if stage not in (0, 1, 2, 3):
             raise ValueError(f'ZeRO stage must be 0..3, got {stage}')
         self.stage = stage
+        self.offload_optimizer = bool(offload_optimizer)
         self.reshard_after_forward = True if stage == 3 else False
         self.zero_optimization = zero_optimization
         self.exclude_frozen_parameters = exclude_frozen_parameters
@@ -61,7 +63,7 @@ class DeepSpeedStrategy(Strategy):
         if precision_plugin is not None:
             self.precision_plugin = precision_plugin
         ignored = {
-            'offload_optimizer': offload_optimizer, 'offload_parameters': offload_parameters,
+            'offload_parameters': offload_parameters,
             'remote_device': remote_device, 'zero_quantized_weights': zero_quantized_weights,
             'zero_quantized_gradients': zero_quantized_gradients, 'partition_activations': partition_activations,
             'cpu_checkpointing': cpu_checkpointing,

@@ -699,5 +699,6 @@ def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_afte
         engine.enable_fused_first_gemm(model)
     if offload_policy is not None and getattr(offload_policy, 'pin_memory', None) is not None \
             and type(offload_policy).__name__ == 'CPUOffloadPolicy':
-        logger.warning('CPU offload requested: not needed at 180 GB/GPU, parameters stay on device')
+        logger.info('CPUOffloadPolicy: optimizer state (fp32 masters + Adam moments) is kept in host memory; bf16 '
+                    'parameters and gradients stay on the device')
     return engine

@@ -387,3 +387,46 @@ def test_hf_causal_lm_wrapper_trains_sharded(reshard):
         ropt.step()
     for n, p in ref.named_parameters():
         assert torch.allclose(params['hf_model.' + n], p.detach(), atol=3e-5, rtol=1e-4), n
+
+
+def _offload_worker(rank: int, world: int, offload: bool):
+    from llm_training_b200.lightning import FSDP2Strategy, Trainer, seed_everything
+    from llm_training_b200.lightning.strategy.precision import CPUOffloadPolicy
+    from llm_training_b200.lms import CLM, CLMConfig
+    seed_everything(11)
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama', model_config=TINY),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=5e-3, weight_decay=0.1)))))
+    strategy = FSDP2Strategy(data_parallel_size=world, offload_policy=CPUOffloadPolicy() if offload else None)
+    trainer = Trainer(strategy=strategy, precision='bf16-true', logger=False, enable_progress_bar=False,
+                      enable_checkpointing=False, accelerator='cpu', gradient_clip_val=1.0)
+    lm.trainer = trainer
+    trainer.lightning_module = lm
+    trainer.strategy.setup_environment(trainer)
+    with trainer.strategy.model_init_context():
+        lm.configure_model()
+    trainer.strategy.setup(trainer)
+    opt = trainer.optimizers[0]
+    assert opt.offload == offload and all(st['master'].device.type == 'cpu' for st in opt.unit_state)
+    losses = []
+    for step in range(4):
+        ids = _batch(500 + step)[rank::world]
+        batch = dict(input_ids=ids, attention_mask=torch.ones_like(ids),
+                     position_ids=torch.arange(ids.shape[1])[None].expand(ids.shape[0], -1), labels=ids)
+        loss = trainer.strategy.training_step(batch, 0)
+        trainer.strategy.backward(loss)
+        trainer.strategy.optimizer_step(opt)
+        opt.zero_grad()
+        losses.append(float(loss.detach()))
+    return {n: p.detach().float().clone() for n, p in lm.model.named_parameters()}, losses
+
+
+def test_cpu_offload_policy_moves_optimizer_state_without_changing_the_update():
+    """`CPUOffloadPolicy` (reference: fsdp2_strategy.py:58) selects the host-resident optimizer state; the update is
+    the same AdamW (bf16 weights, fp32 masters)."""
+    plain = run_distributed(_offload_worker, world=2, args=(False,))
+    off = run_distributed(_offload_worker, world=2, args=(True,))
+    assert plain[0][1] == off[0][1]
+    for n, p in plain[0][0].items():
+        assert torch.equal(off[0][0][n], p), n

@@ -487,3 +487,35 @@ def test_gemm_reduce_scatter_emulated_ranks():
     total = sum(x.float() @ w.float().t() for x, w in zip(xs, ws))
     for r in range(world):
         _close(targets[r], residual[r].float() + total[r * rows:(r + 1) * rows], rtol=3e-2, atol=6e-2)
+
+
+def test_optimizer_state_cpu_offload_matches_device_update():
+    """Host-resident fp32 masters / moments + CPU AdamW (CPUOffloadPolicy) against the fused device kernel."""
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2)
+    results = []
+    for offload in (False, True):
+        torch.manual_seed(0)
+        with torch.device(DEV):
+            model = Llama(cfg).to(torch.bfloat16)
+        engine = apply_fully_sharded(model, None, device=torch.device(DEV))
+        opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
+                               max_grad_norm=1.0, offload=offload)
+        assert all((st['master'].device.type == 'cpu') == offload for st in opt.unit_state)
+        for step in range(3):
+            ids = torch.randint(0, 512, (2, 256), generator=torch.Generator().manual_seed(step)).to(DEV)
+            opt.zero_grad()
+            out = model(input_ids=ids, skip_logits=True)
+            fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                       shift_labels(ids).flatten()).backward()
+            opt.step()
+        torch.cuda.synchronize()
+        results.append([p.detach().float().clone() for p in model.parameters()])
+    for a, b in zip(*results):
+        # same math, different fp32 instruction order: at most a bf16 ulp on a few elements
+        assert float((a - b).abs().max()) <= 2e-2 * max(1.0, float(a.abs().max()))
+        assert float(((a - b).abs() > 1e-6).float().mean()) < 0.05
