@@ -88,24 +88,26 @@ class ClockSampler:
 
 
 def reference_arm(args) -> None:
-    """Run the UNMODIFIED reference from baseline/_ref through its own entry point.  Its stack (Lightning,
-    jsonargparse, DeepSpeed, torchmetrics ...) is not on this image and cannot be installed offline, so the
-    import fails and the arm reports itself unavailable (recorded in DESIGN.md)."""
+    """Run the UNMODIFIED reference tree in baseline/_ref on the bench config (see baseline/reference_arm.py for
+    exactly which of its modules run).  Nothing from llm_training_b200 is imported on this path."""
     ref = os.path.join(ROOT, 'baseline', '_ref')
-    out = {'impl': 'reference'}
     if not os.path.isdir(os.path.join(ref, 'llm_training')):
-        out['unavailable'] = 'baseline/_ref not installed (pip install --no-index of /root/reference; see DESIGN.md)'
-        print(json.dumps(out))
+        if int(os.environ.get('RANK', '0')) == 0:
+            print(json.dumps({'impl': 'reference', 'unavailable': 'baseline/_ref not installed (pip install '
+                              '--no-index --no-deps --target baseline/_ref /root/reference; see DESIGN.md)'}))
         return
-    probe = subprocess.run([sys.executable, '-c', 'import llm_training.cli.main'], cwd='/tmp',
-                           env=dict(os.environ, PYTHONPATH=ref), capture_output=True, text=True)
-    if probe.returncode != 0:
-        last = [l for l in probe.stderr.strip().splitlines() if l.strip()][-1:] or ['import failed']
-        out['unavailable'] = f'reference entry point does not import on this image: {last[0][:160]}'
-        print(json.dumps(out))
-        return
-    out['unavailable'] = 'reference imports but its Lightning/DeepSpeed runtime cannot train on sm_100 here'
-    print(json.dumps(out))
+    sys.path.insert(0, os.path.join(ROOT, 'baseline'))
+    import reference_arm as arm
+    arm.run(args, MODELS, ClockSampler)
+
+
+def relaunch_under_torchrun(n: int) -> None:
+    """``python bench.py --gpus N`` (N > 1) without a launcher: start one rank per GPU ourselves."""
+    import random
+    port = str(29500 + random.randrange(0, 2000))
+    os.execv(sys.executable, [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', f'--nproc-per-node={n}',
+                              '--master-addr', '127.0.0.1', '--master-port', port, os.path.abspath(__file__),
+                              *sys.argv[1:]])
 
 
 def main() -> None:
@@ -122,12 +124,20 @@ def main() -> None:
     ap.add_argument('--micro-batch', type=int, default=1)
     ap.add_argument('--recompute', default='auto', choices=['auto', 'none', 'full', 'selective'])
     ap.add_argument('--tp', type=int, default=1)
+    ap.add_argument('--reshard', action='store_true',
+                    help='ZeRO-3 / FSDP reshard_after_forward=True (the reference default) instead of resident parameters')
     ap.add_argument('--phases', action='store_true', help='also report forward / backward / optimizer device time')
     args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    env_world = int(os.environ.get('WORLD_SIZE', '1'))
+    if env_world != args.gpus:
+        if 'RANK' not in os.environ and env_world == 1 and args.gpus > 1:
+            relaunch_under_torchrun(args.gpus)
+        print(f'bench.py: --gpus {args.gpus} but WORLD_SIZE={env_world}; the two must agree', file=sys.stderr)
+        raise SystemExit(2)
     if args.impl == 'reference':
         reference_arm(args)
         return
-    args.warmup = max(args.warmup, 3)
 
     import torch
     import torch.distributed as dist
@@ -139,9 +149,6 @@ def main() -> None:
     world = int(os.environ.get('WORLD_SIZE', '1'))
     rank = int(os.environ.get('RANK', '0'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit('launch multi-GPU runs with torch.distributed.run (see module docstring)')
     cuda = torch.cuda.is_available()
     seed_everything(1234)
 
@@ -185,7 +192,7 @@ def main() -> None:
                 self.h2d = sum(v.numel() * v.element_size() for v in batch.values() if torch.is_tensor(v))
 
         def on_train_batch_end(self, trainer, module, outputs, batch, batch_idx) -> None:
-            loss_host = float(outputs)          # device -> host read of the step's loss, every step
+            loss_host = float(outputs.detach())          # device -> host read of the step's loss, every step
             self.d2h = outputs.element_size()
             self.last_loss = loss_host
             if batch_idx == args.warmup - 1:    # timed region starts BEFORE the next batch is fetched / copied
@@ -209,12 +216,17 @@ def main() -> None:
                 trainer.should_stop = True
 
     timer = E2ETimer()
-    strategy = FSDP2Strategy(data_parallel_size=dp, tensor_parallel_size=args.tp)
+    strategy = FSDP2Strategy(data_parallel_size=dp, tensor_parallel_size=args.tp,
+                             reshard_after_forward=True if args.reshard else 'auto')
+    # devices = --gpus: on a multi-GPU node a plain `python bench.py --gpus 1` must use exactly one GPU
     trainer = Trainer(strategy=strategy, precision='bf16-true' if cuda else '32-true', logger=False,
                       callbacks=[timer], max_steps=total_steps, gradient_clip_val=1.0, enable_progress_bar=False,
-                      enable_checkpointing=False, accelerator='auto')
+                      enable_checkpointing=False, accelerator='auto', devices=args.gpus)
     trainer.fit(lm, dm)                         # ---- e2e arm: the user's call
     device = trainer.strategy.root_device
+    if trainer.strategy.world_size != args.gpus:
+        print(f'bench.py: trainer runs on {trainer.strategy.world_size} ranks, --gpus says {args.gpus}', file=sys.stderr)
+        raise SystemExit(2)
 
     def reduce_max(x: float) -> float:
         if dist.is_initialized() and world > 1:
@@ -303,7 +315,19 @@ def main() -> None:
         bwd = sum(m[1].elapsed_time(m[2]) for m in phase_events) / len(phase_events)
         opt = sum(m[2].elapsed_time(m[3]) for m in phase_events) / len(phase_events)
         phases = {'forward_ms': reduce_max(fwd), 'backward_ms': reduce_max(bwd), 'optimizer_ms': reduce_max(opt)}
-    zero3 = any(getattr(e, 'reshard', False) for e in trainer.strategy.engines)
+    engines = trainer.strategy.engines
+    zero3 = any(getattr(e, 'reshard', False) for e in engines)
+    # which data plane actually ran (read from the live engines, not from the request)
+    if world == 1:
+        comm_name = 'none (single GPU)'
+    elif all(e.nvlink for e in engines) and all(e.nvlink_grads for e in engines):
+        comm_name = 'nvlink'
+    elif any(e.nvlink for e in engines):
+        comm_name = 'nvlink (parameters) + nccl (gradients)'
+    else:
+        comm_name = 'nccl'
+    multicast = any(bool(getattr(getattr(e, a, None), 'multicast_ptr', 0)) and getattr(e.comm, 'use_multicast', False)
+                    for e in engines for a in ('param_arena', 'grad_arena', 'shard_arena'))
     if rank == 0:
         mfu = (value * flops_per_token / 1e12 / (peak * world)) if peak else None
         print(json.dumps({
@@ -314,6 +338,7 @@ def main() -> None:
                        'parallelism': f'dp{dp}' + (f'xtp{args.tp}' if args.tp > 1 else ''),
                        'sharding': ('flat-param ZeRO-3 (params, grads and optimizer state sharded)' if zero3 else
                                     'flat-param ZeRO (optimizer+grad sharded, params resident)'),
+                       'comm': comm_name, 'reshard': zero3, 'multicast': multicast,
                        'optimizer': 'AdamW fp32 master, grad clip 1.0', 'recompute': recompute,
                        'l2': 'working set (16 GB bf16 weights) >> 126 MB L2, no flush needed'},
             'mfu_of_measured_sustained_peak': mfu, 'model_tflops_per_gpu': value * flops_per_token / 1e12 / world,

@@ -30,6 +30,31 @@ def test_bench_prints_one_json_line_with_the_contract_keys():
     assert {'sm_mhz', 'sm_max_mhz', 'reasons'} <= set(out['clocks'])
 
 
-def test_bench_reference_arm_reports_json():
-    out = _run('--impl', 'reference')
-    assert out['impl'] == 'reference' and ('unavailable' in out or 'value' in out)
+def test_bench_honours_gpus_and_records_the_data_plane():
+    """`--gpus N` is the number of ranks that run (the round-1 bench ignored it and ran on every visible GPU)."""
+    out = _run('--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64', '--gpus', '2')
+    assert out['n_gpus'] == 2 and out['config']['parallelism'] == 'dp2' and out['config']['global_batch'] == 2
+    assert {'comm', 'reshard', 'multicast'} <= set(out['config'])
+    assert out['config']['reshard'] is False
+    out = _run('--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64', '--gpus', '2', '--reshard')
+    assert out['n_gpus'] == 2 and out['config']['reshard'] is True and 'ZeRO-3' in out['config']['sharding']
+
+
+def test_bench_rejects_a_world_size_that_differs_from_gpus():
+    proc = subprocess.run([sys.executable, os.path.join(ROOT, 'bench.py'), '--gpus', '1', '--model', 'llama-tiny'],
+                          capture_output=True, text=True, timeout=120, cwd=ROOT,
+                          env=dict(os.environ, CUDA_VISIBLE_DEVICES='', WORLD_SIZE='4', RANK='0'))
+    assert proc.returncode == 2 and 'must agree' in proc.stderr
+
+
+def test_bench_reference_arm_runs_the_reference_modules():
+    """The reference arm drives the unmodified tree in baseline/_ref (tiny config on CPU here) and never imports
+    this package; without baseline/_ref it must say `unavailable` and exit 0."""
+    out = _run('--impl', 'reference', '--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64')
+    assert out['impl'] == 'reference'
+    if 'unavailable' in out:
+        assert not os.path.isdir(os.path.join(ROOT, 'baseline', '_ref', 'llm_training')), out
+        return
+    assert out['n_gpus'] == 1 and out['value'] > 0 and out['ours_loaded'] is False
+    assert out['e2e']['h2d_bytes_per_step'] > 0 and out['e2e']['d2h_bytes_per_step'] > 0
+    assert out['reference_class'] == 'reference modules, bare loop'
