@@ -496,16 +496,9 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   p.seg_start = seg_start; p.seg_end = seg_end; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
   p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f; p.window = window;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         BwdCfg::kSmemBytes);
-    if (e != cudaSuccess) {
-      set_error("attn_bwd: cannot set %d B dynamic smem: %s", BwdCfg::kSmemBytes, cudaGetErrorString(e));
-      return 2;
-    }
-    configured = true;
-  }
+  static bool configured[kMaxDevices] = {};
+  rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
+  if (rc) return rc;
   dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
   attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
   rc = check_launch("attn_bwd");

@@ -398,15 +398,8 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap&
                cudaStream_t stream) {
   using C = FwdCfg<DPAD>;
   auto kern = attn_fwd_kernel<DPAD>;
-  static bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
-    if (e != cudaSuccess) {
-      set_error("attn_fwd: cannot set %d B dynamic smem: %s", C::kSmemBytes, cudaGetErrorString(e));
-      return 2;
-    }
-    configured = true;
-  }
+  static bool configured[kMaxDevices] = {};
+  if (int rc = ensure_smem_attr(kern, C::kSmemBytes, configured, "attn_fwd")) return rc;
   dim3 grid((p.tokens + kBlockQ - 1) / kBlockQ, p.hq);
   kern<<<grid, kFwdThreads, C::kSmemBytes, stream>>>(tq, tkv, to, p);
   return check_launch("attn_fwd");

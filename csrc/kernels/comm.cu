@@ -166,14 +166,18 @@ sumsq_accumulate_kernel(const float* __restrict__ partial, int n, float* __restr
   if (threadIdx.x == 0) out[0] = accumulate ? out[0] + s : s;
 }
 
-// ---- one-shot all-reduce (sum) of n <= 32 floats through a symmetric fp32 buffer [world][32] + barrier slots
+// ---- one-shot all-reduce (sum) of n <= 32 floats through a symmetric fp32 buffer [2][world][32] + barrier slots.
+// The buffer half is chosen by epoch parity: a rank that has left all-reduce n may already be writing its row for
+// n + 1 while a slower peer still reads the rows of n; it cannot reach n + 2 (same half as n) before that peer has
+// signalled n + 1, which the peer only does after it finished reading n.
 __global__ void allreduce_oneshot_kernel(Peers bufs, Peers pads, int rank, int world, int slot_base, uint32_t epoch,
                                          float* __restrict__ value, int n) {
   const int t = threadIdx.x;
+  const int half = (epoch & 1u) * world * 32;
   // write my contribution into row `rank` of every peer's buffer
   if (t < world * n) {
     const int peer = t / n, j = t % n;
-    float* remote = reinterpret_cast<float*>(bufs.ptr[peer]) + rank * 32 + j;
+    float* remote = reinterpret_cast<float*>(bufs.ptr[peer]) + half + rank * 32 + j;
     asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(remote), "f"(value[j]) : "memory");
   }
   __threadfence_system();
@@ -188,7 +192,7 @@ __global__ void allreduce_oneshot_kernel(Peers bufs, Peers pads, int rank, int w
   }
   __syncthreads();
   if (t < n) {
-    const float* mine = reinterpret_cast<const float*>(bufs.ptr[rank]);
+    const float* mine = reinterpret_cast<const float*>(bufs.ptr[rank]) + half;
     float s = 0.f;
     for (int p = 0; p < world; ++p) {
       float v;

@@ -20,6 +20,30 @@ void count_launch();
     }                                      \
   } while (0)
 
+// cudaFuncSetAttribute is per device: launchers keep one "configured" flag per device ordinal
+constexpr int kMaxDevices = 64;
+
+// Sets the kernel's dynamic shared memory limit once per device.  `flags` is a static bool[kMaxDevices] owned by the
+// calling launcher (one per kernel instantiation).  Returns 0 on success.
+template <typename Kernel>
+inline int ensure_smem_attr(Kernel kern, int bytes, bool* flags, const char* what) {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("%s: device ordinal %d not supported (max %d)", what, dev, kMaxDevices);
+    return 2;
+  }
+  if (!flags[dev]) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e != cudaSuccess) {
+      set_error("%s: cannot set %d B dynamic smem: %s", what, bytes, cudaGetErrorString(e));
+      return 2;
+    }
+    flags[dev] = true;
+  }
+  return 0;
+}
+
 // ---- small device utilities ----------------------------------------------------------------------
 constexpr int kWarp = 32;
 

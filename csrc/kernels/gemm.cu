@@ -541,15 +541,12 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
            int max_ctas, cudaStream_t stream, const DistMaps* dist_maps = nullptr) {
   using C = Cfg<kCtaGroup>;
   auto kern = gemm_bf16_kernel<kCtaGroup, kAMn, kBMn, OutT, kDistA, kDistC>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes);
-    if (e != cudaSuccess) {
-      set_error("gemm: cannot set %d B dynamic smem: %s", C::kSmemBytes, cudaGetErrorString(e));
-      return 2;
-    }
-    configured = true;
-  }
+  // function attributes are per device: one flag per (instantiation, device)
+  static bool configured[kMaxDevices] = {};
+  static int resident_clusters[kMaxDevices] = {};
+  if (int rc = ensure_smem_attr(kern, C::kSmemBytes, configured, "gemm")) return rc;
+  int dev = 0;
+  cudaGetDevice(&dev);
   const int num_m = (p.M + BM * kCtaGroup - 1) / (BM * kCtaGroup);
   const int num_n = (p.N + BN - 1) / BN;
   int workers = num_m * num_n;
@@ -568,6 +565,26 @@ int launch(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& c, con
   cfg.attrs = attr;
   cfg.numAttrs = 1;
   cudaError_t e;
+  if constexpr (kDistA >= 2) {
+    // The pull warps of ALL CTAs feed the arrival counters every TMA producer waits on, so the whole grid has to be
+    // resident at once.  Ask the driver how many clusters of this exact shape (threads, dynamic smem, cluster size)
+    // can be co-scheduled on this device / partition and never launch more than that.
+    if (resident_clusters[dev] == 0) {
+      int n = 0;
+      e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+      if (e != cudaSuccess || n < 1) {
+        set_error("gemm: the gathering GEMM cannot be made resident on this device (%s, %d clusters)",
+                  e != cudaSuccess ? cudaGetErrorString(e) : "ok", n);
+        cudaGetLastError();
+        return 2;
+      }
+      resident_clusters[dev] = n;
+    }
+    if (workers > resident_clusters[dev]) {
+      workers = resident_clusters[dev];
+      cfg.gridDim = dim3(workers * kCtaGroup);
+    }
+  }
   if constexpr (kDistA != 0 || kDistC) e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, *dist_maps);
   else e = cudaLaunchKernelEx(&cfg, kern, a, b, c, r, p, NoDist{});
   if (e != cudaSuccess) {

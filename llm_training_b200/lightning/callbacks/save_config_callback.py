@@ -46,6 +46,8 @@ class SaveConfigCallback(Callback):
                 logger.log_hyperparams(self.yaml_config)
             if logger is not None and hasattr(logger, 'save_file'):
                 logger.save_file(path)
+            if logger is not None and hasattr(logger, 'log_code'):
+                logger.log_code()          # source tree upload (reference :40)
 
     def on_save_checkpoint(self, trainer, pl_module, checkpoint: dict[str, Any]) -> None:
         checkpoint['config'] = trainer.strategy.broadcast(self.yaml_config if trainer.is_global_zero else None, src=0)

@@ -45,7 +45,8 @@ class _Unsharded:
     """Every engine's parameters whole for the duration (ZeRO-3 engines gather, resident engines just sync)."""
 
     def __init__(self, strategy, writeback: bool = False) -> None:
-        self.ctxs = [e.unsharded(writeback=writeback) for e in getattr(strategy, 'engines', [])]
+        engines = list(getattr(strategy, 'engines', [])) + list(getattr(strategy, 'frozen_engines', []))
+        self.ctxs = [e.unsharded(writeback=writeback) for e in engines]
 
     def __enter__(self):
         for c in self.ctxs:

@@ -88,6 +88,30 @@ class WandbLogger:
         except Exception:
             pass
 
+    def log_code(self, root: str | None = None) -> list[str]:
+        """Upload the training source tree with the run (reference: save_config_callback.py:39-49 uploads ``src/`` and
+        ``scripts/``, ``.py/.sh/.j2`` only).  Here the tree is this package, ``scripts/`` and the kernel sources
+        (``csrc/``, ``include/``: ``.cu/.cuh/.cpp/.h``).  Returns the relative paths that were selected (also written
+        to ``code_files.txt`` beside the metrics mirror, so offline runs keep the record)."""
+        root = root or os.path.dirname(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+        tops = ('llm_training_b200', 'llm_training', 'scripts', 'csrc', 'include')
+        suffixes = ('.py', '.sh', '.j2', '.cu', '.cuh', '.cpp', '.h')
+
+        def include(path: str, base: str = root) -> bool:
+            rel = os.path.relpath(path, base)
+            return rel.split(os.sep)[0] in tops and rel.endswith(suffixes)
+
+        selected = sorted(os.path.relpath(os.path.join(d, f), root) for top in tops
+                          for d, _, files in os.walk(os.path.join(root, top)) for f in files
+                          if include(os.path.join(d, f)))
+        with open(os.path.join(self.save_dir, 'code_files.txt'), 'w') as f:
+            f.write('\n'.join(selected) + '\n')
+        try:
+            self.experiment.log_code(root=root, include_fn=include)
+        except Exception as e:   # offline / stub run
+            logger.debug(f'wandb log_code skipped: {e!r}')
+        return selected
+
     def finalize(self, status: str) -> None:
         if self._jsonl is not None:
             self._jsonl.close()

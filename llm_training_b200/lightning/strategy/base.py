@@ -35,6 +35,7 @@ class Strategy:
         self.trainer = None
         self.lightning_module = None
         self.engines: list[FlatParamEngine] = []
+        self.frozen_engines: list[FlatParamEngine] = []   # parameter-only engines of frozen models (DPO reference)
         self._root_device: torch.device | None = None
         self._grad_norm: torch.Tensor | None = None
 
@@ -129,6 +130,8 @@ class Strategy:
             torch.cuda.set_device(self.root_device)
         dp, tp = self._mesh_sizes()
         self.mesh = init_mesh(dp, tp, self.world_size, self.global_rank)
+        self.precision_plugin.bind_device(self.root_device.type)
+        self.precision_plugin.check_supported()     # GPU + a mode without native kernels: stop here, loudly
 
     # ---------------------------------------------------------------- model + optimizers
     reshard_after_forward: bool | int | str = 'auto'
@@ -152,7 +155,7 @@ class Strategy:
         # anything still on CPU / wrong dtype (metrics, user-built submodules)
         self._materialize(module)
         self.engines = self._build_engines(module)
-        for e in self.engines:
+        for e in self.engines + self.frozen_engines:
             e.sync_shards_from_full()     # weights were loaded / broadcast into the full buffers after sharding
         if getattr(module, 'weights_used_once_per_step', False):
             for e in self.engines:
@@ -191,14 +194,15 @@ class Strategy:
 
     def _build_engines(self, module: nn.Module) -> list[FlatParamEngine]:
         engines = []
+        self.frozen_engines = []
         for model in self._sharded_models(module):
-            if not any(p.requires_grad for p in model.parameters()):
-                continue
             engine = getattr(model, '_flat_engine', None)
-            if engine is None:
+            if engine is None and not hasattr(model, '_flat_engine'):
                 engine = apply_fully_sharded(model, self.dp_mesh, device=self.root_device,
                                              reshard_after_forward=self.reshard_after_forward)
-            engines.append(engine)
+            if engine is None:
+                continue                  # frozen model with resident parameters: nothing to manage
+            (self.frozen_engines if engine.frozen else engines).append(engine)
         claimed = {id(p) for e in engines for u in e.units for _, p in u.params}
         rest = [(n, p) for n, p in module.named_parameters() if p.requires_grad and id(p) not in claimed]
         if rest:
@@ -220,7 +224,8 @@ class Strategy:
         if self.tp_size > 1:
             extra.append(get_comm(self.tp_mesh, 'torch'))
         wrapped = ShardedOptimizer(optimizer, self.engines, max_grad_norm=trainer.gradient_clip_val,
-                                   norm_extra_axes=extra, offload=self.offload_optimizer_state)
+                                   norm_extra_axes=extra, offload=self.offload_optimizer_state,
+                                   master_weights=bool(getattr(self, 'use_master_weights', True)))
         sched_cfgs = []
         if sched is not None:
             cfg = sched if isinstance(sched, dict) else {'scheduler': sched}
@@ -257,6 +262,10 @@ class Strategy:
 
     def optimizer_step(self, optimizer: Optimizer, closure=None) -> Any:
         out = self.precision_plugin.optimizer_step(optimizer, self.lightning_module, closure)
+        for e in self.frozen_engines:
+            # units of a frozen model that are read outside a module call (its LM-head weight in the fused loss) stay
+            # whole for the step; the step boundary is where they go back to slices
+            e.reshard_all()
         self._grad_norm = getattr(optimizer, 'last_grad_norm', None)
         if self.lightning_module is not None:
             self.lightning_module._grad_norm = self._grad_norm

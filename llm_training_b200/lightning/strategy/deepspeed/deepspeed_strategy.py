@@ -10,7 +10,9 @@ dependency here — the constructor accepts the same arguments and maps them ont
   stage 3       -> the engine's resharding mode (``reshard_after_forward=True``): parameters and gradients exist
                    whole only around a unit's forward / backward (parallel/fsdp.py)
   offload_optimizer -> fp32 masters + Adam moments in pinned host memory, AdamW on the CPU (optim/sharded_optimizer.py)
-  offload_parameters / nvme / bucket sizes / hpZ / quantised comm -> accepted, not needed on this hardware (logged)
+  offload_parameters / remote_device (CPU / NVMe parameter offload), quantised weights / gradients, cpu_checkpointing
+                -> NOT implemented: a non-default value raises (LLMT_IGNORE_UNSUPPORTED=1 downgrades to a warning)
+  bucket sizes / hpZ / partition_activations / aio knobs -> scheduling hints with no counterpart here (logged)
   loss scaling knobs -> fp16 GradScaler configuration
 """
 import logging
@@ -62,17 +64,25 @@ class DeepSpeedStrategy(Strategy):
         self.config = config
         if precision_plugin is not None:
             self.precision_plugin = precision_plugin
-        ignored = {
-            'offload_parameters': offload_parameters,
-            'remote_device': remote_device, 'zero_quantized_weights': zero_quantized_weights,
-            'zero_quantized_gradients': zero_quantized_gradients, 'partition_activations': partition_activations,
+        # options that would change WHERE state lives or WHAT goes over the wire: refusing beats pretending
+        unsupported = {
+            'offload_parameters': offload_parameters, 'remote_device': remote_device,
+            'zero_quantized_weights': zero_quantized_weights, 'zero_quantized_gradients': zero_quantized_gradients,
             'cpu_checkpointing': cpu_checkpointing,
         }
-        active = [k for k, v in ignored.items() if v]
-        if active or zero_hpz_partition_size != 1:
-            logger.warning('DeepSpeedStrategy: options %s are accepted for config compatibility but unused: the '
-                           'native engine keeps parameters and optimizer state in the 180 GB of HBM3e per GPU',
-                           active + (['zero_hpz_partition_size'] if zero_hpz_partition_size != 1 else []))
+        active = [k for k, v in unsupported.items() if v]
+        if active:
+            import os
+            msg = (f'DeepSpeedStrategy: {active} not implemented by the native engine (parameters, gradients and '
+                   'optimizer state live in HBM, sharded per ZeRO stage; only `offload_optimizer` moves state to the '
+                   'host)')
+            if os.environ.get('LLMT_IGNORE_UNSUPPORTED', '0') != '1':
+                raise NotImplementedError(msg + '; set LLMT_IGNORE_UNSUPPORTED=1 to train without them')
+            logger.warning(msg + ' — ignored')
+        hints = [k for k, v in {'partition_activations': partition_activations,
+                                'zero_hpz_partition_size': zero_hpz_partition_size != 1}.items() if v]
+        if hints:
+            logger.warning('DeepSpeedStrategy: %s are scheduling hints with no counterpart here (ignored)', hints)
 
     @property
     def zero_stage_3(self) -> bool:

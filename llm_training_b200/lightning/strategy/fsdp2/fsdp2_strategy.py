@@ -31,7 +31,22 @@ class FSDP2Strategy(Strategy):
 
     @property
     def mp_policy(self) -> MixedPrecisionPolicy:
-        return self._mp_policy or self.precision_plugin.mp_policy
+        """The compute / reduce dtypes are a function of ``trainer.precision`` in this engine (gradients live in the
+        flat buffer in the parameter dtype and are reduced in it).  An explicit ``mp_policy`` is accepted when it
+        says the same thing and REJECTED when it asks for something else (the reference forwards it to
+        ``fully_shard``, fsdp2_strategy.py:57,93-103); it is never silently dropped."""
+        derived = self.precision_plugin.mp_policy
+        given = self._mp_policy
+        if given is None:
+            return derived
+        for field in ('param_dtype', 'reduce_dtype', 'output_dtype'):
+            want = getattr(given, field, None)
+            if want is not None and want != getattr(derived, field):
+                raise ValueError(
+                    f'FSDP2Strategy(mp_policy=...): {field}={want} conflicts with precision='
+                    f'{self.precision_plugin.precision!r} ({field}={getattr(derived, field)}); this engine derives the '
+                    'mixed-precision policy from `trainer.precision` — change that instead')
+        return derived
 
     @property
     def offload_policy(self) -> OffloadPolicy:

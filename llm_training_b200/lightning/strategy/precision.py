@@ -1,11 +1,24 @@
 """Precision handling (reference: src/llm_training/lightning/strategy/fsdp2/fsdp2_precision.py:24-194).
 
 ``32-true | 16-true | bf16-true | 16-mixed | bf16-mixed`` -> parameter dtype, autocast dtype, reduce dtype.
-``bf16-true`` is the hot path (bf16 parameters + fp32 master weights inside the sharded optimizer, every
-op on the in-tree kernels); the others run through PyTorch ops.  The fp16 GradScaler is created for the
-``16-*`` modes (the reference reads ``self.precision`` before assigning it, so its scaler is never
-auto-created — SURVEY Appendix B7).
+
+On a GPU the sm_100a kernels are bf16 kernels (fp32 accumulation, fp32 softmax / norm / loss statistics inside):
+
+* ``bf16-true``  bf16 parameters + fp32 master weights inside the sharded optimizer — the hot path;
+* ``bf16-mixed`` runs on the SAME kernels: what the reference expresses as "fp32 parameters + bf16 autocast + bf16
+  gradient reduction" (fsdp2_precision.py:63-69) is, in this engine, "fp32 master slices in the optimizer + a bf16
+  compute copy that the modules see"; the ops autocast keeps in fp32 (norm statistics, softmax, loss) are fp32 inside
+  the kernels.  The two bf16 modes therefore differ only in name here (and in the reference only in which copy is
+  checkpointed: the bf16 one here);
+* ``32-true``, ``16-true``, ``16-mixed`` have no native kernels.  They raise on a GPU instead of silently running
+  cuBLAS / eager PyTorch; ``LLMT_ALLOW_TORCH_PRECISION=1`` opts into the PyTorch path (logged once).
+
+On CPU every mode is plain PyTorch (the oracle / gloo test path).  The fp16 GradScaler is created for the ``16-*``
+modes (the reference reads ``self.precision`` before assigning it, so its scaler is never auto-created — SURVEY
+Appendix B7).
 """
+import logging
+import os
 from contextlib import nullcontext
 from dataclasses import dataclass
 from typing import Any, ContextManager, Literal
@@ -54,13 +67,40 @@ class FSDP2Precision:
             '16-mixed': (torch.float32, torch.float16),
             'bf16-mixed': (torch.float32, torch.bfloat16),
         }
-        self.param_dtype, self.autocast_dtype = table[precision]
+        self._table = table
+        self.bind_device(self.device)
+
+    def bind_device(self, device_type: str) -> None:
+        """(Re)derive the dtypes for the device training actually runs on (the strategy calls this once the root
+        device is known: `accelerator='cpu'` on a GPU box must get the CPU semantics)."""
+        self.device = device_type
+        self.param_dtype, self.autocast_dtype = self._table[self.precision]
+        # GPU: which modes own a native kernel path (see module docstring)
+        self.native = self.device == 'cuda' and self.precision in ('bf16-true', 'bf16-mixed')
+        if self.device == 'cuda' and self.precision == 'bf16-mixed':
+            self.param_dtype, self.autocast_dtype = torch.bfloat16, None
+
+    def check_supported(self) -> None:
+        """Called by the strategy when training is set up on a device: a GPU run in a mode without native kernels
+        stops here (or continues on PyTorch ops when ``LLMT_ALLOW_TORCH_PRECISION=1``)."""
+        if self.device != 'cuda' or self.native:
+            return
+        if os.environ.get('LLMT_ALLOW_TORCH_PRECISION', '0') != '1':
+            raise NotImplementedError(
+                f'precision={self.precision!r} has no sm_100a kernel path (the kernels are bf16 with fp32 '
+                'accumulation and fp32 master weights): use bf16-true or bf16-mixed, or set '
+                'LLMT_ALLOW_TORCH_PRECISION=1 to run this mode on PyTorch / cuBLAS ops instead')
+        logging.getLogger(__name__).warning(
+            f'precision={self.precision!r}: running on PyTorch ops (cuBLAS / eager), NOT on the in-tree kernels')
 
     @property
     def mp_policy(self) -> MixedPrecisionPolicy:
-        reduce = self.param_dtype if self.autocast_dtype is None else torch.float32
-        return MixedPrecisionPolicy(param_dtype=self.autocast_dtype or self.param_dtype, reduce_dtype=reduce,
-                                    output_dtype=self.autocast_dtype or self.param_dtype)
+        """The reference's table (fsdp2_precision.py:55-90): compute dtype, gradient-reduction dtype, output dtype.
+        Gradients are reduced in the compute dtype for every mode (bf16 for both bf16 modes, fp16 for both fp16
+        modes, fp32 for 32-true)."""
+        compute = self.autocast_dtype or self.param_dtype
+        return MixedPrecisionPolicy(param_dtype=compute, reduce_dtype=compute, output_dtype=compute,
+                                    cast_forward_inputs=False)
 
     def convert_module(self, module: torch.nn.Module) -> torch.nn.Module:
         """Cast floating-point parameters/buffers that live in a real device; meta tensors are converted too."""
@@ -75,8 +115,7 @@ class FSDP2Precision:
     def forward_context(self) -> ContextManager:
         if self.autocast_dtype is None:
             return nullcontext()
-        device_type = 'cuda' if torch.cuda.is_available() else 'cpu'
-        return torch.autocast(device_type, dtype=self.autocast_dtype)
+        return torch.autocast(self.device, dtype=self.autocast_dtype)
 
     def pre_backward(self, loss: torch.Tensor) -> torch.Tensor:
         return self.scaler.scale(loss) if self.scaler is not None else loss

@@ -1,7 +1,12 @@
 """Any Hugging Face ``AutoModelForCausalLM`` as a model (reference:
-src/llm_training/models/hf_causal_lm/hf_causal_lm.py:19-131).  Best-effort path: it runs the HF
-module's own PyTorch code (no in-tree kernels, no tensor parallel); sharding wraps every
-``_no_split_modules`` block plus the leftovers, like the reference (:88-114)."""
+src/llm_training/models/hf_causal_lm/hf_causal_lm.py:19-131).  The HF module's own code runs the layers (no tensor
+parallel, as in the reference); sharding wraps every ``_no_split_modules`` block plus the leftovers (:88-114).
+
+Attention: with ``attn_implementation`` ``flash_attention_2`` (the auto-pick on a GPU) the HF attention layers call
+the in-tree packed attention kernel through HF's ``AttentionInterface`` — O(T) memory, segment-id masks honoured as
+per-token document bounds computed once per batch.  The reference gets there by monkey-patching HF's
+``_get_unpad_data`` so flash-attn's varlen kernel sees the segment ids (:14-20); the dense ``[B,1,T,T]`` mask is only
+built for ``sdpa`` / ``eager``."""
 from typing import Any
 
 import torch
@@ -10,6 +15,43 @@ from torch import nn
 from ..hf_compat_model import HFCompatModel
 from ..utils.modeling_outputs import CausalLMOutput
 from .hf_causal_lm_config import HFCausalLMConfig
+
+
+PACKED_ATTENTION = 'llmt_packed'
+
+
+def _packed_attention_interface(module: nn.Module, query: torch.Tensor, key: torch.Tensor, value: torch.Tensor,
+                                attention_mask: torch.Tensor | None, dropout: float = 0.0,
+                                scaling: float | None = None, is_causal: bool | None = None,
+                                sliding_window: int | None = None, softcap: float | None = None,
+                                **kwargs: Any) -> tuple[torch.Tensor, None]:
+    """HF attention-interface function: q ``[B, Hq, T, D]``, k / v ``[B, Hkv, T, D]`` -> ``[B, T, Hq, D]``.
+    The per-token document bounds were derived from the batch's segment ids by ``HFCausalLM.forward`` and are shared
+    with every attention layer through ``module._llmt_packed_state``."""
+    from ...ops.attention_op import packed_attention
+    from ...ops.segments import segment_bounds
+    if softcap is not None or (dropout and module.training):
+        raise NotImplementedError('HFCausalLM packed attention: attention dropout / softcap are not supported; use '
+                                  'attn_implementation="sdpa" for such a model')
+    b, hq, t, d = query.shape
+    hkv = key.shape[1]
+    state = getattr(module, '_llmt_packed_state', None) or {}
+    bounds = state.get('bounds')
+    if bounds is None or bounds[0].numel() != b * t or bounds[0].device != query.device:
+        bounds = segment_bounds(None, b, t, query.device)
+    qkv = torch.cat((query.transpose(1, 2).reshape(b * t, hq * d), key.transpose(1, 2).reshape(b * t, hkv * d),
+                     value.transpose(1, 2).reshape(b * t, hkv * d)), dim=-1)
+    out = packed_attention(qkv, bounds[0], bounds[1], hq, hkv, d, scaling, sliding_window)
+    return out.view(b, t, hq, d), None
+
+
+def _register_packed_attention() -> None:
+    from transformers import AttentionInterface
+    from transformers.masking_utils import AttentionMaskInterface
+    if PACKED_ATTENTION not in AttentionInterface._global_mapping:
+        AttentionInterface.register(PACKED_ATTENTION, _packed_attention_interface)
+        # no 4-D mask: documents, causality and the sliding window are all expressed by the bounds
+        AttentionMaskInterface.register(PACKED_ATTENTION, lambda *args, **kwargs: None)
 
 
 def patch_hf_modules_with_in_tree_kernels(model: nn.Module) -> int:
@@ -59,7 +101,16 @@ class HFCausalLM(HFCompatModel):
         if self.hf_config is None and self.config.hf_config is not None:
             self.hf_config = self.config.hf_config
         self.config.hf_config = self.hf_config
-        self.hf_model = self.construct_hf_model()
+        self._packed_state: dict[str, Any] = {}
+        self.uses_packed_attention = self.config._attn_implementation == 'flash_attention_2'
+        if self.uses_packed_attention:
+            _register_packed_attention()
+            self.hf_model = self.construct_hf_model(attn_implementation=PACKED_ATTENTION)
+            for module in self.hf_model.modules():
+                if hasattr(module, 'q_proj') or hasattr(module, 'qkv_proj') or type(module).__name__.endswith('Attention'):
+                    module._llmt_packed_state = self._packed_state
+        else:
+            self.hf_model = self.construct_hf_model()
         if self.config.enable_liger_kernel:
             self.patched_modules = patch_hf_modules_with_in_tree_kernels(self.hf_model)
         if self.config.enable_gradient_checkpointing:
@@ -78,7 +129,17 @@ class HFCausalLM(HFCompatModel):
     def forward(self, input_ids: torch.Tensor | None = None, attention_mask: torch.Tensor | None = None,
                 position_ids: torch.Tensor | None = None, inputs_embeds: torch.Tensor | None = None,
                 return_last_hidden_states: bool = False, skip_logits: bool = False) -> CausalLMOutput:
-        if attention_mask is not None and attention_mask.dim() == 2:
+        if self.uses_packed_attention:
+            # segment ids -> per-token document bounds, once per batch, on device, no host sync; the attention layers
+            # read them from the shared state (also during activation recompute in backward)
+            from ...ops.segments import segment_bounds
+            ref = input_ids if input_ids is not None else inputs_embeds
+            bsz, seq = ref.shape[:2]
+            self._packed_state['bounds'] = segment_bounds(
+                attention_mask if (attention_mask is not None and attention_mask.dim() == 2) else None, bsz, seq,
+                ref.device)
+            attention_mask = None
+        elif attention_mask is not None and attention_mask.dim() == 2:
             if bool((attention_mask > 1).any()):
                 # packed batch (segment ids 1, 2, 3, ...): HF modules only know 0/1 masks, so hand them the
                 # block-diagonal causal 4-D mask instead — documents of a pack stay isolated.  The reference gets the

@@ -48,8 +48,12 @@ class ShardedUnit:
     def __init__(self, name: str, params: list[tuple[str, nn.Parameter]], world: int, rank: int,
                  device: torch.device, dtype: torch.dtype, grad_dtype: torch.dtype,
                  flat_param: torch.Tensor | None = None, flat_grad: torch.Tensor | None = None,
-                 arena_offset: int = 0, reshard: bool = False, shard_store: torch.Tensor | None = None) -> None:
+                 arena_offset: int = 0, reshard: bool = False, shard_store: torch.Tensor | None = None,
+                 with_grad: bool = True) -> None:
+        """``with_grad=False``: a frozen unit (e.g. DPO's reference model) — parameters are sharded / gathered like
+        any other unit, but no gradient buffer, no reduce-scatter target and no optimizer state ever exist."""
         self.name = name
+        self.with_grad = with_grad
         self.params = params
         self.world, self.rank = world, rank
         self.offsets, self.numel, self.padded_numel = self.layout(params, world)
@@ -57,16 +61,20 @@ class ShardedUnit:
         self.arena_offset = arena_offset          # element offset inside the engine's symmetric arenas
         self.flat_param = flat_param if flat_param is not None else torch.zeros(self.padded_numel, dtype=dtype,
                                                                                  device=device)
-        self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(self.padded_numel, dtype=grad_dtype,
-                                                                              device=device)
+        if not with_grad:
+            self.flat_grad = torch.zeros(0, dtype=grad_dtype, device=device)
+        else:
+            self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(self.padded_numel, dtype=grad_dtype,
+                                                                                  device=device)
         for (_, p), o in zip(params, self.offsets):
             view = self.flat_param[o:o + p.numel()].view(p.shape)
             if not p.is_meta:
                 view.copy_(p.data)
             p.data = view
-            p.grad = self.flat_grad[o:o + p.numel()].view(p.shape)
+            if with_grad:
+                p.grad = self.flat_grad[o:o + p.numel()].view(p.shape)
         # reduce-scatter target: separate buffer so the in-flight collective never aliases live grads
-        self.grad_shard = (self.flat_grad if world == 1
+        self.grad_shard = (self.flat_grad if (world == 1 or not with_grad)
                            else torch.zeros(self.shard_numel, dtype=grad_dtype, device=device))
         self.pending_grads = 0
         self.reduced = False
@@ -81,7 +89,7 @@ class ShardedUnit:
                 self.shard_numel, dtype=dtype, device=device)
             self._shard.copy_(self.flat_param[rank * self.shard_numel:(rank + 1) * self.shard_numel])
         self.is_sharded = False       # flat_param currently has no storage
-        self.grad_live = True         # flat_grad currently has storage (and holds zeros or partial sums)
+        self.grad_live = with_grad    # flat_grad currently has storage (and holds zeros or partial sums)
         self.in_backward = False
         self.gather_event: Any = None
         self.gather_pending = False
@@ -116,7 +124,10 @@ class ShardedUnit:
 class FlatParamEngine:
     def __init__(self, units: list[tuple[str, list[tuple[str, nn.Parameter]]]], dp_axis: MeshAxis | None,
                  device: torch.device, comm: Comm | None = None, grad_dtype: torch.dtype | None = None,
-                 tp_axis: MeshAxis | None = None, reshard: bool = False) -> None:
+                 tp_axis: MeshAxis | None = None, reshard: bool = False, frozen: bool = False) -> None:
+        """``frozen=True``: every unit is parameter-only (``ShardedUnit(with_grad=False)``); the engine then only
+        gathers before use and drops after use (ZeRO-3 for a model that is never trained)."""
+        self.frozen = bool(frozen)
         self.axis = dp_axis if dp_axis is not None else MeshAxis('data_parallel', [0], 0, None)
         # tensor-parallel peers hold different shards of most parameters but REPLICAS of a few (norm weights);
         # under sequence parallelism the replicas' gradients are partial sums over the tp axis
@@ -144,10 +155,11 @@ class FlatParamEngine:
                 assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
                 store = self.shard_arena.tensor[off:off + ssz] if self.shard_arena is not None else None
                 self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype,
-                                              arena_offset=off, reshard=True, shard_store=store))
+                                              arena_offset=off, reshard=True, shard_store=store,
+                                              with_grad=not self.frozen))
                 off += ssz
             self.nvlink_grads = False
-        elif self.nvlink and len(dtypes) == 1:
+        elif self.nvlink and len(dtypes) == 1 and not self.frozen:
             # one symmetric allocation for all parameters and one for all gradients: peers address any unit as
             # arena base + offset, and a single rendezvous exchanges the handles
             dtype = next(iter(dtypes))
@@ -168,7 +180,8 @@ class FlatParamEngine:
             for name, params in units:
                 dtype = params[0][1].dtype
                 assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
-                self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype))
+                self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype,
+                                              with_grad=not self.frozen))
         # `nvlink` = parameters travel through our kernels; `nvlink_grads` = gradients do too (resident mode only)
         self.nvlink_grads = self.nvlink and not self.reshard
         import os
@@ -269,6 +282,8 @@ class FlatParamEngine:
 
     def finish_backward(self) -> None:
         """Make every unit's reduced gradient shard available on the current stream."""
+        if self.frozen:
+            return
         if not self.require_sync:
             self._rearm()
             return
@@ -326,6 +341,8 @@ class FlatParamEngine:
 
         def root_hook(module, args):
             if self.reshard:
+                if self.frozen and self._forward_order:     # no backward ever records the order for a frozen model
+                    self._last_forward_order = list(self._forward_order)
                 self._forward_order = []
             for u in self.units:
                 if not u.hook_seen:
@@ -482,7 +499,7 @@ class FlatParamEngine:
         return None
 
     def _alloc_grad(self, u: ShardedUnit) -> None:
-        if not u.grad_live:
+        if not u.grad_live and u.with_grad:
             u._set_storage(u.flat_grad, True)
             u.flat_grad.zero_()
             u.grad_live = True
@@ -514,7 +531,7 @@ class FlatParamEngine:
 
     def zero_grad(self) -> None:
         for u in self.units:
-            if not u.grad_live:           # ZeRO-3: no storage until the unit's next backward allocates + clears it
+            if not u.grad_live or not u.with_grad:           # ZeRO-3: no storage until the unit's next backward allocates + clears it
                 continue
             if not u.grad_zeroed:
                 self.wait_unit(u)
@@ -657,7 +674,8 @@ def _collect_units(model: nn.Module, only_trainable: bool = True
     return groups
 
 
-def _resolve_reshard(mode: Any, units: list, dp_mesh: MeshAxis | None, device: torch.device) -> bool:
+def _resolve_reshard(mode: Any, units: list, dp_mesh: MeshAxis | None, device: torch.device,
+                     frozen: bool = False) -> bool:
     """``True`` / an int -> ZeRO-3 (full buffers only around a unit's use), ``False`` -> resident parameters
     (ZeRO-2), ``'auto'`` (our default) -> resident unless bf16 parameters + gradients would take more than 40% of
     the device.  ``LLMT_RESHARD=0|1`` overrides.  The reference's default is ``True``
@@ -671,8 +689,14 @@ def _resolve_reshard(mode: Any, units: list, dp_mesh: MeshAxis | None, device: t
     if isinstance(mode, str) or mode is None:
         if device.type != 'cuda':
             return False
-        need = 2 * sum(p.numel() * p.element_size() for _, ps in units for _, p in ps)
-        return need > 0.4 * torch.cuda.get_device_properties(device).total_memory
+        need = (1 if frozen else 2) * sum(p.numel() * p.element_size() for _, ps in units for _, p in ps)
+        return need > (0.2 if frozen else 0.4) * torch.cuda.get_device_properties(device).total_memory
+    if not isinstance(mode, bool) and isinstance(mode, int):
+        # FSDP2: an int N means "after forward keep the parameters sharded over N ranks" (a middle ground between
+        # True and False).  One NVSwitch box has no cheaper sub-group than the full group, so N > 1 is the same
+        # schedule as True here; N == 1 ("keep whole parameters") is False.
+        logger.info(f'reshard_after_forward={mode}: treated as {mode > 1} (no intermediate shard group on one box)')
+        return mode > 1
     return bool(mode)
 
 
@@ -690,9 +714,16 @@ def apply_fully_sharded(model: nn.Module, dp_mesh: MeshAxis | None, reshard_afte
     # gradients are reduced in the parameter dtype (bf16 for `bf16-true`, like the reference's default
     # MixedPrecisionPolicy, fsdp2_precision.py:72-76); `.grad` must match the parameter dtype anyway
     tp_axis = getattr(getattr(model, 'tp_context', None), 'axis', None)
-    units = _collect_units(model)
-    engine = FlatParamEngine(units, dp_mesh, device, comm=comm, tp_axis=tp_axis,
-                             reshard=_resolve_reshard(reshard_after_forward, units, dp_mesh, device))
+    # A model without a single trainable parameter (DPO's reference policy; the reference shards it with the same
+    # mesh as the policy, lms/dpo/dpo.py:69-71) gets a parameter-only engine: it is worth sharding only in ZeRO-3
+    # mode — resident parameters of a frozen model are just the model.
+    frozen = not any(p.requires_grad for p in model.parameters())
+    units = _collect_units(model, only_trainable=not frozen)
+    reshard = _resolve_reshard(reshard_after_forward, units, dp_mesh, device, frozen=frozen)
+    if frozen and not reshard:
+        model._flat_engine = None
+        return None
+    engine = FlatParamEngine(units, dp_mesh, device, comm=comm, tp_axis=tp_axis, reshard=reshard, frozen=frozen)
     model._flat_engine = engine
     engine.attach_module_hooks(model)
     if engine.reshard:

@@ -59,7 +59,7 @@ class NVLinkComm(Comm):
         self.device = torch.device('cuda', torch.cuda.current_device())
         symm_mem.enable_symm_mem_for_group(self.group.group_name) if hasattr(symm_mem, 'enable_symm_mem_for_group') \
             else None
-        self._scalars = self.alloc(32 * max(axis.size(), 1), torch.float32)      # [world][32] for one-shot reduce
+        self._scalars = self.alloc(2 * 32 * max(axis.size(), 1), torch.float32)  # [2][world][32], half = epoch parity
         self._scalars.tensor.zero_()
         pad_bytes = int(self._scalars.handle.signal_pad_size)
         assert pad_bytes >= 4 * (_ALLREDUCE_SLOT + axis.size()), f'signal pad too small ({pad_bytes} B)'

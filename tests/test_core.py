@@ -541,3 +541,109 @@ def test_hf_causal_lm_in_tree_kernel_patching_preserves_outputs():
     b.float().pow(2).mean().backward()
     for (n, p), (_, q) in zip(plain.named_parameters(), patched.named_parameters()):
         assert torch.allclose(p.grad, q.grad, atol=1e-5), n
+
+
+def test_precision_modes_route_to_kernels_or_refuse_on_gpu(monkeypatch):
+    """bf16-mixed shares the bf16 kernel path (bf16 compute copy + fp32 masters); modes without native kernels raise
+    on a GPU instead of silently running PyTorch ops, unless explicitly allowed.  (Device type is passed explicitly,
+    so this runs without a GPU.)"""
+    import pytest
+    from llm_training_b200.lightning.strategy.precision import FSDP2Precision
+    for mode in ('bf16-true', 'bf16-mixed'):
+        plugin = FSDP2Precision(mode, device='cuda')
+        assert plugin.native and plugin.param_dtype == torch.bfloat16 and plugin.autocast_dtype is None
+        assert plugin.mp_policy.reduce_dtype == torch.bfloat16
+    for mode in ('32-true', '16-true'):
+        monkeypatch.delenv('LLMT_ALLOW_TORCH_PRECISION', raising=False)
+        with pytest.raises(NotImplementedError, match='no sm_100a kernel path'):
+            FSDP2Precision(mode, device='cuda').check_supported()
+        monkeypatch.setenv('LLMT_ALLOW_TORCH_PRECISION', '1')
+        allowed = FSDP2Precision(mode, device='cuda')
+        allowed.check_supported()
+        assert allowed.native is False
+    # CPU keeps the reference's semantics for every mode (fp32 parameters + autocast for the mixed ones)
+    cpu = FSDP2Precision('bf16-mixed', device='cpu')
+    assert cpu.param_dtype == torch.float32 and cpu.autocast_dtype == torch.bfloat16
+    assert cpu.mp_policy.param_dtype == torch.bfloat16 and cpu.mp_policy.reduce_dtype == torch.bfloat16
+
+
+def test_strategy_arguments_are_honoured_or_rejected_never_dropped(monkeypatch):
+    import pytest
+    from llm_training_b200.lightning import DeepSpeedStrategy, FSDP2Strategy
+    from llm_training_b200.lightning.strategy.precision import FSDP2Precision, MixedPrecisionPolicy
+    ok = FSDP2Strategy(mp_policy=MixedPrecisionPolicy(param_dtype=torch.float32, reduce_dtype=torch.float32))
+    ok.precision_plugin = FSDP2Precision('32-true', device='cpu')
+    assert ok.mp_policy.reduce_dtype == torch.float32
+    bad = FSDP2Strategy(mp_policy=MixedPrecisionPolicy(param_dtype=torch.bfloat16, reduce_dtype=torch.float32))
+    bad.precision_plugin = FSDP2Precision('bf16-true', device='cpu')
+    with pytest.raises(ValueError, match='reduce_dtype'):
+        bad.mp_policy
+    monkeypatch.delenv('LLMT_IGNORE_UNSUPPORTED', raising=False)
+    with pytest.raises(NotImplementedError, match='offload_parameters'):
+        DeepSpeedStrategy(stage=3, offload_parameters=True)
+    monkeypatch.setenv('LLMT_IGNORE_UNSUPPORTED', '1')
+    assert DeepSpeedStrategy(stage=3, offload_parameters=True).stage == 3
+    from llm_training_b200.parallel.fsdp import _resolve_reshard
+    from llm_training_b200.parallel.mesh import MeshAxis
+    two = MeshAxis('data_parallel', [0, 1], 0, None)
+    cpu = torch.device('cpu')
+    assert _resolve_reshard(2, [], two, cpu) is True and _resolve_reshard(1, [], two, cpu) is False
+
+
+def test_optimizer_without_master_weights_steps_the_low_precision_slices():
+    """FSDP2Strategy(use_master_weights=False): no fp32 copy; the user's optimizer class updates the bf16 slices."""
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded
+    torch.manual_seed(0)
+    model = torch.nn.Linear(16, 16, bias=False).to(torch.bfloat16)
+    ref = torch.nn.Linear(16, 16, bias=False).to(torch.bfloat16)
+    ref.load_state_dict(model.state_dict())
+    engine = apply_fully_sharded(model, None)
+    opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2), [engine], master_weights=False)
+    assert not opt.fused and all('master' not in st for st in opt.unit_state)
+    ropt = torch.optim.AdamW(ref.parameters(), lr=1e-2)
+    x = torch.randn(4, 16, dtype=torch.bfloat16)
+    for m, o in ((model, opt), (ref, ropt)):
+        o.zero_grad()
+        m(x).float().pow(2).mean().backward()
+        o.step()
+    assert torch.equal(model.weight, ref.weight)
+
+
+def test_wandb_logger_uploads_the_source_tree(tmp_path):
+    """SaveConfigCallback hands the code to the logger like the reference's `experiment.log_code`
+    (save_config_callback.py:39-49): python / shell / template / kernel sources only."""
+    import os
+    from llm_training_b200.lightning.loggers.wandb import WandbLogger, _NullRun
+    lg = WandbLogger(name='run-b', project='proj', save_dir=str(tmp_path), experiment=_NullRun())
+    files = lg.log_code()
+    assert 'llm_training_b200/lms/clm/clm.py' in files and 'csrc/kernels/gemm.cu' in files
+    assert 'scripts/train.sh' in files and not any(f.endswith(('.so', '.md', '.yaml')) for f in files)
+    assert os.path.exists(os.path.join(lg.log_dir, 'code_files.txt'))
+
+
+def test_hf_causal_lm_packed_attention_hook_matches_dense_mask_path():
+    """`attn_implementation: flash_attention_2` routes HF's attention layers to the in-tree packed attention through
+    HF's AttentionInterface (per-token document bounds, no [B,1,T,T] mask; reference: the `_get_unpad_data` patch,
+    hf_causal_lm.py:14-20).  Same logits and gradients as the sdpa path with the block-diagonal 4-D mask."""
+    from transformers import LlamaConfig as HFLlamaConfig
+    from llm_training_b200.models import HFCausalLM, HFCausalLMConfig
+    hf_cfg = dict(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+                  num_key_value_heads=2)
+    torch.manual_seed(0)
+    dense = HFCausalLM(HFCausalLMConfig(hf_config=HFLlamaConfig(**hf_cfg), attn_implementation='sdpa'))
+    hooked = HFCausalLM(HFCausalLMConfig(hf_config=HFLlamaConfig(**hf_cfg), attn_implementation='flash_attention_2'))
+    assert hooked.uses_packed_attention and not dense.uses_packed_attention
+    assert hooked.hf_model.config._attn_implementation == 'llmt_packed'
+    hooked.load_state_dict(dense.state_dict())
+    ids = torch.randint(0, 128, (2, 12))
+    seg = torch.tensor([[1] * 5 + [2] * 4 + [0] * 3, [1] * 12])
+    pos = torch.tensor([[0, 1, 2, 3, 4, 0, 1, 2, 3, 0, 0, 0], list(range(12))])
+    a = dense(input_ids=ids, attention_mask=seg, position_ids=pos).logits
+    b = hooked(input_ids=ids, attention_mask=seg, position_ids=pos).logits
+    keep = seg > 0                                            # pad rows are ignored by every loss
+    assert torch.allclose(a[keep], b[keep], atol=1e-5)
+    (a[keep].float().pow(2).mean()).backward()
+    (b[keep].float().pow(2).mean()).backward()
+    for (n, p), (_, q) in zip(dense.named_parameters(), hooked.named_parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-5), n
