@@ -24,6 +24,7 @@
 // 128-column q steps).
 // The head dimension is always padded to 128 here (TMA zero-fills the out-of-range columns).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -63,6 +64,32 @@ struct BwdCfg {
   static constexpr int kNumBars = 14;
   static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
   static constexpr int kColST = 0, kColDPT = 64, kColDQT = 128 /* two buffers: 128, 192 */, kColDK = 256, kColDV = 384;
+};
+
+// "TS" layout (the default kernel): P^T and dS^T live in TENSOR MEMORY as the A operands of the dV / dK MMAs
+// (tcgen05.mma with A from TMEM), so per 128x64 step the shared-memory ports no longer carry the 16 KB P^T tile
+// write, nor the 32 KB the two MMAs read back; dS^T is additionally written to smem because the dQ^T MMA needs it as
+// its B operand.  dQ^T is single-buffered to make room:
+//   dK @0 (128) | dV @128 (128) | S^T @256 (64) | dP^T @320 (64) | dQ^T @384 (64) | P^T bf16 @448 (32) | dS^T bf16 @480 (32)
+struct BwdTsCfg {
+  static constexpr int kKBytes = kBwdKV * kBwdD * 2;        // 32 KB : 2 boxes [128][64]
+  static constexpr int kQBytes = kBwdQ * kBwdD * 2;         // 16 KB : 2 boxes [64][64]
+  static constexpr int kDSBytes = kBwdKV * kBwdQ * 2;       // 16 KB : 1 box  [128][64]
+  static constexpr int kKOff = 0;
+  static constexpr int kVOff = kKOff + kKBytes;
+  static constexpr int kQOff = kVOff + kKBytes;             // 2 stages
+  static constexpr int kDOOff = kQOff + 2 * kQBytes;        // 2 stages
+  static constexpr int kDSOff = kDOOff + 2 * kQBytes;
+  static constexpr int kDQOff = kDSOff + kDSBytes;          // fp32 [64 q][128 d] staging for the TMA reduce-add
+  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB
+  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 3 x {L[64], delta[64], seg_start[64]}
+  static constexpr int kMetaBytes = 3 * 3 * 64 * 4;
+  static constexpr int kBarOff = kMetaOff + kMetaBytes;
+  // kv_full, qdo_full[2], qdo_empty[2], s_full, s_empty, dp_full, dp_empty, pds_full, pds_empty, dq_full, dq_empty,
+  // acc_done
+  static constexpr int kNumBars = 14;
+  static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
+  static constexpr int kColDK = 0, kColDV = 128, kColST = 256, kColDPT = 320, kColDQT = 384, kColP = 448, kColDS = 480;
 };
 
 struct BwdParams {
@@ -457,6 +484,350 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,1
   if (warp == kBwdTmaWarp) tmem_dealloc<1>(tmem_base, 512);
 }
 
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1)
+attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,128}
+                   const __grid_constant__ CUtensorMap tmQ,     // qkv, box {64,1,64}
+                   const __grid_constant__ CUtensorMap tmDO,    // dO [T][Hq][D], box {64,1,64}
+                   const __grid_constant__ CUtensorMap tmDKV,   // dqkv, box {64,1,128} (store)
+                   const __grid_constant__ CUtensorMap tmDQ,    // dq_acc fp32 [T][Hq*D], box {128, 64}, no swizzle
+                   BwdParams p) {
+  using C = BwdTsCfg;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t sbase = smem_u32(smem);
+  if ((sbase & 1023u) != 0) __trap();
+
+  const uint32_t bars = sbase + C::kBarOff;
+  const uint32_t kv_full = bars;
+  auto qdo_full = [&](int s) { return bars + 8u * (1 + s); };
+  auto qdo_empty = [&](int s) { return bars + 8u * (3 + s); };
+  const uint32_t s_full = bars + 8u * 5, s_empty = bars + 8u * 6;
+  const uint32_t dp_full = bars + 8u * 7, dp_empty = bars + 8u * 8;
+  const uint32_t pds_full = bars + 8u * 9, pds_empty = bars + 8u * 10;
+  const uint32_t dq_full = bars + 8u * 11, dq_empty = bars + 8u * 12;
+  const uint32_t acc_done = bars + 8u * 13;
+  const uint32_t tmem_ptr_smem = bars + 8u * 14;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 14);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = blockIdx.x;                       // kv head (fast axis: longest jobs of every head start first)
+  const int G = p.hq / p.hkv;
+  const int k0 = (int)blockIdx.y * kBwdKV;
+  const int k_last = min(k0 + kBwdKV, p.tokens) - 1;
+  int q_hi = p.seg_end[k_last] - 1;
+  if (p.window > 0) q_hi = min(q_hi, k_last + p.window - 1);
+  q_hi = min(q_hi, p.tokens - 1);
+  const int i_lo = k0 / kBwdQ;
+  const int nq = q_hi / kBwdQ - i_lo + 1;
+  const int n_total = G * nq;
+
+  if (warp == kBwdMmaWarp && lane == 0) {
+    mbar_init(kv_full, 1);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(qdo_full(s), 1);
+      mbar_init(qdo_empty(s), 1);
+    }
+    mbar_init(s_full, 1);
+    mbar_init(s_empty, kBwdComputeThreads);
+    mbar_init(dp_full, 1);
+    mbar_init(dp_empty, kBwdComputeThreads);
+    mbar_init(pds_full, kBwdComputeThreads);
+    mbar_init(pds_empty, 1);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_empty, kBwdComputeThreads);
+    mbar_init(acc_done, 1);
+    fence_barrier_init();
+  }
+  if (warp == kBwdTmaWarp) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmKV);
+      tma_prefetch_desc(&tmQ);
+      tma_prefetch_desc(&tmDO);
+      tma_prefetch_desc(&tmDKV);
+      tma_prefetch_desc(&tmDQ);
+    }
+    tmem_alloc<1>(tmem_ptr_smem, 512);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_gen;
+
+  if (warp == kBwdTmaWarp) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      mbar_arrive_expect_tx(kv_full, 2 * C::kKBytes);
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        tma_load_3d(sbase + C::kKOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + g, k0);
+        tma_load_3d(sbase + C::kVOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + p.hkv + g, k0);
+      }
+      for (int it = 0; it < n_total; ++it) {
+        const int st = it & 1;
+        const int h = g * G + it / nq;
+        const int q0 = (i_lo + it % nq) * kBwdQ;
+        mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1);
+        mbar_arrive_expect_tx(qdo_full(st), 2 * C::kQBytes);
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          tma_load_3d(sbase + C::kQOff + st * C::kQBytes + b * (kBwdQ * 128), &tmQ, qdo_full(st), b * 64, h, q0);
+          tma_load_3d(sbase + C::kDOOff + st * C::kQBytes + b * (kBwdQ * 128), &tmDO, qdo_full(st), b * 64, h, q0);
+        }
+      }
+    }
+  } else if (warp == kBwdMmaWarp) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc_st = make_idesc_bf16(kBwdKV, kBwdQ, false, false);   // S^T, dP^T
+      constexpr uint32_t idesc_dkv = make_idesc_bf16(kBwdKV, kBwdD, false, true);   // dV, dK (A from TMEM)
+      constexpr uint32_t idesc_dq = make_idesc_bf16(kBwdD, kBwdQ, true, true);      // dQ^T
+      const uint32_t ka = sbase + C::kKOff, va = sbase + C::kVOff, dsa = sbase + C::kDSOff;
+      auto issue_s = [&](int it) {
+        const uint32_t qa = sbase + C::kQOff + (it & 1) * C::kQBytes;
+#pragma unroll
+        for (int kk = 0; kk < kBwdD / 16; ++kk) {
+          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
+          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
+          umma_f16<1>(tmem_base + C::kColST, make_smem_desc(ka + aoff, 0, 1024), make_smem_desc(qa + boff, 0, 1024),
+                      idesc_st, kk != 0);
+        }
+        umma_commit(s_full);
+      };
+      auto issue_dp = [&](int it) {
+        const uint32_t doa = sbase + C::kDOOff + (it & 1) * C::kQBytes;
+#pragma unroll
+        for (int kk = 0; kk < kBwdD / 16; ++kk) {
+          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
+          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
+          umma_f16<1>(tmem_base + C::kColDPT, make_smem_desc(va + aoff, 0, 1024),
+                      make_smem_desc(doa + boff, 0, 1024), idesc_st, kk != 0);
+        }
+        umma_commit(dp_full);
+      };
+      mbar_wait(kv_full, 0);
+      mbar_wait(qdo_full(0), 0);
+      tc_fence_after();
+      issue_s(0);
+      issue_dp(0);
+      for (int it = 0; it < n_total; ++it) {
+        if (it + 1 < n_total) {
+          mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+          mbar_wait(s_empty, it & 1);             // S^T(it) is in the threads' registers
+          tc_fence_after();
+          issue_s(it + 1);
+          mbar_wait(dp_empty, it & 1);            // dP^T(it) is in the threads' registers
+          tc_fence_after();
+          issue_dp(it + 1);
+        }
+        mbar_wait(pds_full, it & 1);              // P^T / dS^T (it) are in tensor memory, dS^T also in smem
+        tc_fence_after();
+        const int st = it & 1;
+        const uint32_t qa = sbase + C::kQOff + st * C::kQBytes, doa = sbase + C::kDOOff + st * C::kQBytes;
+#pragma unroll
+        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dV += P^T dO     (A = P^T from TMEM, 8 columns per k-step)
+          umma_f16_ts<1>(tmem_base + C::kColDV, tmem_base + C::kColP + kk * 8,
+                         make_smem_desc(doa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dK += dS^T Q    (A = dS^T from TMEM)
+          umma_f16_ts<1>(tmem_base + C::kColDK, tmem_base + C::kColDS + kk * 8,
+                         make_smem_desc(qa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
+        }
+        mbar_wait(dq_empty, (it & 1) ^ 1);          // dQ^T(it-1) has left its TMEM buffer
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < kBwdKV / 16; ++kk) {  // dQ^T = K^T dS^T
+          umma_f16<1>(tmem_base + C::kColDQT, make_smem_desc(ka + kk * 2048, kBwdKV * 128, 1024),
+                      make_smem_desc(dsa + kk * 2048, kBwdKV * 128, 1024), idesc_dq, kk != 0);
+        }
+        umma_commit(qdo_empty(st));
+        umma_commit(pds_empty);
+        umma_commit(dq_full);
+      }
+      umma_commit(acc_done);
+    }
+  } else {
+    // ===== compute warps: thread <-> kv row r, q-column half hf =====
+    const int r = (warp & 3) * 32 + lane;
+    const int hf = warp >> 2;
+    const int c_base = hf * 32;
+    const int kvi = k0 + r;
+    const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    uint8_t* ds_row = smem + C::kDSOff + r * 128;
+
+    auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 192; };
+    float pre0 = 0.f, pre1 = 0.f;
+    auto meta_fetch = [&](int it) {
+      if (hf != 0) return;
+      const int h = g * G + it / nq;
+      const int q = (i_lo + it % nq) * kBwdQ + (r & 63);
+      const bool ok = q < p.tokens;
+      if (r < 64) {
+        pre0 = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
+        pre1 = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
+      } else {
+        pre0 = __int_as_float(ok ? p.seg_start[q] : 0x7fffffff);
+      }
+    };
+    auto meta_store = [&](int it) {
+      if (hf != 0) return;
+      float* m = meta(it);
+      if (r < 64) { m[r] = pre0; m[64 + r] = pre1; }
+      else        { m[128 + (r - 64)] = pre0; }
+    };
+    uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
+    auto compute_p = [&](int it) {
+      const int q0 = (i_lo + it % nq) * kBwdQ;
+      const float* mL = meta(it);
+      const int* mS = reinterpret_cast<const int*>(mL + 128);
+      const bool need_mask = (q0 < k0 + kBwdKV - 1) || (mS[63] > k0) || (p.window > 0);
+      mbar_wait(s_full, it & 1);
+      tc_fence_after();
+      tmem_ld_32x32b_x32(t_lane + C::kColST + c_base, sv);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(s_empty);                              // S^T(it+1) may overwrite the columns now
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c_base + c]));
+        if (need_mask) {
+          const int q = q0 + c_base + c;
+          const bool valid = (mS[c_base + c] <= kvi) && (kvi <= q) && (p.window == 0 || q - kvi < p.window);
+          pv = valid ? pv : 0.f;
+        }
+        sv[c] = __float_as_uint(pv);
+      }
+    };
+
+    auto drain_dq = [&](int j, int meta_it) {
+      uint32_t dq[32];
+      if (j >= 0) {
+        mbar_wait(dq_full, j & 1);
+        tc_fence_after();
+        tmem_ld_32x32b_x32(t_lane + C::kColDQT + c_base, dq);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(dq_empty);
+        if (threadIdx.x == 0) tma_store_wait_read<0>();   // previous reduce has finished reading the staging tile
+      }
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (j >= 0) {
+        float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
+#pragma unroll
+        for (int c = 0; c < 32; ++c) stage[(c_base + c) * kBwdD + r] = __uint_as_float(dq[c]);
+      }
+      if (meta_it < n_total) meta_store(meta_it);
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 2, 256;" ::: "memory");
+      if (j >= 0 && threadIdx.x == 0) {
+        const int hj = g * G + j / nq;
+        const int qj = (i_lo + j % nq) * kBwdQ;
+        tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, hj * p.head_dim, qj);
+        tma_store_commit();
+      }
+    };
+
+    meta_fetch(0);
+    meta_store(0);
+    if (n_total > 1) { meta_fetch(1); meta_store(1); }
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    compute_p(0);
+
+    for (int it = 0; it < n_total; ++it) {
+      const float* mD = meta(it) + 64;
+      if (it + 2 < n_total) meta_fetch(it + 2);
+
+      // ---- P^T(it): registers -> tensor memory (bf16 pairs, column c/2 holds q columns c, c+1)
+      mbar_wait(pds_empty, (it & 1) ^ 1);                 // dV / dK / dQ MMAs of the previous step are done
+      {
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16x2(__uint_as_float(sv[2 * c]), __uint_as_float(sv[2 * c + 1]));
+        tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
+      }
+      // ---- dS^T(it) = P^T o (dP^T - delta) * scale -> tensor memory (dK) and smem (B operand of dQ^T)
+      {
+        uint32_t dp[32];
+        mbar_wait(dp_full, it & 1);
+        tc_fence_after();
+        tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(dp_empty);
+        uint32_t pk[16];
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float a = __uint_as_float(sv[2 * c]) * (__uint_as_float(dp[2 * c]) - mD[c_base + 2 * c]) * p.scale;
+          const float b = __uint_as_float(sv[2 * c + 1]) * (__uint_as_float(dp[2 * c + 1]) - mD[c_base + 2 * c + 1]) * p.scale;
+          pk[c] = pack_bf16x2(a, b);
+        }
+        tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch)
+          *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
+              make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+      }
+      tmem_st_wait();
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(pds_full);
+
+      // ---- dQ^T(it-1): TMEM -> smem [q][d] fp32 -> TMA reduce-add, under the MMAs of this step
+      drain_dq(it - 1, it + 2);
+
+      // ---- while the tensor cores run dP^T(it+1) and dV/dK/dQ^T(it), build P^T(it+1)
+      if (it + 1 < n_total) compute_p(it + 1);
+    }
+    drain_dq(n_total - 1, n_total + 2);
+    if (threadIdx.x == 0) tma_store_wait<0>();
+
+    // ---- dK / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
+    mbar_wait(acc_done, 0);
+    tc_fence_after();
+    {
+      const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
+      uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
+      const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
+#pragma unroll
+      for (int c0 = 0; c0 < kBwdD; c0 += 32) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(t_lane + col + c0, o);
+        tmem_ld_wait();
+        uint8_t* box_row = stage + (c0 / 64) * (kBwdKV * 128) + r * 128;
+#pragma unroll
+        for (int ch = 0; ch < 4; ++ch) {
+          float f[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(o[ch * 8 + e]);
+          const int chunk = ((c0 % 64) / 8) + ch;
+          *reinterpret_cast<bf16x8*>(box_row + ((chunk ^ (r & 7)) << 4)) = pack8(f);
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        tma_store_3d(&tmDKV, sbase + C::kKOff + b * (kBwdKV * 128), b * 64, p.hq + g, k0);
+        tma_store_3d(&tmDKV, sbase + C::kVOff + b * (kBwdKV * 128), b * 64, p.hq + p.hkv + g, k0);
+      }
+      tma_store_commit();
+      tma_store_wait<0>();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kBwdTmaWarp) tmem_dealloc<1>(tmem_base, 512);
+}
+
 }  // namespace attn
 }  // namespace llmt
 
@@ -496,11 +867,21 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   p.seg_start = seg_start; p.seg_end = seg_end; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
   p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f; p.window = window;
-  static bool configured[kMaxDevices] = {};
-  rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
-  if (rc) return rc;
   dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
-  attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+  // LLMT_ATTN_BWD=ss selects the first-generation kernel (every MMA operand in shared memory); default: P^T / dS^T in
+  // tensor memory
+  static const bool use_ss = [] { const char* e = getenv("LLMT_ATTN_BWD"); return e && e[0] == 's'; }();
+  if (use_ss) {
+    static bool configured[kMaxDevices] = {};
+    rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
+    if (rc) return rc;
+    attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+  } else {
+    static bool configured[kMaxDevices] = {};
+    rc = ensure_smem_attr(attn_bwd_ts_kernel, BwdTsCfg::kSmemBytes, configured, "attn_bwd");
+    if (rc) return rc;
+    attn_bwd_ts_kernel<<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+  }
   rc = check_launch("attn_bwd");
   if (rc) return rc;
   const int width = hq * head_dim;

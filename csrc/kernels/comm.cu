@@ -124,18 +124,31 @@ rs_sumsq_kernel(Peers grads, int rank, int world, int64_t shard_elems, T* __rest
     float acc[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    // all peers' vectors are requested before any is consumed: up to 8 independent NVLink loads in flight per
+    // thread (a dependent load per peer left the links latency-bound); summation order stays rank, rank+1, ...
 #pragma unroll 1
-    for (int p = 0; p < world; ++p) {
-      const int src_rank = (rank + p) % world;
-      const uint4 raw = ld_peer_16_fresh(reinterpret_cast<const uint4*>(grads.ptr[src_rank]) + base + i);
-      if constexpr (sizeof(T) == 2) {
-        float f[8];
-        unpack8(*reinterpret_cast<const bf16x8*>(&raw), f);
+    for (int p0 = 0; p0 < world; p0 += 8) {
+      uint4 raw[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) acc[e] += f[e];
-      } else {
-        acc[0] += __uint_as_float(raw.x); acc[1] += __uint_as_float(raw.y);
-        acc[2] += __uint_as_float(raw.z); acc[3] += __uint_as_float(raw.w);
+      for (int q = 0; q < 8; ++q) {
+        if (p0 + q < world) {
+          const int src_rank = (rank + p0 + q) % world;
+          raw[q] = ld_peer_16_fresh(reinterpret_cast<const uint4*>(grads.ptr[src_rank]) + base + i);
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        if (p0 + q < world) {
+          if constexpr (sizeof(T) == 2) {
+            float f[8];
+            unpack8(*reinterpret_cast<const bf16x8*>(&raw[q]), f);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[e] += f[e];
+          } else {
+            acc[0] += __uint_as_float(raw[q].x); acc[1] += __uint_as_float(raw[q].y);
+            acc[2] += __uint_as_float(raw[q].z); acc[3] += __uint_as_float(raw[q].w);
+          }
+        }
       }
     }
     if constexpr (sizeof(T) == 2) {
@@ -152,6 +165,36 @@ rs_sumsq_kernel(Peers grads, int rank, int world, int64_t shard_elems, T* __rest
       for (int e = 0; e < 4; ++e) { acc[e] *= inv_world; ss += acc[e] * acc[e]; }
       reinterpret_cast<float4*>(out_shard)[i] = make_float4(acc[0], acc[1], acc[2], acc[3]);
     }
+  }
+  ss = block_sum(ss, red);
+  if (threadIdx.x == 0) sumsq_partial[blockIdx.x] = ss;
+}
+
+// ---- reduce-scatter (mean) INSIDE THE SWITCH: one multimem.ld_reduce per 16 bytes of this rank's slice returns
+// the sum over every rank's copy (fp32 accumulation in the NVSwitch, result rounded to bf16), so each GPU receives
+// shard bytes instead of world x shard bytes.  `mc` is the multicast address of the gradient buffer (same offset on
+// every rank).  bf16 only.  The sum is rounded to bf16 before the 1/world scaling (exact for power-of-two worlds).
+__global__ void __launch_bounds__(512)
+rs_sumsq_mc_kernel(const uint4* __restrict__ mc, int rank, int64_t shard_elems, __nv_bfloat16* __restrict__ out_shard,
+                   float inv_world, float* __restrict__ sumsq_partial) {
+  __shared__ float red[32];
+  const int64_t nvec = shard_elems / 8;
+  const int64_t base = (int64_t)rank * nvec;
+  float ss = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+    uint4 raw;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(raw.x), "=r"(raw.y), "=r"(raw.z), "=r"(raw.w) : "l"(mc + base + i) : "memory");
+    float acc[8];
+    unpack8(*reinterpret_cast<const bf16x8*>(&raw), acc);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] *= inv_world;
+    const bf16x8 packed = pack8(acc);
+    float back[8];
+    unpack8(packed, back);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ss += back[e] * back[e];
+    reinterpret_cast<uint4*>(out_shard)[i] = *reinterpret_cast<const uint4*>(&packed);
   }
   ss = block_sum(ss, red);
   if (threadIdx.x == 0) sumsq_partial[blockIdx.x] = ss;
@@ -366,6 +409,26 @@ extern "C" int llmt_comm_rs_sumsq(const void* const* grad_ptrs, int rank, int wo
 }
 
 // value[0..n) <- sum over ranks (n <= 32). bufs: symmetric fp32 [world][32]; uses barrier slots like llmt_comm_barrier.
+// Same result layout as llmt_comm_rs_sumsq, computed by in-switch reduction (NVLS): mc_grads is the MULTICAST address
+// of the gradient buffer's unit (bf16).  Needs a symmetric allocation that has a multicast mapping; a cross-rank
+// barrier must precede the call (every rank's gradients written) and follow it before the buffer is rewritten.
+extern "C" int llmt_comm_rs_sumsq_mc(const void* mc_grads, int rank, int world, int64_t shard_elems, void* out_shard,
+                                     float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream) {
+  LLMT_REQUIRE(mc_grads != nullptr && (uintptr_t)mc_grads % 16 == 0, "rs_sumsq_mc: multicast pointer missing / misaligned");
+  LLMT_REQUIRE(shard_elems % 8 == 0 && world >= 1 && rank >= 0 && rank < world, "rs_sumsq_mc: bad shard / rank");
+  if (shard_elems == 0) return 0;
+  const int grid = grid_for(shard_elems / 8, 512, 2);
+  rs_sumsq_mc_kernel<<<grid, 512, 0, stream>>>((const uint4*)mc_grads, rank, shard_elems, (__nv_bfloat16*)out_shard,
+                                               1.f / world, partial);
+  int rc = check_launch("comm_rs_sumsq_mc");
+  if (rc) return rc;
+  if (norm_sq != nullptr) {
+    sumsq_accumulate_kernel<<<1, 1024, 0, stream>>>(partial, grid, norm_sq, accumulate_norm);
+    return check_launch("comm_rs_sumsq_mc_final");
+  }
+  return 0;
+}
+
 extern "C" int llmt_comm_allreduce_f32(const void* const* buf_ptrs, const void* const* signal_pads, int rank,
                                        int world, int slot_base, uint32_t epoch, float* value, int n,
                                        cudaStream_t stream) {
@@ -390,8 +453,8 @@ extern "C" int llmt_comm_adamw_push_mc(float* master, float* m, float* v, const 
   if (shard_elems == 0) return 0;
   comm::AdamWArgs a;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
-  a.bc1 = 1.f - powf(beta1, (float)step);
-  a.bc2 = 1.f - powf(beta2, (float)step);
+  a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));   // in double: 1 - beta^step cancels badly in fp32
+  a.bc2 = (float)(1.0 - pow((double)beta2, (double)step));
   a.grad_scale = grad_scale; a.max_norm = max_norm;
   const int grid = grid_for(shard_elems / 8, 256, update_ctas_per_sm());
   if (grad_is_fp32)

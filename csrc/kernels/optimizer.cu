@@ -152,8 +152,8 @@ extern "C" int llmt_adamw(float* master, float* m, float* v, const void* grad, v
                "adamw: buffers must be 16-byte aligned");
   AdamWArgs a;
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay;
-  a.bc1 = 1.f - powf(beta1, (float)step);
-  a.bc2 = 1.f - powf(beta2, (float)step);
+  a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));   // in double: 1 - beta^step cancels badly in fp32
+  a.bc2 = (float)(1.0 - pow((double)beta2, (double)step));
   a.grad_scale = grad_scale; a.max_norm = max_norm;
   int64_t blocks = (n / 4 + 255) / 256;
   const int64_t cap = (int64_t)num_sms() * update_ctas_per_sm();

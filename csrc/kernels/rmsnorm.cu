@@ -123,16 +123,48 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
   }
 }
 
-// dw[c] (+)= sum_p partial[p, c]; output bf16 or fp32
+// dw[c] (+)= sum_p partial[p, c]; output bf16 or fp32.  One CTA per 32 columns: 16 row groups stride over the
+// partial rows (coalesced 128-byte row segments), then a fixed-order smem reduction — the first version walked all
+// (up to 592) partial rows serially in one thread per column and cost 3x the backward kernel it finishes.
+constexpr int kColsumRows = 16;
 template <typename OutT>
-__global__ void colsum_partials_kernel(const float* __restrict__ partial, OutT* __restrict__ out,
-                                       int nparts, int cols, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+__global__ void __launch_bounds__(32 * kColsumRows)
+colsum_partials_kernel(const float* __restrict__ partial, OutT* __restrict__ out, int nparts, int cols,
+                       int accumulate) {
+  __shared__ float tile[kColsumRows][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float s = 0.f;
-  for (int p = 0; p < nparts; ++p) s += partial[(size_t)p * cols + c];
-  if (accumulate) s += (float)out[c];
-  out[c] = (OutT)s;
+  if (c < cols) {
+    float s0 = 0.f, s1 = 0.f;
+    int p = threadIdx.y;
+    for (; p + kColsumRows < nparts; p += 2 * kColsumRows) {
+      s0 += partial[(size_t)p * cols + c];
+      s1 += partial[(size_t)(p + kColsumRows) * cols + c];
+    }
+    if (p < nparts) s0 += partial[(size_t)p * cols + c];
+    s = s0 + s1;
+  }
+  tile[threadIdx.y][threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.y == 0 && c < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int y = 0; y < kColsumRows; ++y) t += tile[y][threadIdx.x];
+    if (accumulate) t += (float)out[c];
+    out[c] = (OutT)t;
+  }
+}
+
+static int launch_colsum(const float* partial, void* dw, int nparts, int cols, int dw_is_fp32, int accumulate,
+                         cudaStream_t stream) {
+  const dim3 block(32, kColsumRows);
+  const int grid = (cols + 31) / 32;
+  if (dw_is_fp32)
+    colsum_partials_kernel<float><<<grid, block, 0, stream>>>(partial, (float*)dw, nparts, cols, accumulate);
+  else
+    colsum_partials_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(partial, (__nv_bfloat16*)dw, nparts, cols,
+                                                                     accumulate);
+  return 0;
 }
 
 int norm_grid(int rows) {
@@ -187,13 +219,7 @@ extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, co
     rmsnorm_bwd_kernel<8><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
   int rc = check_launch("rmsnorm_bwd");
   if (rc) return rc;
-  const int tb = 128;
-  if (dw_is_fp32)
-    colsum_partials_kernel<float><<<(cols + tb - 1) / tb, tb, 0, stream>>>(dw_partial, (float*)dw, grid, cols,
-                                                                          accumulate_dw);
-  else
-    colsum_partials_kernel<__nv_bfloat16>
-        <<<(cols + tb - 1) / tb, tb, 0, stream>>>(dw_partial, (__nv_bfloat16*)dw, grid, cols, accumulate_dw);
+  launch_colsum(dw_partial, dw, grid, cols, dw_is_fp32, accumulate_dw, stream);
   return check_launch("rmsnorm_bwd_colsum");
 }
 
@@ -279,12 +305,6 @@ extern "C" int llmt_rmsnorm_bwd_noalloc(const void* dy, const void* x, const voi
     rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, partial, rows, cols);
   rc = check_launch("rmsnorm_bwd_noalloc");
   if (rc) return rc;
-  const int tb = 128;
-  if (dw_is_fp32)
-    colsum_partials_kernel<float><<<(cols + tb - 1) / tb, tb, 0, stream>>>(partial, (float*)dw, grid, cols,
-                                                                          accumulate_dw);
-  else
-    colsum_partials_kernel<__nv_bfloat16>
-        <<<(cols + tb - 1) / tb, tb, 0, stream>>>(partial, (__nv_bfloat16*)dw, grid, cols, accumulate_dw);
+  launch_colsum(partial, dw, grid, cols, dw_is_fp32, accumulate_dw, stream);
   return check_launch("rmsnorm_bwd_noalloc_colsum");
 }

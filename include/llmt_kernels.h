@@ -75,6 +75,9 @@ int llmt_comm_gather_range(const void* const* shard_ptrs, void* dst_full, int wo
 int llmt_comm_rs_num_partials(void);
 int llmt_comm_rs_sumsq(const void* const* grad_ptrs, int rank, int world, int64_t shard_elems, int is_fp32,
                        void* out_shard, float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream);
+/* reduce-scatter by in-switch reduction (multimem.ld_reduce): mc_grads = multicast address of the unit's gradients */
+int llmt_comm_rs_sumsq_mc(const void* mc_grads, int rank, int world, int64_t shard_elems, void* out_shard,
+                          float* partial, float* norm_sq, int accumulate_norm, cudaStream_t stream);
 /* buf_ptrs: every rank's symmetric fp32 buffer of 2 * world * 32 floats (double-buffered by epoch parity) */
 int llmt_comm_allreduce_f32(const void* const* buf_ptrs, const void* const* signal_pads, int rank, int world,
                             int slot_base, uint32_t epoch, float* value, int n, cudaStream_t stream);

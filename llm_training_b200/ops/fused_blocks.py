@@ -29,10 +29,12 @@ class _NormMultiLinearFn(torch.autograd.Function):
         xn, rstd = rmsnorm_fwd_raw(x2, nw, eps)
         fused = _adjacent_rows_view(weights)
         lazy = getattr(weights[0], '_llmt_lazy_unit', None)
-        if fused is not None and lazy is not None and lazy[1].head_pending \
-                and lazy[1].head[1] == fused.shape[0] and x2.shape[0] % 128 == 0:
-            # ZeRO-3 on NVLink: this GEMM is the first consumer of the layer's q|k|v rows and gathers them itself
-            y = lazy[0].first_gemm(xn, lazy[1])
+        head = lazy[1].lazy_heads.get(lazy[2]) if lazy is not None else None
+        if fused is not None and head is not None and head['pending'] and head['n'] == fused.shape[0] \
+                and x2.shape[0] % 128 == 0:
+            # ZeRO-3 on NVLink: this GEMM is the first consumer of the layer's q|k|v (or gate|up) rows and gathers
+            # them itself
+            y = lazy[0].first_gemm(xn, lazy[1], lazy[2])
         else:
             complete_lazy_gather(weights)
             if fused is None:

@@ -24,8 +24,8 @@ def complete_lazy_gather(weights) -> None:
     (``FlatParamEngine.first_gemm``); any other consumer calls this first."""
     for w in weights:
         lazy = getattr(w, '_llmt_lazy_unit', None)
-        if lazy is not None and lazy[1].head_pending:
-            lazy[0].complete_head(lazy[1])
+        if lazy is not None and lazy[1].lazy_heads[lazy[2]]['pending']:
+            lazy[0].complete_head(lazy[1], lazy[2])
 
 
 def wgrad(dy2: torch.Tensor, x2: torch.Tensor, weights: tuple[torch.Tensor, ...]) -> list:

@@ -93,10 +93,14 @@ class ShardedUnit:
         self.in_backward = False
         self.gather_event: Any = None
         self.gather_pending = False
-        # ZeRO-3 on NVLink: (element offset, rows, cols) of the row-stacked weights the unit's FIRST GEMM consumes
-        # (q|k|v); in forward that GEMM gathers them itself, the side-stream gather covers the rest of the unit
-        self.head: tuple[int, int, int] | None = None
-        self.head_pending = False
+        # ZeRO-3 on NVLink: row-stacked weight groups whose consuming GEMM gathers them itself in forward (q|k|v and
+        # gate|up of a decoder layer): key -> {'off': element offset, 'n': rows, 'k': cols, 'pending': bool}.  The
+        # side-stream gather covers the rest of the unit.
+        self.lazy_heads: dict[int, dict] = {}
+
+    @property
+    def head_pending(self) -> bool:
+        return any(h['pending'] for h in self.lazy_heads.values())
 
     @property
     def param_shard(self) -> torch.Tensor:
@@ -158,7 +162,16 @@ class FlatParamEngine:
                                               arena_offset=off, reshard=True, shard_store=store,
                                               with_grad=not self.frozen))
                 off += ssz
-            self.nvlink_grads = False
+            # ZeRO-3 gradients on NVLink: a unit's full gradient buffer is ordinary (resizable) memory, so right
+            # before its reduce-scatter it is staged into one of TWO symmetric slots that every peer can read (or the
+            # switch can reduce).  Two are enough: the barrier that opens reduce-scatter j+1 proves every rank has
+            # finished pulling slot (j mod 2), and the copy for unit j+2 is queued behind it on the same stream.
+            self.grad_ring = None
+            import os as _os
+            if self.shard_arena is not None and not self.frozen and _os.environ.get('LLMT_ZERO3_NVLINK_GRADS', '1') != '0':
+                biggest = max(ShardedUnit.layout(ps, self.world)[2] for _, ps in units)
+                self.grad_ring = [self.comm.alloc(biggest, next(iter(dtypes))) for _ in range(2)]
+                self._ring_next = 0
         elif self.nvlink and len(dtypes) == 1 and not self.frozen:
             # one symmetric allocation for all parameters and one for all gradients: peers address any unit as
             # arena base + offset, and a single rendezvous exchanges the handles
@@ -182,8 +195,9 @@ class FlatParamEngine:
                 assert all(p.dtype == dtype for _, p in params), f'unit {name}: mixed parameter dtypes'
                 self.units.append(ShardedUnit(name, params, self.world, self.rank, device, dtype, grad_dtype or dtype,
                                               with_grad=not self.frozen))
-        # `nvlink` = parameters travel through our kernels; `nvlink_grads` = gradients do too (resident mode only)
-        self.nvlink_grads = self.nvlink and not self.reshard
+        # `nvlink` = parameters travel through our kernels; `nvlink_grads` = gradients do too (resident mode: straight
+        # from the symmetric gradient arena; ZeRO-3: through the staging ring)
+        self.nvlink_grads = self.nvlink and (not self.reshard or getattr(self, 'grad_ring', None) is not None)
         import os
         self.fused_first_gemm = os.environ.get('LLMT_FUSED_FIRST_GEMM', '1') != '0'
         self._forward_order: list[ShardedUnit] = []      # hooked units in the order the last forward used them
@@ -256,7 +270,14 @@ class FlatParamEngine:
                     dist.all_reduce(p.grad, group=self.tp_axis.group)
         if self.world == 1:
             return
-        if self.nvlink_grads:
+        if self.nvlink_grads and self.reshard:
+            slot = self.grad_ring[self._ring_next]
+            self._ring_next ^= 1
+            slot.tensor[:u.padded_numel].copy_(u.flat_grad)      # on the communication stream, behind the unit's backward
+            self.comm.reduce_scatter_sumsq(slot, 0, u.shard_numel, u.grad_shard, self._norm_sq,
+                                           accumulate_norm=self._norm_accumulating)
+            self._norm_accumulating = True
+        elif self.nvlink_grads:
             # barrier + pull of this rank's slice from every peer + squared-norm partial, one pass over NVLink
             esize = u.flat_grad.element_size()
             self.comm.reduce_scatter_sumsq(self.grad_arena, u.arena_offset * esize, u.shard_numel, u.grad_shard,
@@ -357,55 +378,62 @@ class FlatParamEngine:
 
     # ------------------------------------------------------------------ ZeRO-3: gather before use, drop after use
     def enable_fused_first_gemm(self, model: nn.Module) -> None:
-        """ZeRO-3 + NVLink: let the first GEMM of every decoder layer (q|k|v projection) pull its own weights from
-        the owners' slices while it runs (``NVLinkComm.gemm_weight_gather``) instead of waiting for a gather."""
+        """ZeRO-3 + NVLink: let the column GEMMs that open each half of a decoder layer — the q|k|v projection and
+        the gate|up projection (285 of a LLaMA-3-8B layer's 436 MB) — pull their own weights from the owners' slices
+        while they run (``NVLinkComm.gemm_weight_gather``) instead of waiting for a gather."""
         if self.shard_arena is None or not hasattr(model, 'sharding_units'):
             return
+        n_max = 0
         for _, module in model.sharding_units():
-            attn = getattr(module, 'self_attn', None)
-            if attn is None:
-                continue
-            if all(hasattr(attn, n) for n in ('q_proj', 'k_proj', 'v_proj')):
-                ws = [attn.q_proj.weight, attn.k_proj.weight, attn.v_proj.weight]
-            elif hasattr(attn, 'qkv_proj'):
-                ws = [attn.qkv_proj.weight]
-            else:
-                continue
-            u = self._param_to_unit.get(id(ws[0]))
-            if u is None or any(self._param_to_unit.get(id(w)) is not u for w in ws):
-                continue
-            offs = {id(p): o for (_, p), o in zip(u.params, u.offsets)}
-            k = ws[0].shape[1]
-            ok, expect = True, offs[id(ws[0])]
-            for w in ws:
-                ok &= w.dim() == 2 and w.shape[1] == k and w.dtype == torch.bfloat16 and offs[id(w)] == expect
-                expect += w.numel()
-            if not ok or k % 8:
-                continue
-            u.head = (offs[id(ws[0])], sum(w.shape[0] for w in ws), k)
-            for w in ws:
-                w._llmt_lazy_unit = (self, u)
-        n_max = max((u.head[1] for u in self.units if u.head is not None), default=0)
+            groups = []
+            attn, mlp = getattr(module, 'self_attn', None), getattr(module, 'mlp', None)
+            if attn is not None and all(hasattr(attn, n) for n in ('q_proj', 'k_proj', 'v_proj')):
+                groups.append([attn.q_proj.weight, attn.k_proj.weight, attn.v_proj.weight])
+            elif attn is not None and hasattr(attn, 'qkv_proj'):
+                groups.append([attn.qkv_proj.weight])
+            if mlp is not None and all(hasattr(mlp, n) for n in ('gate_proj', 'up_proj')):
+                groups.append([mlp.gate_proj.weight, mlp.up_proj.weight])
+            elif mlp is not None and hasattr(mlp, 'gate_up_proj'):
+                groups.append([mlp.gate_up_proj.weight])
+            for ws in groups:
+                u = self._param_to_unit.get(id(ws[0]))
+                if u is None or any(self._param_to_unit.get(id(w)) is not u for w in ws):
+                    continue
+                offs = {id(p): o for (_, p), o in zip(u.params, u.offsets)}
+                k = ws[0].shape[1]
+                ok, expect = True, offs[id(ws[0])]
+                for w in ws:
+                    ok &= w.dim() == 2 and w.shape[1] == k and w.dtype == torch.bfloat16 and offs[id(w)] == expect
+                    expect += w.numel()
+                if not ok or k % 8:
+                    continue
+                key = id(ws[0])
+                u.lazy_heads[key] = {'off': offs[id(ws[0])], 'n': sum(w.shape[0] for w in ws), 'k': k,
+                                     'pending': False}
+                n_max = max(n_max, u.lazy_heads[key]['n'])
+                for w in ws:
+                    w._llmt_lazy_unit = (self, u, key)
         if n_max:
             self._head_flags = torch.zeros(n_max // 256 + 2, dtype=torch.int32, device=self.device)
 
-    def first_gemm(self, x: torch.Tensor, u: ShardedUnit) -> torch.Tensor:
-        """``x @ head(u)^T`` while the head weights are gathered by the GEMM itself."""
-        off, n, _ = u.head
+    def first_gemm(self, x: torch.Tensor, u: ShardedUnit, key: int) -> torch.Tensor:
+        """``x @ W^T`` for the lazy weight group ``key`` of ``u`` while the GEMM itself gathers W."""
+        h = u.lazy_heads[key]
         esize = u.flat_param.element_size()
-        y = self.comm.gemm_weight_gather(x, self.shard_arena, u.arena_offset * esize, u.flat_param, off,
-                                         u.shard_numel, n, self._head_flags)
-        u.head_pending = False
+        y = self.comm.gemm_weight_gather(x, self.shard_arena, u.arena_offset * esize, u.flat_param, h['off'],
+                                         u.shard_numel, h['n'], self._head_flags)
+        h['pending'] = False
         return y
 
-    def complete_head(self, u: ShardedUnit) -> None:
-        """Some other consumer needs the head weights first: gather them now on the current stream."""
-        if u.head_pending:
-            off, n, k = u.head
-            esize = u.flat_param.element_size()
-            self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
-                                   off * esize, (off + n * k) * esize, barrier=False)
-            u.head_pending = False
+    def complete_head(self, u: ShardedUnit, key: int | None = None) -> None:
+        """Some other consumer needs lazy weights first: gather them now on the current stream."""
+        esize = u.flat_param.element_size()
+        for hk, h in u.lazy_heads.items():
+            if h['pending'] and (key is None or hk == key):
+                lo, hi = h['off'] * esize, (h['off'] + h['n'] * h['k']) * esize
+                self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
+                                       lo, hi, barrier=False)
+                h['pending'] = False
 
     def unshard(self, u: ShardedUnit, lazy_head: bool = False) -> None:
         """Give ``flat_param`` storage and start gathering every rank's slice into it on the side stream.  With
@@ -414,8 +442,9 @@ class FlatParamEngine:
             return
         u._set_storage(u.flat_param, True)
         u.is_sharded = False
-        u.head_pending = bool(lazy_head and u.head is not None and self._comm_stream is not None
-                              and self.fused_first_gemm)
+        lazy = bool(lazy_head and u.lazy_heads and self._comm_stream is not None and self.fused_first_gemm)
+        for h in u.lazy_heads.values():
+            h['pending'] = lazy
         main = torch.cuda.current_stream(self.device) if self._comm_stream is not None else None
         if self._comm_stream is not None:
             self._comm_stream.wait_stream(main)        # the slice may have just been written by the optimizer
@@ -432,9 +461,16 @@ class FlatParamEngine:
         if self.shard_arena is not None:
             esize = u.flat_param.element_size()
             if u.head_pending:
-                off, n, k = u.head
-                self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
-                                       0, u.padded_numel * esize, off * esize, (off + n * k) * esize)
+                # everything except the lazy groups: the ranges between them, one launch each, one barrier in front
+                pos, first = 0, True
+                spans = sorted((h['off'] * esize, (h['off'] + h['n'] * h['k']) * esize)
+                               for h in u.lazy_heads.values() if h['pending'])
+                for lo, hi in spans + [(u.padded_numel * esize, u.padded_numel * esize)]:
+                    if lo > pos or first:
+                        self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize,
+                                               u.flat_param, pos, max(lo, pos), barrier=first)
+                        first = False
+                    pos = max(pos, hi)
                 return
             self.comm.gather_shards(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param)
         else:
@@ -451,7 +487,8 @@ class FlatParamEngine:
         if u.is_sharded or not self.reshard:
             return
         self.wait_unshard(u, keep_lazy_head=True)     # never free under an in-flight gather
-        u.head_pending = False
+        for h in u.lazy_heads.values():
+            h['pending'] = False
         u._set_storage(u.flat_param, False)
         u.is_sharded = True
 

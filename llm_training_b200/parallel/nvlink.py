@@ -68,6 +68,9 @@ class NVLinkComm(Comm):
         self._allreduce_epoch = 0
         import os
         self.use_multicast = os.environ.get('LLMT_MULTICAST', '1') != '0'   # NVSwitch multicast stores when mapped
+        # gradient reduce-scatter by in-switch reduction (multimem.ld_reduce) when the buffer has a multicast mapping
+        self.use_multimem_rs = os.environ.get('LLMT_MULTIMEM_RS', '1') != '0'
+        self.last_rs_kind = None          # 'multimem' | 'pull': what the last reduce-scatter actually ran
         self._lib = _lib.lib()
         self._rs_partial = torch.empty(self._lib.llmt_comm_rs_num_partials(), dtype=torch.float32, device=self.device)
         dist.barrier(group=self.group, device_ids=[self.device.index])
@@ -148,6 +151,16 @@ class NVLinkComm(Comm):
     def reduce_scatter_sumsq(self, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, out_shard: torch.Tensor,
                              norm_sq: torch.Tensor, accumulate_norm: bool) -> None:
         self.barrier()                                           # every rank finished writing this unit's grads
+        if self.use_multimem_rs and arena.multicast_ptr and out_shard.dtype == torch.bfloat16:
+            # one multimem.ld_reduce per 16 bytes: the NVSwitch sums every rank's copy, this GPU receives 1/world of
+            # what the pull version reads
+            self.last_rs_kind = 'multimem'
+            _lib.check(self._lib.llmt_comm_rs_sumsq_mc(
+                ctypes.c_void_p(arena.multicast_ptr + byte_offset), _lib.c_int(self.rank), _lib.c_int(self.size),
+                _lib.c_i64(shard_numel), _lib.ptr(out_shard), _lib.ptr(self._rs_partial), _lib.ptr(norm_sq),
+                _lib.c_int(accumulate_norm), _lib.stream()), 'comm_rs_sumsq_mc')
+            return
+        self.last_rs_kind = 'pull'
         _lib.check(self._lib.llmt_comm_rs_sumsq(
             arena.peer_ptrs_at(byte_offset), _lib.c_int(self.rank), _lib.c_int(self.size), _lib.c_i64(shard_numel),
             _lib.c_int(out_shard.dtype == torch.float32), _lib.ptr(out_shard), _lib.ptr(self._rs_partial),
