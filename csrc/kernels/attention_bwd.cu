@@ -80,10 +80,10 @@ struct BwdTsCfg {
   static constexpr int kQOff = kVOff + kKBytes;             // 2 stages
   static constexpr int kDOOff = kQOff + 2 * kQBytes;        // 2 stages
   static constexpr int kDSOff = kDOOff + 2 * kQBytes;
-  static constexpr int kDQOff = kDSOff + kDSBytes;          // fp32 [64 q][128 d] staging for the TMA reduce-add
-  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB
-  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 3 x {L[64], delta[64], seg_start[64]}
-  static constexpr int kMetaBytes = 3 * 3 * 64 * 4;
+  static constexpr int kDQOff = kDSOff + kDSBytes;          // 2 x fp32 [64 q][128 d] staging for the TMA reduce-add
+  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB each
+  static constexpr int kMetaOff = kDQOff + 2 * kDQBytes;    // 3 x {L[64], delta[64]}
+  static constexpr int kMetaBytes = 3 * 2 * 64 * 4;
   static constexpr int kBarOff = kMetaOff + kMetaBytes;
   // kv_full, qdo_full[2], qdo_empty[2], s_full, s_empty, dp_full, dp_empty, pds_full, pds_empty, dq_full, dq_empty,
   // acc_done
@@ -132,10 +132,10 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __re
   if (lane == 0) delta[(size_t)h * tokens + t] = s;
 }
 
-// dqkv[t, 0 : Hq*D] = bf16(dq_acc[t, :])
+// dqkv[t, 0 : Hq*D] = bf16(mul * dq_acc[t, :])
 __global__ void __launch_bounds__(256)
 attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, int tokens, int width,
-                       int64_t out_stride) {
+                       int64_t out_stride, float mul) {
   const int vec_per_row = width >> 3;
   const int64_t total = (int64_t)tokens * vec_per_row;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
@@ -144,7 +144,7 @@ attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restri
     const int c = (int)(i - t * vec_per_row) << 3;
     const float4 a = *reinterpret_cast<const float4*>(dq_acc + t * width + c);
     const float4 b = *reinterpret_cast<const float4*>(dq_acc + t * width + c + 4);
-    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+    const float f[8] = {a.x * mul, a.y * mul, a.z * mul, a.w * mul, b.x * mul, b.y * mul, b.z * mul, b.w * mul};
     st_bf16x8(dqkv + t * out_stride + c, pack8(f));
   }
 }
@@ -514,7 +514,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   const uint32_t tmem_ptr_smem = bars + 8u * 14;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 14);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const int g = blockIdx.x;                       // kv head (fast axis: longest jobs of every head start first)
   const int G = p.hq / p.hkv;
   const int k0 = (int)blockIdx.y * kBwdKV;
@@ -582,76 +582,86 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       }
     }
   } else if (warp == kBwdMmaWarp) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc_st = make_idesc_bf16(kBwdKV, kBwdQ, false, false);   // S^T, dP^T
-      constexpr uint32_t idesc_dkv = make_idesc_bf16(kBwdKV, kBwdD, false, true);   // dV, dK (A from TMEM)
-      constexpr uint32_t idesc_dq = make_idesc_bf16(kBwdD, kBwdQ, true, true);      // dQ^T
-      const uint32_t ka = sbase + C::kKOff, va = sbase + C::kVOff, dsa = sbase + C::kDSOff;
-      auto issue_s = [&](int it) {
-        const uint32_t qa = sbase + C::kQOff + (it & 1) * C::kQBytes;
+    // ===== MMA issuer: the WHOLE warp walks the loop (uniform control flow, waits included); one elected lane
+    // issues.  Descriptors are built once; a k-step only adds a constant to the start-address field.
+    constexpr uint32_t idesc_st = make_idesc_bf16(kBwdKV, kBwdQ, false, false);   // S^T, dP^T
+    constexpr uint32_t idesc_dkv = make_idesc_bf16(kBwdKV, kBwdD, false, true);   // dV, dK (A from TMEM)
+    constexpr uint32_t idesc_dq = make_idesc_bf16(kBwdD, kBwdQ, true, true);      // dQ^T
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t k_a = make_smem_desc(sbase + C::kKOff, 0, 1024);               // K  as A, K-major   (S^T)
+    const uint64_t v_a = make_smem_desc(sbase + C::kVOff, 0, 1024);               // V  as A, K-major   (dP^T)
+    const uint64_t kt_a = make_smem_desc(sbase + C::kKOff, kBwdKV * 128, 1024);   // K^T as A, MN-major (dQ^T)
+    const uint64_t ds_b = make_smem_desc(sbase + C::kDSOff, kBwdKV * 128, 1024);  // dS^T as B, MN-major (dQ^T)
+    const uint64_t q_b0 = make_smem_desc(sbase + C::kQOff, 0, 1024);              // Q  as B, K-major   (S^T), stage 0
+    const uint64_t do_b0 = make_smem_desc(sbase + C::kDOOff, 0, 1024);            // dO as B, K-major   (dP^T)
+    const uint64_t q_mn0 = make_smem_desc(sbase + C::kQOff, kBwdQ * 128, 1024);   // Q  as B, MN-major  (dK)
+    const uint64_t do_mn0 = make_smem_desc(sbase + C::kDOOff, kBwdQ * 128, 1024); // dO as B, MN-major  (dV)
+    constexpr uint64_t kStage = C::kQBytes >> 4;                                  // descriptor units per Q / dO stage
+    // k-step offsets in descriptor units (16 bytes): K-major tiles hold 4 k-steps per 64-column box
+    auto kmaj = [](int kk, int rows) -> uint64_t { return (uint64_t)((kk / 4) * (rows * 8) + (kk % 4) * 2); };
+    auto issue_s = [&](int it) {
+      const uint64_t q_b = q_b0 + (uint64_t)(it & 1) * kStage;
 #pragma unroll
-        for (int kk = 0; kk < kBwdD / 16; ++kk) {
-          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
-          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
-          umma_f16<1>(tmem_base + C::kColST, make_smem_desc(ka + aoff, 0, 1024), make_smem_desc(qa + boff, 0, 1024),
-                      idesc_st, kk != 0);
-        }
-        umma_commit(s_full);
-      };
-      auto issue_dp = [&](int it) {
-        const uint32_t doa = sbase + C::kDOOff + (it & 1) * C::kQBytes;
+      for (int kk = 0; kk < kBwdD / 16; ++kk)
+        umma_f16<1>(tb + C::kColST, k_a + kmaj(kk, kBwdKV), q_b + kmaj(kk, kBwdQ), idesc_st, kk != 0);
+      umma_commit(s_full);
+    };
+    auto issue_dp = [&](int it) {
+      const uint64_t do_b = do_b0 + (uint64_t)(it & 1) * kStage;
 #pragma unroll
-        for (int kk = 0; kk < kBwdD / 16; ++kk) {
-          const uint32_t aoff = (kk / 4) * (kBwdKV * 128) + (kk % 4) * 32;
-          const uint32_t boff = (kk / 4) * (kBwdQ * 128) + (kk % 4) * 32;
-          umma_f16<1>(tmem_base + C::kColDPT, make_smem_desc(va + aoff, 0, 1024),
-                      make_smem_desc(doa + boff, 0, 1024), idesc_st, kk != 0);
-        }
-        umma_commit(dp_full);
-      };
-      mbar_wait(kv_full, 0);
-      mbar_wait(qdo_full(0), 0);
-      tc_fence_after();
+      for (int kk = 0; kk < kBwdD / 16; ++kk)
+        umma_f16<1>(tb + C::kColDPT, v_a + kmaj(kk, kBwdKV), do_b + kmaj(kk, kBwdQ), idesc_st, kk != 0);
+      umma_commit(dp_full);
+    };
+    mbar_wait(kv_full, 0);
+    mbar_wait(qdo_full(0), 0);
+    tc_fence_after();
+    if (elect_one()) {
       issue_s(0);
       issue_dp(0);
-      for (int it = 0; it < n_total; ++it) {
-        if (it + 1 < n_total) {
-          mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
-          mbar_wait(s_empty, it & 1);             // S^T(it) is in the threads' registers
-          tc_fence_after();
-          issue_s(it + 1);
-          mbar_wait(dp_empty, it & 1);            // dP^T(it) is in the threads' registers
-          tc_fence_after();
-          issue_dp(it + 1);
-        }
-        mbar_wait(pds_full, it & 1);              // P^T / dS^T (it) are in tensor memory, dS^T also in smem
+    }
+    __syncwarp();
+#pragma unroll 1
+    for (int it = 0; it < n_total; ++it) {
+      if (it + 1 < n_total) {
+        mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+        mbar_wait(s_empty, it & 1);             // S^T(it) is in the threads' registers
         tc_fence_after();
-        const int st = it & 1;
-        const uint32_t qa = sbase + C::kQOff + st * C::kQBytes, doa = sbase + C::kDOOff + st * C::kQBytes;
-#pragma unroll
-        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dV += P^T dO     (A = P^T from TMEM, 8 columns per k-step)
-          umma_f16_ts<1>(tmem_base + C::kColDV, tmem_base + C::kColP + kk * 8,
-                         make_smem_desc(doa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
-        }
-#pragma unroll
-        for (int kk = 0; kk < kBwdQ / 16; ++kk) {   // dK += dS^T Q    (A = dS^T from TMEM)
-          umma_f16_ts<1>(tmem_base + C::kColDK, tmem_base + C::kColDS + kk * 8,
-                         make_smem_desc(qa + kk * 2048, kBwdQ * 128, 1024), idesc_dkv, (it | kk) != 0);
-        }
-        mbar_wait(dq_empty, (it & 1) ^ 1);          // dQ^T(it-1) has left its TMEM buffer
+        if (elect_one()) issue_s(it + 1);
+        __syncwarp();
+        mbar_wait(dp_empty, it & 1);            // dP^T(it) is in the threads' registers
         tc_fence_after();
+        if (elect_one()) issue_dp(it + 1);
+        __syncwarp();
+      }
+      mbar_wait(pds_full, it & 1);              // P^T / dS^T (it) are in tensor memory, dS^T also in smem
+      tc_fence_after();
+      const uint64_t q_mn = q_mn0 + (uint64_t)(it & 1) * kStage, do_mn = do_mn0 + (uint64_t)(it & 1) * kStage;
+      if (elect_one()) {
 #pragma unroll
-        for (int kk = 0; kk < kBwdKV / 16; ++kk) {  // dQ^T = K^T dS^T
-          umma_f16<1>(tmem_base + C::kColDQT, make_smem_desc(ka + kk * 2048, kBwdKV * 128, 1024),
-                      make_smem_desc(dsa + kk * 2048, kBwdKV * 128, 1024), idesc_dq, kk != 0);
-        }
-        umma_commit(qdo_empty(st));
+        for (int kk = 0; kk < kBwdQ / 16; ++kk)   // dV += P^T dO     (A = P^T from TMEM, 8 columns per k-step)
+          umma_f16_ts<1>(tb + C::kColDV, tb + C::kColP + kk * 8, do_mn + (uint64_t)kk * 128, idesc_dkv,
+                         (it | kk) != 0);
+#pragma unroll
+        for (int kk = 0; kk < kBwdQ / 16; ++kk)   // dK += dS^T Q    (A = dS^T from TMEM; scaled at the end)
+          umma_f16_ts<1>(tb + C::kColDK, tb + C::kColDS + kk * 8, q_mn + (uint64_t)kk * 128, idesc_dkv,
+                         (it | kk) != 0);
+      }
+      __syncwarp();
+      mbar_wait(dq_empty, (it & 1) ^ 1);          // dQ^T(it-1) has left its TMEM buffer
+      tc_fence_after();
+      if (elect_one()) {
+#pragma unroll
+        for (int kk = 0; kk < kBwdKV / 16; ++kk)  // dQ^T = K^T dS^T
+          umma_f16<1>(tb + C::kColDQT, kt_a + (uint64_t)kk * 128, ds_b + (uint64_t)kk * 128, idesc_dq, kk != 0);
+        umma_commit(qdo_empty(it & 1));
         umma_commit(pds_empty);
         umma_commit(dq_full);
       }
-      umma_commit(acc_done);
+      __syncwarp();
     }
+    if (elect_one()) umma_commit(acc_done);
+    __syncwarp();
   } else {
     // ===== compute warps: thread <-> kv row r, q-column half hf =====
     const int r = (warp & 3) * 32 + lane;
@@ -661,140 +671,170 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     const uint32_t t_lane = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
     uint8_t* ds_row = smem + C::kDSOff + r * 128;
 
-    auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 192; };
-    float pre0 = 0.f, pre1 = 0.f;
+    // A kv row sees the queries q in [kvi, q_end): its own document from its position on, clipped by the window.
+    // Both ends are constants of the thread, so masking a block is one unsigned compare per element and needs no
+    // per-query metadata.  Blocks strictly inside every row's range skip it (CTA-uniform test below).
+    int q_end = 0;
+    if (kvi < p.tokens) {
+      q_end = p.seg_end[kvi];
+      if (p.window > 0) q_end = min(q_end, kvi + p.window);
+    }
+    const uint32_t valid_len = q_end > kvi ? (uint32_t)(q_end - kvi) : 0u;
+    int q_end_first = p.seg_end[k0];                     // smallest q_end of the tile (bounds are non-decreasing)
+    if (p.window > 0) q_end_first = min(q_end_first, k0 + p.window);
+    const bool tail_tile = k0 + kBwdKV > p.tokens;
+
+    // Per-step metadata {L[64], delta[64]} lives in a 3-deep smem ring: step it+2 is fetched from global memory
+    // while step it is processed and published by the CTA barrier of the dQ drain.
+    auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 128; };
+    float pre = 0.f;
     auto meta_fetch = [&](int it) {
-      if (hf != 0) return;
+      if (hf != 0) return;                               // warps 0-3 fetch for everybody
       const int h = g * G + it / nq;
       const int q = (i_lo + it % nq) * kBwdQ + (r & 63);
       const bool ok = q < p.tokens;
-      if (r < 64) {
-        pre0 = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
-        pre1 = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
-      } else {
-        pre0 = __int_as_float(ok ? p.seg_start[q] : 0x7fffffff);
-      }
+      if (r < 64) pre = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
+      else        pre = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
     };
     auto meta_store = [&](int it) {
       if (hf != 0) return;
-      float* m = meta(it);
-      if (r < 64) { m[r] = pre0; m[64 + r] = pre1; }
-      else        { m[128 + (r - 64)] = pre0; }
-    };
-    uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
-    auto compute_p = [&](int it) {
-      const int q0 = (i_lo + it % nq) * kBwdQ;
-      const float* mL = meta(it);
-      const int* mS = reinterpret_cast<const int*>(mL + 128);
-      const bool need_mask = (q0 < k0 + kBwdKV - 1) || (mS[63] > k0) || (p.window > 0);
-      mbar_wait(s_full, it & 1);
-      tc_fence_after();
-      tmem_ld_32x32b_x32(t_lane + C::kColST + c_base, sv);
-      tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(s_empty);                              // S^T(it+1) may overwrite the columns now
-#pragma unroll
-      for (int c = 0; c < 32; ++c) {
-        float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -mL[c_base + c]));
-        if (need_mask) {
-          const int q = q0 + c_base + c;
-          const bool valid = (mS[c_base + c] <= kvi) && (kvi <= q) && (p.window == 0 || q - kvi < p.window);
-          pv = valid ? pv : 0.f;
-        }
-        sv[c] = __float_as_uint(pv);
-      }
+      meta(it)[r] = pre;                                 // [0, 64): L, [64, 128): delta
     };
 
-    auto drain_dq = [&](int j, int meta_it) {
-      uint32_t dq[32];
-      if (j >= 0) {
-        mbar_wait(dq_full, j & 1);
-        tc_fence_after();
-        tmem_ld_32x32b_x32(t_lane + C::kColDQT + c_base, dq);
-        tmem_ld_wait();
-        tc_fence_before();
-        mbar_arrive(dq_empty);
-        if (threadIdx.x == 0) tma_store_wait_read<0>();   // previous reduce has finished reading the staging tile
-      }
-      asm volatile("bar.sync 2, 256;" ::: "memory");
-      if (j >= 0) {
-        float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
-#pragma unroll
-        for (int c = 0; c < 32; ++c) stage[(c_base + c) * kBwdD + r] = __uint_as_float(dq[c]);
-      }
-      if (meta_it < n_total) meta_store(meta_it);
-      fence_proxy_async_smem();
-      asm volatile("bar.sync 2, 256;" ::: "memory");
-      if (j >= 0 && threadIdx.x == 0) {
-        const int hj = g * G + j / nq;
-        const int qj = (i_lo + j % nq) * kBwdQ;
-        tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, hj * p.head_dim, qj);
-        tma_store_commit();
-      }
-    };
+    uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
 
     meta_fetch(0);
     meta_store(0);
     if (n_total > 1) { meta_fetch(1); meta_store(1); }
     asm volatile("bar.sync 1, 256;" ::: "memory");
-    compute_p(0);
 
-    for (int it = 0; it < n_total; ++it) {
-      const float* mD = meta(it) + 64;
-      if (it + 2 < n_total) meta_fetch(it + 2);
+    // One loop instance of every phase (the body is ~1.5k instructions; peeled copies pushed the first version
+    // past the instruction cache): iteration `it` finishes step it, drains dQ^T(it-1) and starts P^T(it+1).
+#pragma unroll 1
+    for (int it = -1; it <= n_total; ++it) {
+      if (it >= 0 && it + 2 < n_total) meta_fetch(it + 2);   // global loads in flight during this whole step
 
-      // ---- P^T(it): registers -> tensor memory (bf16 pairs, column c/2 holds q columns c, c+1)
-      mbar_wait(pds_empty, (it & 1) ^ 1);                 // dV / dK / dQ MMAs of the previous step are done
-      {
-        uint32_t pk[16];
+      if (it >= 0 && it < n_total) {
+        const float* mD = meta(it) + 64 + c_base;
+        // ---- P^T(it): registers -> tensor memory (bf16 pairs: column c/2 holds q columns c, c+1)
+        mbar_wait(pds_empty, (it & 1) ^ 1);               // dV / dK / dQ MMAs of the previous step are done
+        {
+          uint32_t pk[16];
 #pragma unroll
-        for (int c = 0; c < 16; ++c) pk[c] = pack_bf16x2(__uint_as_float(sv[2 * c]), __uint_as_float(sv[2 * c + 1]));
-        tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
+          for (int c = 0; c < 16; ++c)
+            pk[c] = pack_bf16x2(__uint_as_float(sv[2 * c]), __uint_as_float(sv[2 * c + 1]));
+          tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
+        }
+        // ---- dS^T(it) = P^T o (dP^T - delta)  (the softmax scale is applied to dK / dQ at the end)
+        {
+          uint32_t dp[32];
+          mbar_wait(dp_full, it & 1);
+          tc_fence_after();
+          tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(dp_empty);
+          uint32_t pk[16];
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 d4 = *reinterpret_cast<const float4*>(mD + ch * 4);
+            const int c = ch * 4;
+            pk[ch * 2] = pack_bf16x2(__uint_as_float(sv[c]) * (__uint_as_float(dp[c]) - d4.x),
+                                     __uint_as_float(sv[c + 1]) * (__uint_as_float(dp[c + 1]) - d4.y));
+            pk[ch * 2 + 1] = pack_bf16x2(__uint_as_float(sv[c + 2]) * (__uint_as_float(dp[c + 2]) - d4.z),
+                                         __uint_as_float(sv[c + 3]) * (__uint_as_float(dp[c + 3]) - d4.w));
+          }
+          tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch)
+            *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
+                make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+        }
+        tmem_st_wait();
+        fence_proxy_async_smem();
+        tc_fence_before();
+        mbar_arrive(pds_full);
       }
-      // ---- dS^T(it) = P^T o (dP^T - delta) * scale -> tensor memory (dK) and smem (B operand of dQ^T)
-      {
-        uint32_t dp[32];
-        mbar_wait(dp_full, it & 1);
+
+      // ---- dQ^T(j = it-1): TMEM [lane = d][col = q] -> smem [q][d] fp32 (two staging tiles) -> one TMA reduce-add
+      //      into dq_acc, under the MMAs of step it.  The single CTA barrier also publishes metadata(it+2).
+      if (it >= 0) {
+        const int j = it - 1;
+        if (j >= 0) {
+          uint32_t dq[32];
+          mbar_wait(dq_full, j & 1);
+          tc_fence_after();
+          tmem_ld_32x32b_x32(t_lane + C::kColDQT + c_base, dq);
+          tmem_ld_wait();
+          tc_fence_before();
+          mbar_arrive(dq_empty);
+          float* stage = reinterpret_cast<float*>(smem + C::kDQOff + (j & 1) * C::kDQBytes);
+#pragma unroll
+          for (int c = 0; c < 32; ++c) stage[(c_base + c) * kBwdD + r] = __uint_as_float(dq[c]);
+        }
+        if (it + 2 < n_total) meta_store(it + 2);           // ring slot (it+2) % 3 was last read two steps ago
+        fence_proxy_async_smem();
+        // the tile the NEXT drain writes was read by the reduce issued one drain ago: make sure that read is over
+        if (threadIdx.x == 0) tma_store_wait_read<0>();
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (j >= 0 && threadIdx.x == 0) {
+          const int hj = g * G + j / nq;
+          const int qj = (i_lo + j % nq) * kBwdQ;
+          tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff + (j & 1) * C::kDQBytes, hj * p.head_dim, qj);
+          tma_store_commit();
+        }
+      }
+
+      // ---- while the tensor cores run dP^T(it+1) and dV / dK / dQ^T(it): P^T(it+1) = exp2(S^T c - L) masked
+      if (it + 1 < n_total) {
+        const int nx = it + 1;
+        const int q0 = (i_lo + nx % nq) * kBwdQ;
+        const float* mL = meta(nx) + c_base;
+        const bool need_mask = tail_tile || (q0 < k0 + kBwdKV - 1) || (q0 + kBwdQ > q_end_first);
+        mbar_wait(s_full, nx & 1);
         tc_fence_after();
-        tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
+        tmem_ld_32x32b_x32(t_lane + C::kColST + c_base, sv);
         tmem_ld_wait();
         tc_fence_before();
-        mbar_arrive(dp_empty);
-        uint32_t pk[16];
+        mbar_arrive(s_empty);                              // S^T(it+2) may overwrite the columns now
+        if (need_mask) {
+          const uint32_t off0 = (uint32_t)(q0 + c_base - kvi);
 #pragma unroll
-        for (int c = 0; c < 16; ++c) {
-          const float a = __uint_as_float(sv[2 * c]) * (__uint_as_float(dp[2 * c]) - mD[c_base + 2 * c]) * p.scale;
-          const float b = __uint_as_float(sv[2 * c + 1]) * (__uint_as_float(dp[2 * c + 1]) - mD[c_base + 2 * c + 1]) * p.scale;
-          pk[c] = pack_bf16x2(a, b);
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              const float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
+              sv[c] = (off0 + (uint32_t)c < valid_len) ? __float_as_uint(pv) : 0u;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              sv[c] = __float_as_uint(bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e])));
+            }
+          }
         }
-        tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
-#pragma unroll
-        for (int ch = 0; ch < 4; ++ch)
-          *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
-              make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
       }
-      tmem_st_wait();
-      fence_proxy_async_smem();
-      tc_fence_before();
-      mbar_arrive(pds_full);
-
-      // ---- dQ^T(it-1): TMEM -> smem [q][d] fp32 -> TMA reduce-add, under the MMAs of this step
-      drain_dq(it - 1, it + 2);
-
-      // ---- while the tensor cores run dP^T(it+1) and dV/dK/dQ^T(it), build P^T(it+1)
-      if (it + 1 < n_total) compute_p(it + 1);
     }
-    drain_dq(n_total - 1, n_total + 2);
     if (threadIdx.x == 0) tma_store_wait<0>();
 
-    // ---- dK / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
+    // ---- dK (x softmax scale) / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
     mbar_wait(acc_done, 0);
     tc_fence_after();
     {
       const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
       uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
       const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
-#pragma unroll
+      const float mul = which == 0 ? p.scale : 1.f;
+#pragma unroll 1
       for (int c0 = 0; c0 < kBwdD; c0 += 32) {
         uint32_t o[32];
         tmem_ld_32x32b_x32(t_lane + col + c0, o);
@@ -804,7 +844,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         for (int ch = 0; ch < 4; ++ch) {
           float f[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(o[ch * 8 + e]);
+          for (int e = 0; e < 8; ++e) f[e] = __uint_as_float(o[ch * 8 + e]) * mul;
           const int chunk = ((c0 % 64) / 8) + ch;
           *reinterpret_cast<bf16x8*>(box_row + ((chunk ^ (r & 7)) << 4)) = pack8(f);
         }
@@ -888,7 +928,8 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   int64_t blocks = ((int64_t)tokens * width / 8 + 255) / 256;
   const int64_t cap = (int64_t)num_sms() * 8;
   if (blocks > cap) blocks = cap;
+  // the TS kernel accumulates unscaled dS^T K; the softmax scale is folded into this pass
   attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, (__nv_bfloat16*)dqkv, tokens, width,
-                                                               qkv_stride);
+                                                               qkv_stride, use_ss ? 1.f : scale);
   return check_launch("attn_dq_convert");
 }

@@ -15,6 +15,22 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 }
 __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 
+// One lane of a converged warp (elect.sync).  Single-thread instructions (tcgen05.mma / commit, TMA) belong inside
+// `if (elect_one())` in WARP-UNIFORM control flow: after a divergent `if (lane == 0)` ptxas cannot keep the operands
+// in uniform registers and wraps every such instruction in an election loop with vector->uniform register moves
+// (~15 extra instructions per MMA — more than a 128x64x16 MMA takes to execute).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+// warp index that the compiler can treat as warp-uniform
+__device__ __forceinline__ int warp_idx_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 // ---------------------------------------------------------------- cluster ------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
