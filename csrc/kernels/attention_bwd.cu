@@ -77,17 +77,20 @@ struct BwdTsCfg {
   static constexpr int kDSBytes = kBwdKV * kBwdQ * 2;       // 16 KB : 1 box  [128][64]
   static constexpr int kKOff = 0;
   static constexpr int kVOff = kKOff + kKBytes;
-  static constexpr int kQOff = kVOff + kKBytes;             // 2 stages
-  static constexpr int kDOOff = kQOff + 2 * kQBytes;        // 2 stages
-  static constexpr int kDSOff = kDOOff + 2 * kQBytes;
-  static constexpr int kDQOff = kDSOff + kDSBytes;          // 2 x fp32 [64 q][128 d] staging for the TMA reduce-add
-  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB each
-  static constexpr int kMetaOff = kDQOff + 2 * kDQBytes;    // 3 x {L[64], delta[64]}
+  // Q / dO ring: THREE stages.  With two, the load of step it+1 could only start when the MMAs of step it-1 had
+  // released their stage, and its ~1 us flight sat in front of S^T(it+1) every step (35% of the issuer's samples).
+  static constexpr int kStages = 3;
+  static constexpr int kQOff = kVOff + kKBytes;
+  static constexpr int kDOOff = kQOff + kStages * kQBytes;
+  static constexpr int kDSOff = kDOOff + kStages * kQBytes;
+  static constexpr int kDQOff = kDSOff + kDSBytes;          // fp32 [64 q][128 d] staging for the TMA reduce-add
+  static constexpr int kDQBytes = kBwdQ * kBwdD * 4;        // 32 KB
+  static constexpr int kMetaOff = kDQOff + kDQBytes;        // 3 x {L[64], delta[64]}
   static constexpr int kMetaBytes = 3 * 2 * 64 * 4;
   static constexpr int kBarOff = kMetaOff + kMetaBytes;
-  // kv_full, qdo_full[2], qdo_empty[2], s_full, s_empty, dp_full, dp_empty, pds_full, pds_empty, dq_full, dq_empty,
+  // kv_full, qdo_full[3], qdo_empty[3], s_full, s_empty, dp_full, dp_empty, pds_full, pds_empty, dq_full, dq_empty,
   // acc_done
-  static constexpr int kNumBars = 14;
+  static constexpr int kNumBars = 16;
   static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
   static constexpr int kColDK = 0, kColDV = 128, kColST = 256, kColDPT = 320, kColDQT = 384, kColP = 448, kColDS = 480;
 };
@@ -505,14 +508,14 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   const uint32_t bars = sbase + C::kBarOff;
   const uint32_t kv_full = bars;
   auto qdo_full = [&](int s) { return bars + 8u * (1 + s); };
-  auto qdo_empty = [&](int s) { return bars + 8u * (3 + s); };
-  const uint32_t s_full = bars + 8u * 5, s_empty = bars + 8u * 6;
-  const uint32_t dp_full = bars + 8u * 7, dp_empty = bars + 8u * 8;
-  const uint32_t pds_full = bars + 8u * 9, pds_empty = bars + 8u * 10;
-  const uint32_t dq_full = bars + 8u * 11, dq_empty = bars + 8u * 12;
-  const uint32_t acc_done = bars + 8u * 13;
-  const uint32_t tmem_ptr_smem = bars + 8u * 14;
-  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 14);
+  auto qdo_empty = [&](int s) { return bars + 8u * (4 + s); };
+  const uint32_t s_full = bars + 8u * 7, s_empty = bars + 8u * 8;
+  const uint32_t dp_full = bars + 8u * 9, dp_empty = bars + 8u * 10;
+  const uint32_t pds_full = bars + 8u * 11, pds_empty = bars + 8u * 12;
+  const uint32_t dq_full = bars + 8u * 13, dq_empty = bars + 8u * 14;
+  const uint32_t acc_done = bars + 8u * 15;
+  const uint32_t tmem_ptr_smem = bars + 8u * 16;
+  volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 16);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   const int g = blockIdx.x;                       // kv head (fast axis: longest jobs of every head start first)
@@ -528,7 +531,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 
   if (warp == kBwdMmaWarp && lane == 0) {
     mbar_init(kv_full, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < C::kStages; ++s) {
       mbar_init(qdo_full(s), 1);
       mbar_init(qdo_empty(s), 1);
     }
@@ -560,19 +563,23 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   const uint32_t tmem_base = *tmem_ptr_gen;
 
   if (warp == kBwdTmaWarp) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer (whole warp in uniform control flow, one elected lane issues) =====
+    if (elect_one()) {
       mbar_arrive_expect_tx(kv_full, 2 * C::kKBytes);
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
         tma_load_3d(sbase + C::kKOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + g, k0);
         tma_load_3d(sbase + C::kVOff + b * (kBwdKV * 128), &tmKV, kv_full, b * 64, p.hq + p.hkv + g, k0);
       }
-      for (int it = 0; it < n_total; ++it) {
-        const int st = it & 1;
-        const int h = g * G + it / nq;
-        const int q0 = (i_lo + it % nq) * kBwdQ;
-        mbar_wait(qdo_empty(st), ((it >> 1) & 1) ^ 1);
+    }
+    __syncwarp();
+    int st = 0, h = g * G, qi = 0;
+    uint32_t ph = 0;
+#pragma unroll 1
+    for (int it = 0; it < n_total; ++it) {
+      const int q0 = (i_lo + qi) * kBwdQ;
+      mbar_wait(qdo_empty(st), ph ^ 1);
+      if (elect_one()) {
         mbar_arrive_expect_tx(qdo_full(st), 2 * C::kQBytes);
 #pragma unroll
         for (int b = 0; b < 2; ++b) {
@@ -580,6 +587,9 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
           tma_load_3d(sbase + C::kDOOff + st * C::kQBytes + b * (kBwdQ * 128), &tmDO, qdo_full(st), b * 64, h, q0);
         }
       }
+      __syncwarp();
+      if (++st == C::kStages) { st = 0; ph ^= 1; }
+      if (++qi == nq) { qi = 0; ++h; }
     }
   } else if (warp == kBwdMmaWarp) {
     // ===== MMA issuer: the WHOLE warp walks the loop (uniform control flow, waits included); one elected lane
@@ -599,15 +609,15 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     constexpr uint64_t kStage = C::kQBytes >> 4;                                  // descriptor units per Q / dO stage
     // k-step offsets in descriptor units (16 bytes): K-major tiles hold 4 k-steps per 64-column box
     auto kmaj = [](int kk, int rows) -> uint64_t { return (uint64_t)((kk / 4) * (rows * 8) + (kk % 4) * 2); };
-    auto issue_s = [&](int it) {
-      const uint64_t q_b = q_b0 + (uint64_t)(it & 1) * kStage;
+    auto issue_s = [&](int st) {
+      const uint64_t q_b = q_b0 + (uint64_t)st * kStage;
 #pragma unroll
       for (int kk = 0; kk < kBwdD / 16; ++kk)
         umma_f16<1>(tb + C::kColST, k_a + kmaj(kk, kBwdKV), q_b + kmaj(kk, kBwdQ), idesc_st, kk != 0);
       umma_commit(s_full);
     };
-    auto issue_dp = [&](int it) {
-      const uint64_t do_b = do_b0 + (uint64_t)(it & 1) * kStage;
+    auto issue_dp = [&](int st) {
+      const uint64_t do_b = do_b0 + (uint64_t)st * kStage;
 #pragma unroll
       for (int kk = 0; kk < kBwdD / 16; ++kk)
         umma_f16<1>(tb + C::kColDPT, v_a + kmaj(kk, kBwdKV), do_b + kmaj(kk, kBwdQ), idesc_st, kk != 0);
@@ -621,22 +631,24 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       issue_dp(0);
     }
     __syncwarp();
+    int st = 0, st_next = 1 % C::kStages;                 // ring slots of step it / it+1
+    uint32_t ph_next = (C::kStages == 1) ? 1u : 0u;       // parity of qdo_full(st_next) for step it+1
 #pragma unroll 1
     for (int it = 0; it < n_total; ++it) {
       if (it + 1 < n_total) {
-        mbar_wait(qdo_full((it + 1) & 1), ((it + 1) >> 1) & 1);
+        mbar_wait(qdo_full(st_next), ph_next);
         mbar_wait(s_empty, it & 1);             // S^T(it) is in the threads' registers
         tc_fence_after();
-        if (elect_one()) issue_s(it + 1);
+        if (elect_one()) issue_s(st_next);
         __syncwarp();
         mbar_wait(dp_empty, it & 1);            // dP^T(it) is in the threads' registers
         tc_fence_after();
-        if (elect_one()) issue_dp(it + 1);
+        if (elect_one()) issue_dp(st_next);
         __syncwarp();
       }
       mbar_wait(pds_full, it & 1);              // P^T / dS^T (it) are in tensor memory, dS^T also in smem
       tc_fence_after();
-      const uint64_t q_mn = q_mn0 + (uint64_t)(it & 1) * kStage, do_mn = do_mn0 + (uint64_t)(it & 1) * kStage;
+      const uint64_t q_mn = q_mn0 + (uint64_t)st * kStage, do_mn = do_mn0 + (uint64_t)st * kStage;
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < kBwdQ / 16; ++kk)   // dV += P^T dO     (A = P^T from TMEM, 8 columns per k-step)
@@ -646,6 +658,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         for (int kk = 0; kk < kBwdQ / 16; ++kk)   // dK += dS^T Q    (A = dS^T from TMEM; scaled at the end)
           umma_f16_ts<1>(tb + C::kColDK, tb + C::kColDS + kk * 8, q_mn + (uint64_t)kk * 128, idesc_dkv,
                          (it | kk) != 0);
+        umma_commit(qdo_empty(st));               // Q / dO of this step are not read again: release the ring slot
       }
       __syncwarp();
       mbar_wait(dq_empty, (it & 1) ^ 1);          // dQ^T(it-1) has left its TMEM buffer
@@ -654,11 +667,12 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 #pragma unroll
         for (int kk = 0; kk < kBwdKV / 16; ++kk)  // dQ^T = K^T dS^T
           umma_f16<1>(tb + C::kColDQT, kt_a + (uint64_t)kk * 128, ds_b + (uint64_t)kk * 128, idesc_dq, kk != 0);
-        umma_commit(qdo_empty(it & 1));
         umma_commit(pds_empty);
         umma_commit(dq_full);
       }
       __syncwarp();
+      st = st_next;
+      if (++st_next == C::kStages) { st_next = 0; ph_next ^= 1; }
     }
     if (elect_one()) umma_commit(acc_done);
     __syncwarp();
@@ -688,13 +702,17 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     // while step it is processed and published by the CTA barrier of the dQ drain.
     auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 128; };
     float pre = 0.f;
-    auto meta_fetch = [&](int it) {
-      if (hf != 0) return;                               // warps 0-3 fetch for everybody
-      const int h = g * G + it / nq;
-      const int q = (i_lo + it % nq) * kBwdQ + (r & 63);
-      const bool ok = q < p.tokens;
-      if (r < 64) pre = ok ? p.lse[(size_t)h * p.tokens + q] : INFINITY;
-      else        pre = ok ? p.delta[(size_t)h * p.tokens + q] : 0.f;
+    // (head, q block) of steps it+2 [metadata fetch], it+1 [P^T] and it-1 [dQ^T drain], advanced once per iteration
+    int f_h = g * G, f_qi = 0, n_qi = 0, d_h = g * G, d_qi = 0;
+    auto advance = [&](int& h, int& qi) { if (++qi == nq) { qi = 0; ++h; } };
+    auto meta_fetch = [&]() {                            // fetches step (f_h, f_qi), then advances the cursor
+      if (hf == 0) {                                     // warps 0-3 fetch for everybody
+        const int q = (i_lo + f_qi) * kBwdQ + (r & 63);
+        const bool ok = q < p.tokens;
+        if (r < 64) pre = ok ? p.lse[(size_t)f_h * p.tokens + q] : INFINITY;
+        else        pre = ok ? p.delta[(size_t)f_h * p.tokens + q] : 0.f;
+      }
+      advance(f_h, f_qi);
     };
     auto meta_store = [&](int it) {
       if (hf != 0) return;
@@ -703,16 +721,16 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 
     uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
 
-    meta_fetch(0);
+    meta_fetch();
     meta_store(0);
-    if (n_total > 1) { meta_fetch(1); meta_store(1); }
+    if (n_total > 1) { meta_fetch(); meta_store(1); }
     asm volatile("bar.sync 1, 256;" ::: "memory");
 
     // One loop instance of every phase (the body is ~1.5k instructions; peeled copies pushed the first version
     // past the instruction cache): iteration `it` finishes step it, drains dQ^T(it-1) and starts P^T(it+1).
 #pragma unroll 1
     for (int it = -1; it <= n_total; ++it) {
-      if (it >= 0 && it + 2 < n_total) meta_fetch(it + 2);   // global loads in flight during this whole step
+      if (it >= 0 && it + 2 < n_total) meta_fetch();         // step it+2: global loads in flight during this whole step
 
       if (it >= 0 && it < n_total) {
         const float* mD = meta(it) + 64 + c_base;
@@ -756,39 +774,43 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         mbar_arrive(pds_full);
       }
 
-      // ---- dQ^T(j = it-1): TMEM [lane = d][col = q] -> smem [q][d] fp32 (two staging tiles) -> one TMA reduce-add
-      //      into dq_acc, under the MMAs of step it.  The single CTA barrier also publishes metadata(it+2).
+      // ---- dQ^T(j = it-1): TMEM [lane = d][col = q] -> smem [q][d] fp32 -> one TMA reduce-add into dq_acc, under
+      //      the MMAs of step it.  The CTA barriers also publish metadata(it+2).
       if (it >= 0) {
         const int j = it - 1;
+        uint32_t dq[32];
         if (j >= 0) {
-          uint32_t dq[32];
           mbar_wait(dq_full, j & 1);
           tc_fence_after();
           tmem_ld_32x32b_x32(t_lane + C::kColDQT + c_base, dq);
           tmem_ld_wait();
           tc_fence_before();
           mbar_arrive(dq_empty);
-          float* stage = reinterpret_cast<float*>(smem + C::kDQOff + (j & 1) * C::kDQBytes);
+          if (threadIdx.x == 0) tma_store_wait_read<0>();   // previous reduce has finished reading the staging tile
+        }
+        asm volatile("bar.sync 2, 256;" ::: "memory");
+        if (j >= 0) {
+          float* stage = reinterpret_cast<float*>(smem + C::kDQOff);
 #pragma unroll
           for (int c = 0; c < 32; ++c) stage[(c_base + c) * kBwdD + r] = __uint_as_float(dq[c]);
         }
         if (it + 2 < n_total) meta_store(it + 2);           // ring slot (it+2) % 3 was last read two steps ago
         fence_proxy_async_smem();
-        // the tile the NEXT drain writes was read by the reduce issued one drain ago: make sure that read is over
-        if (threadIdx.x == 0) tma_store_wait_read<0>();
         asm volatile("bar.sync 2, 256;" ::: "memory");
-        if (j >= 0 && threadIdx.x == 0) {
-          const int hj = g * G + j / nq;
-          const int qj = (i_lo + j % nq) * kBwdQ;
-          tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff + (j & 1) * C::kDQBytes, hj * p.head_dim, qj);
-          tma_store_commit();
+        if (j >= 0) {
+          if (threadIdx.x == 0) {
+            tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, d_h * p.head_dim, (i_lo + d_qi) * kBwdQ);
+            tma_store_commit();
+          }
+          advance(d_h, d_qi);
         }
       }
 
       // ---- while the tensor cores run dP^T(it+1) and dV / dK / dQ^T(it): P^T(it+1) = exp2(S^T c - L) masked
       if (it + 1 < n_total) {
         const int nx = it + 1;
-        const int q0 = (i_lo + nx % nq) * kBwdQ;
+        const int q0 = (i_lo + n_qi) * kBwdQ;
+        if (++n_qi == nq) n_qi = 0;
         const float* mL = meta(nx) + c_base;
         const bool need_mask = tail_tile || (q0 < k0 + kBwdKV - 1) || (q0 + kBwdQ > q_end_first);
         mbar_wait(s_full, nx & 1);

@@ -86,7 +86,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
   const uint32_t tmem_ptr_smem = bars + 8u * 15;
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 15);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   // heavy (late) query tiles first: they have the most KV blocks
   const int num_q_tiles = (p.tokens + kBlockQ - 1) / kBlockQ;
   const int qt = num_q_tiles - 1 - (int)blockIdx.x;
@@ -161,50 +161,58 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
       }
     }
   } else if (warp == 4) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
-      constexpr uint32_t idesc_s = make_idesc_bf16(kBlockQ, kBlockKV, false, false);
-      constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockQ, DPAD, false, true);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        const uint32_t qa = sbase + C::kQOff, ka = sbase + C::kKOff + st * C::kKVBytes;
+    // ===== MMA issuer: the whole warp walks the loop in uniform control flow, one elected lane issues; smem
+    // descriptors are built once and a k-step only adds a constant to the start-address field (a divergent
+    // `if (lane == 0)` made ptxas wrap every tcgen05.mma in an election loop with vector->uniform moves).
+    constexpr uint32_t idesc_s = make_idesc_bf16(kBlockQ, kBlockKV, false, false);
+    constexpr uint32_t idesc_pv = make_idesc_bf16(kBlockQ, DPAD, false, true);
+    const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint64_t q_a = make_smem_desc(sbase + C::kQOff, 0, 1024);                    // Q as A, K-major
+    const uint64_t k_b0 = make_smem_desc(sbase + C::kKOff, 0, 1024);                   // K as B, K-major, stage 0
+    const uint64_t p_a = make_smem_desc(sbase + C::kPOff, 0, 1024);                    // P as A, K-major
+    const uint64_t v_b0 = make_smem_desc(sbase + C::kVOff, kBlockKV * 128, 1024);      // V as B, MN-major, stage 0
+    constexpr uint64_t kStage = C::kKVBytes >> 4;
+    auto kmaj = [](int kk, int rows) -> uint64_t { return (uint64_t)((kk / 4) * (rows * 8) + (kk % 4) * 2); };
+    auto issue_s = [&](int j) {
+      const int st = j & 1;
+      const uint64_t k_b = k_b0 + (uint64_t)st * kStage;
 #pragma unroll
-        for (int kk = 0; kk < DPAD / 16; ++kk) {
-          const uint64_t ad = make_smem_desc(qa + (kk / 4) * (kBlockQ * 128) + (kk % 4) * 32, 0, 1024);
-          const uint64_t bd = make_smem_desc(ka + (kk / 4) * (kBlockKV * 128) + (kk % 4) * 32, 0, 1024);
-          umma_f16<1>(tmem_base + (uint32_t)(st * kBlockKV), ad, bd, idesc_s, kk != 0);
-        }
-        umma_commit(k_empty(st));
-        umma_commit(s_full(st));
-      };
-      mbar_wait(q_full, 0);
-      mbar_wait(k_full(0), 0);
-      tc_fence_after();
-      issue_s(0);
-      for (int j = 0; j < nb; ++j) {
-        if (j + 1 < nb) {
-          const int st = (j + 1) & 1;
-          const uint32_t par = ((j + 1) >> 1) & 1;
-          mbar_wait(k_full(st), par);
-          mbar_wait(s_empty(st), par ^ 1);
-          tc_fence_after();
-          issue_s(j + 1);
-        }
-        const int st = j & 1;
-        mbar_wait(v_full(st), (j >> 1) & 1);
-        mbar_wait(p_full, j & 1);
+      for (int kk = 0; kk < DPAD / 16; ++kk)
+        umma_f16<1>(tb + (uint32_t)(st * kBlockKV), q_a + kmaj(kk, kBlockQ), k_b + kmaj(kk, kBlockKV), idesc_s,
+                    kk != 0);
+      umma_commit(k_empty(st));
+      umma_commit(s_full(st));
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(k_full(0), 0);
+    tc_fence_after();
+    if (elect_one()) issue_s(0);
+    __syncwarp();
+#pragma unroll 1
+    for (int j = 0; j < nb; ++j) {
+      if (j + 1 < nb) {
+        const int st = (j + 1) & 1;
+        const uint32_t par = ((j + 1) >> 1) & 1;
+        mbar_wait(k_full(st), par);
+        mbar_wait(s_empty(st), par ^ 1);
         tc_fence_after();
-        const uint32_t pa = sbase + C::kPOff, va = sbase + C::kVOff + st * C::kKVBytes;
+        if (elect_one()) issue_s(j + 1);
+        __syncwarp();
+      }
+      const int st = j & 1;
+      mbar_wait(v_full(st), (j >> 1) & 1);
+      mbar_wait(p_full, j & 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint64_t v_b = v_b0 + (uint64_t)st * kStage;
 #pragma unroll
-        for (int kk = 0; kk < kBlockKV / 16; ++kk) {
-          const uint64_t ad = make_smem_desc(pa + kk * 32, 0, 1024);
-          // V: MN-major B, [kv rows][64 d] boxes; next 64-wide d group = next box (LBO), 8 kv rows = 1024 B (SBO)
-          const uint64_t bd = make_smem_desc(va + kk * (16 * 128), kBlockKV * 128, 1024);
-          umma_f16<1>(tmem_base + C::kOCol, ad, bd, idesc_pv, (j | kk) != 0);
-        }
+        for (int kk = 0; kk < kBlockKV / 16; ++kk)
+          // P: 2 descriptor units per k-step; V: MN-major B, [kv rows][64 d] boxes, 16 kv rows per k-step
+          umma_f16<1>(tb + C::kOCol, p_a + (uint64_t)kk * 2, v_b + (uint64_t)kk * 128, idesc_pv, (j | kk) != 0);
         umma_commit(v_empty(st));
         umma_commit(o_done);
       }
+      __syncwarp();
     }
   } else {
     // ===== softmax warps: thread <-> query row =====
