@@ -165,7 +165,8 @@ def test_adamw_single_step_against_float64():
         tol = 2.0 ** -22 * p64.abs() + 2e-6 * delta.abs() + 1e-12
         worst = ((master.double() - p64).abs() / tol).max().item()
         assert worst <= 1.0, f'step {step}: master differs from the float64 result by {worst:.2f}x the fp32 bound'
-        assert ((m.double() - m64).abs() <= 2.0 ** -22 * (m64.abs() + 1e-6)).all()
-        assert ((v.double() - v64).abs() <= 2.0 ** -22 * (v64.abs() + 1e-9)).all()
+        # moments: (1 - beta) is itself rounded to fp32, then two products and a sum -> 4 roundings of 2^-24 each
+        assert ((m.double() - m64).abs() <= 2.0 ** -21 * (m64.abs() + (1 - b1) * g64.abs()) + 1e-12).all()
+        assert ((v.double() - v64).abs() <= 2.0 ** -21 * v64.abs() + 1e-16).all()
         flips = (param.float() != p64.float().bfloat16().float()).float().mean().item()
         assert flips < 1e-3, f'step {step}: {flips:.2e} of the bf16 copies differ from round(float64 result)'
