@@ -30,6 +30,11 @@ def main() -> None:
     ap.add_argument('--seq-len', type=int, default=4096)
     ap.add_argument('--pairs', type=int, default=2, help='preference pairs per GPU per step')
     ap.add_argument('--layers', type=int, default=0)
+    ap.add_argument('--loss', default='fused', choices=['fused', 'materialized'],
+                    help="'materialized' computes the sequence log-probs the reference's way (full [B, T, V] logits -> "
+                         'fp32 log_softmax -> gather; /root/reference/src/llm_training/lms/dpo/dpo.py:110-114, '
+                         'lms/orpo/orpo.py:89-93) on the same model and kernels, so the fused linear + log-prob loss '
+                         'has a like-for-like ratio')
     args = ap.parse_args()
     world = int(os.environ.get('WORLD_SIZE', 1))
     rank = int(os.environ.get('RANK', 0))
@@ -53,6 +58,10 @@ def main() -> None:
     if args.objective == 'dpo' and getattr(lm, 'ref_model', None) is not None:
         # the reference model starts as a copy of the policy (both load the same pre-trained weights in real use)
         lm.ref_model.load_state_dict(lm.model.state_dict())
+    if args.loss == 'materialized':
+        for m in (lm.model, getattr(lm, 'ref_model', None)):
+            if m is not None:
+                m.supports_fused_loss = False       # sequence_logps then takes its logits -> log_softmax branch
     trainer.strategy.setup(trainer)
     dev = trainer.strategy.root_device
     g = torch.Generator().manual_seed(7 + rank)
@@ -97,7 +106,7 @@ def main() -> None:
                           'dtype': 'bf16', 'data': 'synthetic',
                           'config': {'model': 'phi-3-mini' + (f'-{args.layers}layers' if args.layers else ''),
                                      'pairs_per_gpu': args.pairs, 'seq_len': args.seq_len,
-                                     'parallelism': f'dp{world}', 'objective': args.objective},
+                                     'parallelism': f'dp{world}', 'objective': args.objective, 'loss': args.loss},
                           'peak_mem_gib': round(torch.cuda.max_memory_allocated() / 2**30, 1),
                           'last_loss': float(loss)}))
     if dist.is_initialized():
