@@ -126,6 +126,11 @@ def main() -> None:
     ap.add_argument('--tp', type=int, default=1)
     ap.add_argument('--reshard', action='store_true',
                     help='ZeRO-3 / FSDP reshard_after_forward=True (the reference default) instead of resident parameters')
+    ap.add_argument('--docs', type=int, default=1,
+                    help='documents per packed sequence (> 1: instruction-tuning shaped batches, BASELINE config 3: '
+                         'segment-id attention masks that block cross-document attention, position ids restart per '
+                         'document, prompt tokens carry no loss)')
+    ap.add_argument('--neftune', type=float, default=0.0, help='NEFTune alpha (config 3 uses 5)')
     ap.add_argument('--phases', action='store_true', help='also report forward / backward / optimizer device time')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
@@ -165,7 +170,7 @@ def main() -> None:
                      recompute_granularity='selective' if recompute == 'selective' else 'full',
                      attn_implementation='flash_attention_2' if cuda else 'sdpa')
     lm = CLM(CLMConfig.model_validate(dict(
-        init_weights=True, load_weights=False,
+        init_weights=True, load_weights=False, neftune_alpha=args.neftune if args.neftune > 0 else None,
         model=dict(model_class='llm_training.models.Llama', model_config=model_cfg),
         optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=1e-5, weight_decay=0.1),
                    lr_scheduler_class='llm_training.lr_schedulers.CosineAnnealingWarmupLR',
@@ -176,6 +181,28 @@ def main() -> None:
                                                max_length=args.seq_len,
                                                num_samples=(total_steps + 2) * args.micro_batch * dp, base_seed=11,
                                                pin_memory=True, num_workers=0))
+
+    def pack_documents(sample: dict, seed: int) -> dict:
+        """Turn one dummy sample into an instruction-tuning shaped pack: `--docs` documents of uneven length
+        (segment ids 1..N in `attention_mask`, like InstructionTuningDataCollator with GROUP_BY_LENGTH packing),
+        position ids restarting per document, the first third of every document masked out of the loss."""
+        g = torch.Generator().manual_seed(seed)
+        n = args.seq_len
+        cuts = sorted(torch.randperm(n - 1, generator=g)[:args.docs - 1].add(1).tolist())
+        bounds = [0] + cuts + [n]
+        seg = torch.empty(n, dtype=torch.long)
+        pos = torch.empty(n, dtype=torch.long)
+        labels = sample['input_ids'].clone()
+        for d, (a, b) in enumerate(zip(bounds[:-1], bounds[1:])):
+            seg[a:b] = d + 1
+            pos[a:b] = torch.arange(b - a)
+            labels[a:a + (b - a) // 3] = -100
+        return dict(input_ids=sample['input_ids'], attention_mask=seg, position_ids=pos, labels=labels)
+
+    if args.docs > 1:
+        from llm_training_b200.data.dummy.dummy_dataset import DummyDataset
+        plain_getitem = DummyDataset.__getitem__
+        DummyDataset.__getitem__ = lambda self, i: pack_documents(plain_getitem(self, i), 7000 + i)
 
     tokens_per_step = args.micro_batch * args.seq_len * dp
 
@@ -241,8 +268,13 @@ def main() -> None:
     lm.train()
     g = torch.Generator().manual_seed(99 + rank)
     ids = torch.randint(0, model_cfg['vocab_size'], (args.micro_batch, args.seq_len), generator=g)
-    batch = {'input_ids': ids.to(device), 'attention_mask': torch.ones_like(ids).to(device),
-             'position_ids': torch.arange(args.seq_len).unsqueeze(0).to(device), 'labels': ids.to(device)}
+    batch = {'input_ids': ids, 'attention_mask': torch.ones_like(ids),
+             'position_ids': torch.arange(args.seq_len).unsqueeze(0).expand(args.micro_batch, -1).contiguous(),
+             'labels': ids}
+    if args.docs > 1:
+        rows = [pack_documents({'input_ids': ids[r]}, 9000 + r) for r in range(args.micro_batch)]
+        batch = {k: torch.stack([row[k] for row in rows]) for k in rows[0]}
+    batch = {k: v.to(device) for k, v in batch.items()}
     optimizer = trainer.optimizers[0]
 
     phase_events: list = []
@@ -340,6 +372,8 @@ def main() -> None:
                                     'flat-param ZeRO (optimizer+grad sharded, params resident)'),
                        'comm': comm_name, 'reshard': zero3, 'multicast': multicast,
                        'optimizer': 'AdamW fp32 master, grad clip 1.0', 'recompute': recompute,
+                       **({'documents_per_sequence': args.docs} if args.docs > 1 else {}),
+                       **({'neftune_alpha': args.neftune} if args.neftune > 0 else {}),
                        'l2': 'working set (16 GB bf16 weights) >> 126 MB L2, no flush needed'},
             'mfu_of_measured_sustained_peak': mfu, 'model_tflops_per_gpu': value * flops_per_token / 1e12 / world,
             'clocks': clocks,
