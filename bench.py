@@ -381,6 +381,7 @@ def main() -> None:
                     'h2d_bytes_per_step': timer.h2d, 'd2h_bytes_per_step': timer.d2h,
                     'api': 'Trainer.fit(CLM, DummyDataModule)'},
             'gpu_launches': int(launches), 'last_loss': getattr(timer, 'last_loss', None),
+            'peak_mem_gib': round(torch.cuda.max_memory_allocated() / 2 ** 30, 1) if cuda else None,
             **({'phases': phases} if phases else {}),
         }))
     if dist.is_initialized():

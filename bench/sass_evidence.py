@@ -17,7 +17,9 @@ PATTERNS = collections.OrderedDict([
     ('UTMALDG (TMA load)', r'\bUTMALDG'), ('UTMASTG (TMA store)', r'\bUTMASTG'),
     ('UTMAREDG (TMA reduce-add)', r'\bUTMAREDG'), ('UTCBAR (tcgen05.commit)', r'\bUTCBAR'),
     ('SYNCS (mbarrier)', r'\bSYNCS'), ('LDG .SYS (peer / system-scope load)', r'\bLDG\.[A-Z0-9.]*SYS'),
-    ('STG .SYS / RED / ATOM', r'\b(STG\.[A-Z0-9.]*SYS|RED\.|REDG\.|ATOM|ATOMG)'), ('HMMA (legacy mma.sync)', r'\bHMMA'),
+    ('STG .SYS / RED / ATOM', r'\b(STG\.[A-Z0-9.]*SYS|RED\.|REDG\.|ATOM|ATOMG)'),
+    ('LDGMC / multimem (in-switch reduce, multicast store)', r'\b(LDGMC|STGMC|REDGMC|[A-Z]*\.MC\b)'),
+    ('HMMA (legacy mma.sync)', r'\bHMMA'),
 ])
 
 

@@ -6,7 +6,7 @@ Same class names and constructor arguments as the reference
 scheduler.  That makes ``state_dict`` trivially resumable (only ``last_epoch`` matters) and lets
 the fused optimizer kernel read the next LR without extra Python objects.
 
-Value parity with the reference (checked in tests/test_lr_schedulers.py):
+Value parity with the reference (checked in tests/test_core.py::test_lr_schedules_values_and_resume and the warm-up cases of tests/test_reference_oracle.py):
   * warm-up:  lr(t) = base * (t + 1) / W                 for t <  W      (warmup.py:25-28)
   * constant: lr(t) = base * factor if (t-W) < total_iters else base     (constant.py:7-26)
   * cosine:   lr(t) = min + (base-min) * (1+cos(pi*(t-W)/(N-W)))/2       (cosine.py:7-26)
