@@ -332,8 +332,13 @@ def main() -> None:
     hd = c['hidden_size'] // c['num_attention_heads']
     layer_params = c['hidden_size'] * (c['num_attention_heads'] + 2 * c['num_key_value_heads']) * hd \
         + c['hidden_size'] * c['hidden_size'] + 3 * c['hidden_size'] * c['intermediate_size']
+    # effective attended length: the whole sequence for pre-training packs, sum(len_i^2) / T for packed documents
+    attended = args.seq_len
+    if args.docs > 1:
+        seg = batch['attention_mask'][0]
+        attended = float(torch.bincount(seg)[1:].double().pow(2).sum()) / args.seq_len
     flops_per_token = 6 * layer_params * c['num_hidden_layers'] + 6 * c['hidden_size'] * c['vocab_size'] \
-        + 6 * c['num_hidden_layers'] * c['hidden_size'] * args.seq_len
+        + 6 * c['num_hidden_layers'] * c['hidden_size'] * attended
     peak = None
     try:
         peak = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))['bf16_tflops_sustained']
@@ -358,6 +363,10 @@ def main() -> None:
         comm_name = 'nvlink (parameters) + nccl (gradients)'
     else:
         comm_name = 'nccl'
+    tp_ctx = getattr(getattr(lm, 'model', None), 'tp_context', None)
+    if args.tp > 1:
+        tp_plane = 'nvlink fused GEMM+collective kernels' if getattr(tp_ctx, 'comm', None) is not None else 'nccl'
+        comm_name = f'tp: {tp_plane}; dp: {comm_name}'
     multicast = any(bool(getattr(getattr(e, a, None), 'multicast_ptr', 0)) and getattr(e.comm, 'use_multicast', False)
                     for e in engines for a in ('param_arena', 'grad_arena', 'shard_arena'))
     if rank == 0:

@@ -38,8 +38,16 @@ def wgrad(dy2: torch.Tensor, x2: torch.Tensor, weights: tuple[torch.Tensor, ...]
     if direct:
         target = weights[0].grad if len(weights) == 1 else _adjacent_rows_view(tuple(w.grad for w in weights))
         if target is not None and target.is_contiguous():
-            gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=target, residual=target)
+            # first gradient of the step for these weights: the engine skipped zeroing their range of the flat buffer
+            # (`_llmt_grad_fresh`), so the GEMM overwrites instead of accumulating — one pass over dW less on each side
+            fresh = all(getattr(w, '_llmt_grad_fresh', False) for w in weights)
+            if not fresh:
+                for w in weights:
+                    if getattr(w, '_llmt_grad_fresh', False):   # mixed group: make the stale ranges well defined
+                        w.grad.zero_()
+            gemm(dy2, x2, a_mn_major=True, b_mn_major=True, out=target, residual=None if fresh else target)
             for w in weights:
+                w._llmt_grad_fresh = False
                 w._llmt_grad_ready(w)
             return [None] * len(weights)
     dw = gemm(dy2, x2, a_mn_major=True, b_mn_major=True)

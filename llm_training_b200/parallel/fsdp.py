@@ -138,6 +138,7 @@ class FlatParamEngine:
         self.tp_axis = tp_axis if (tp_axis is not None and tp_axis.size() > 1) else None
         self.comm = comm if comm is not None else get_comm(self.axis)
         self.device = device
+        self.world_is_cuda = device.type == 'cuda'
         self.world, self.rank = self.axis.size(), self.axis.rank
         self.units: list[ShardedUnit] = []
         units = [(n, ps) for n, ps in units if ps]
@@ -245,10 +246,20 @@ class FlatParamEngine:
         if u.pending_grads == 0 and self.require_sync:
             self._launch_reduce(u)
 
+    def _settle_fresh(self, u: ShardedUnit) -> None:
+        """Weights whose zeroing was deferred to their first wgrad GEMM (`zero_grad`) but that received NO gradient
+        this step still hold last step's values: clear them before anything reads the buffer."""
+        for _, p in u.params:
+            if getattr(p, '_llmt_grad_fresh', False):
+                p._llmt_grad_fresh = False
+                if p.grad is not None:
+                    p.grad.zero_()
+
     def _launch_reduce(self, u: ShardedUnit) -> None:
         if u.reduced:
             return
         u.reduced = True
+        self._settle_fresh(u)
         if self.world == 1:
             if self.tp_axis is not None:
                 self._reduce(u)
@@ -290,11 +301,23 @@ class FlatParamEngine:
         """Let the wgrad GEMMs accumulate straight into the flat gradient buffer (``ops.linear_op.wgrad``).  Only
         valid when every weight is used ONCE per backward pass (the engine counts one notification per
         parameter to know when a unit's gradients are complete) — CLM turns it on, DPO / ORPO do not."""
+        def settle_before_accumulate(grad, p):
+            # a gradient is about to arrive through autograd's AccumulateGrad (an op that does not use the direct
+            # wgrad path: fused linear + loss, embedding): a deferred zeroing has to happen before the `+=`
+            if getattr(p, '_llmt_grad_fresh', False):
+                p._llmt_grad_fresh = False
+                if p.grad is not None:
+                    p.grad.zero_()
+            return grad
+
         for u in self.units:
             for _, p in u.params:
                 if p.requires_grad and p.dim() == 2:
                     p._llmt_direct_grad = flag
                     p._llmt_grad_ready = self._on_grad_ready
+                    if flag and not getattr(p, '_llmt_settle_hook', False):
+                        p.register_hook(lambda g, p=p: settle_before_accumulate(g, p))
+                        p._llmt_settle_hook = True
 
     def set_requires_gradient_sync(self, flag: bool) -> None:
         """False on non-boundary micro-batches of gradient accumulation (reference:
@@ -570,12 +593,23 @@ class FlatParamEngine:
         for u in self.units:
             if not u.grad_live or not u.with_grad:           # ZeRO-3: no storage until the unit's next backward allocates + clears it
                 continue
-            if not u.grad_zeroed:
-                self.wait_unit(u)
-                u.flat_grad.zero_()
             for (_, p), o in zip(u.params, u.offsets):   # something may have replaced .grad (set_to_none)
                 if p.grad is None or p.grad.data_ptr() != u.flat_grad.data_ptr() + o * u.flat_grad.element_size():
                     p.grad = u.flat_grad[o:o + p.numel()].view(p.shape)
+            if not u.grad_zeroed:
+                self.wait_unit(u)
+                direct = [getattr(p, '_llmt_direct_grad', False) and p.requires_grad for _, p in u.params]
+                if self.require_sync and self.world_is_cuda and any(direct):
+                    # weights that accumulate straight from their wgrad GEMM are not cleared here: their first GEMM
+                    # of the step overwrites (ops.linear_op.wgrad).  Everything else (norm weights, embeddings,
+                    # alignment gaps, which are never written) is cleared as before.
+                    for (_, p), o, d in zip(u.params, u.offsets, direct):
+                        if d:
+                            p._llmt_grad_fresh = True
+                        else:
+                            u.flat_grad[o:o + p.numel()].zero_()
+                else:
+                    u.flat_grad.zero_()
         self._reset_pending()
 
     def grad_norm_sq(self, extra_axes: list[Comm] | None = None) -> torch.Tensor:

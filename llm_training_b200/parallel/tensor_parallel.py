@@ -287,8 +287,12 @@ class _FusedGatherLinear(torch.autograd.Function):
         weight = weights[0] if len(weights) == 1 else _adjacent_rows_view(weights)
         if weight is None:
             weight = torch.cat([w.detach() for w in weights], dim=0)
-        out, x_full = _gather_gemm(tp, x_local.contiguous(), weight, b_mn_major=False)
-        ctx.save_for_backward(x_full, weight)
+        x_local = x_local.contiguous()
+        out, x_full = _gather_gemm(tp, x_local, weight, b_mn_major=False)
+        # memory-tight runs (activation checkpointing on) keep the [T/tp, d] shard and gather it again for dW in
+        # backward, like Megatron's sequence parallelism; otherwise the gathered input the kernel left behind is kept
+        ctx.regather = tp.regather_in_backward
+        ctx.save_for_backward(x_local if ctx.regather else x_full, weight)
         ctx.tp = tp
         ctx.splits = [w.shape[0] for w in weights]
         return out
@@ -297,6 +301,10 @@ class _FusedGatherLinear(torch.autograd.Function):
     def backward(ctx, dy: torch.Tensor):
         x_full, weight = ctx.saved_tensors
         tp = ctx.tp
+        if ctx.regather:
+            shard = x_full
+            x_full = torch.empty((shard.shape[0] * tp.size, shard.shape[1]), dtype=shard.dtype, device=shard.device)
+            dist.all_gather_into_tensor(x_full, shard, group=tp.axis.group)
         dy = dy.contiguous()
         dws = gemm(dy, x_full, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0)
         dx = _fused_linear_reduce_scatter(tp, dy, weight, None, b_mn_major=True)   # dy @ W, reduce-scattered
@@ -351,6 +359,7 @@ class TensorParallelContext:
         self.rank = axis.rank
         self.comm = None
         self.ring = None
+        self.regather_in_backward = False     # set by apply_decoder_tensor_parallel (LLMT_TP_REGATHER / checkpointing)
         if torch.cuda.is_available() and dist.is_initialized() and dist.get_backend(axis.group) == 'nccl':
             from .comm import get_comm
             comm = get_comm(axis)
@@ -490,3 +499,7 @@ def apply_decoder_tensor_parallel(model: nn.Module, tp_axis: MeshAxis, fused_qkv
         _shard_param(model.lm_head, 'weight', *col)
     model.norm.weight._tp_replicated = True
     model.tp_context = TensorParallelContext(tp_axis)
+    import os
+    regather = os.environ.get('LLMT_TP_REGATHER', 'auto')
+    model.tp_context.regather_in_backward = (bool(getattr(cfg, 'enable_gradient_checkpointing', False))
+                                             if regather == 'auto' else regather == '1')
