@@ -526,3 +526,45 @@ def test_optimizer_state_cpu_offload_matches_device_update():
         # same math, different fp32 instruction order: at most a bf16 ulp on a few elements
         assert float((a - b).abs().max()) <= 2e-2 * max(1.0, float(a.abs().max()))
         assert float(((a - b).abs() > 1e-6).float().mean()) < 0.05
+
+
+def test_direct_wgrad_accumulation_with_deferred_zeroing_matches_autograd_accumulation():
+    """Engine path of the benchmark on one GPU: wgrad GEMMs write straight into the flat gradient buffer, and the
+    buffer's weight ranges are NOT cleared between steps (the first wgrad of a step overwrites).  Four steps must
+    give the same parameters as the plain path (temporary dW + AccumulateGrad into a zeroed buffer)."""
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded
+    cfg = LlamaConfig(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2)
+    runs = []
+    for direct in (False, True):
+        torch.manual_seed(0)
+        with torch.device(DEV):
+            model = Llama(cfg).to(torch.bfloat16)
+        engine = apply_fully_sharded(model, None, device=torch.device(DEV))
+        engine.enable_direct_grad_accumulation(direct)
+        opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=0.1), [engine],
+                               max_grad_norm=1.0)
+        losses, saw_fresh = [], False
+        for step in range(4):
+            ids = torch.randint(0, 1024, (2, 256), generator=torch.Generator().manual_seed(step)).to(DEV)
+            opt.zero_grad()
+            saw_fresh |= any(getattr(p, '_llmt_grad_fresh', False) for p in model.parameters())
+            out = model(input_ids=ids, skip_logits=True)
+            loss = fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight,
+                                              shift_labels(ids).flatten())
+            loss.backward()
+            assert not any(getattr(p, '_llmt_grad_fresh', False) for p in model.parameters())
+            opt.step()
+            losses.append(float(loss))
+        assert saw_fresh == direct                       # the deferred zeroing really was in effect
+        torch.cuda.synchronize()
+        runs.append((losses, [p.detach().float().clone() for p in model.parameters()], float(opt.last_grad_norm)))
+    (l0, p0, n0), (l1, p1, n1) = runs
+    for a, b in zip(l0, l1):
+        assert abs(a - b) < 5e-3, (l0, l1)
+    assert abs(n0 - n1) < 5e-3 * max(1.0, n0)
+    for a, b in zip(p0, p1):
+        assert float((a - b).abs().max()) <= 2e-2 * max(1e-2, float(a.abs().max()))
