@@ -104,6 +104,10 @@ struct BwdParams {
   int tokens, hq, hkv, head_dim;
   float scale, scale_log2;
   int window;
+  // extras (attn_bwd_ts_kernel<true> only); same meaning as in the forward kernel
+  float softcap_in, softcap_out;   // scale / softcap, softcap * log2(e); 0 = no soft-capping
+  uint32_t drop_thr, seed;         // dropped when the element's random byte < drop_thr; 0 = no dropout
+  float drop_scale;                // 1 / (1 - p)
 };
 
 __device__ __forceinline__ float bwd_exp2(float x) {
@@ -493,6 +497,13 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+__device__ __forceinline__ float bwd_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <bool kExtras>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,128}
                    const __grid_constant__ CUtensorMap tmQ,     // qkv, box {64,1,64}
@@ -720,6 +731,8 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     };
 
     uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
+    float tv[32];                                        // soft-capping only: tanh(s * scale / cap) of the same step
+    int a_h = g * G, a_qi = 0;                           // (head, q block) of the step whose P^T / dS^T is being built
 
     meta_fetch();
     meta_store(0);
@@ -736,11 +749,29 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         const float* mD = meta(it) + 64 + c_base;
         // ---- P^T(it): registers -> tensor memory (bf16 pairs: column c/2 holds q columns c, c+1)
         mbar_wait(pds_empty, (it & 1) ^ 1);               // dV / dK / dQ MMAs of the previous step are done
+        uint32_t keep = 0xffffffffu;                       // bit c: P^T column c survives dropout
+        if constexpr (kExtras) {
+          if (p.drop_thr != 0) {
+            keep = 0;
+            const int qb = (i_lo + a_qi) * kBwdQ + c_base;
+#pragma unroll
+            for (int c = 0; c < 32; ++c) {
+              const uint32_t rnd = dropout_bits(p.seed, a_h, qb + c, kvi >> 2);
+              keep |= (((rnd >> (8 * (kvi & 3))) & 0xffu) >= p.drop_thr ? 1u : 0u) << c;
+            }
+          }
+        }
         {
           uint32_t pk[16];
 #pragma unroll
-          for (int c = 0; c < 16; ++c)
-            pk[c] = pack_bf16x2(__uint_as_float(sv[2 * c]), __uint_as_float(sv[2 * c + 1]));
+          for (int c = 0; c < 16; ++c) {
+            float p0 = __uint_as_float(sv[2 * c]), p1 = __uint_as_float(sv[2 * c + 1]);
+            if constexpr (kExtras) {
+              p0 = (keep >> (2 * c)) & 1u ? p0 : 0.f;      // dV sees the dropped probabilities (x 1/(1-p) at the end)
+              p1 = (keep >> (2 * c + 1)) & 1u ? p1 : 0.f;
+            }
+            pk[c] = pack_bf16x2(p0, p1);
+          }
           tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
         }
         // ---- dS^T(it) = P^T o (dP^T - delta)  (the softmax scale is applied to dK / dQ at the end)
@@ -756,11 +787,22 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) {
             const float4 d4 = *reinterpret_cast<const float4*>(mD + ch * 4);
-            const int c = ch * 4;
-            pk[ch * 2] = pack_bf16x2(__uint_as_float(sv[c]) * (__uint_as_float(dp[c]) - d4.x),
-                                     __uint_as_float(sv[c + 1]) * (__uint_as_float(dp[c + 1]) - d4.y));
-            pk[ch * 2 + 1] = pack_bf16x2(__uint_as_float(sv[c + 2]) * (__uint_as_float(dp[c + 2]) - d4.z),
-                                         __uint_as_float(sv[c + 3]) * (__uint_as_float(dp[c + 3]) - d4.w));
+            const float dl[4] = {d4.x, d4.y, d4.z, d4.w};
+            float ds[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              float dpv = __uint_as_float(dp[c]);
+              if constexpr (kExtras) {
+                if (p.drop_thr != 0) dpv = (keep >> c) & 1u ? dpv * p.drop_scale : 0.f;
+              }
+              ds[e] = __uint_as_float(sv[c]) * (dpv - dl[e]);
+              if constexpr (kExtras) {
+                if (p.softcap_in > 0.f) ds[e] *= 1.f - tv[c] * tv[c];    // d tanh
+              }
+            }
+            pk[ch * 2] = pack_bf16x2(ds[0], ds[1]);
+            pk[ch * 2 + 1] = pack_bf16x2(ds[2], ds[3]);
           }
           tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
 #pragma unroll
@@ -768,6 +810,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
             *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
                 make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
         }
+        advance(a_h, a_qi);
         tmem_st_wait();
         fence_proxy_async_smem();
         tc_fence_before();
@@ -819,29 +862,24 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         tmem_ld_wait();
         tc_fence_before();
         mbar_arrive(s_empty);                              // S^T(it+2) may overwrite the columns now
-        if (need_mask) {
-          const uint32_t off0 = (uint32_t)(q0 + c_base - kvi);
+        const uint32_t off0 = (uint32_t)(q0 + c_base - kvi);
+        const bool capped = kExtras && p.softcap_in > 0.f;
 #pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
-            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+        for (int ch = 0; ch < 8; ++ch) {
+          const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+          const float l[4] = {l4.x, l4.y, l4.z, l4.w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = ch * 4 + e;
-              const float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
-              sv[c] = (off0 + (uint32_t)c < valid_len) ? __float_as_uint(pv) : 0u;
+          for (int e = 0; e < 4; ++e) {
+            const int c = ch * 4 + e;
+            float pv;
+            if (capped) {
+              tv[c] = bwd_tanh(__uint_as_float(sv[c]) * p.softcap_in);
+              pv = bwd_exp2(fmaf(tv[c], p.softcap_out, -l[e]));
+            } else {
+              pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
             }
-          }
-        } else {
-#pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
-            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = ch * 4 + e;
-              sv[c] = __float_as_uint(bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e])));
-            }
+            if (need_mask) pv = (off0 + (uint32_t)c < valid_len) ? pv : 0.f;
+            sv[c] = __float_as_uint(pv);
           }
         }
       }
@@ -855,7 +893,10 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
       uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
       const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
-      const float mul = which == 0 ? p.scale : 1.f;
+      float mul = which == 0 ? p.scale : 1.f;
+      if constexpr (kExtras) {
+        if (which == 1 && p.drop_thr != 0) mul = p.drop_scale;   // dV = (P o mask)^T dO / (1 - p)
+      }
 #pragma unroll 1
       for (int c0 = 0; c0 < kBwdD; c0 += 32) {
         uint32_t o[32];
@@ -898,10 +939,11 @@ using namespace llmt::attn;
 
 // Backward of llmt_attn_fwd.  delta: fp32 [Hq, T] scratch; dq_acc: fp32 [T, Hq*D] scratch, must be ZERO on
 // entry; dqkv: bf16 [T, (Hq+2Hkv)*D] (same row stride as qkv), fully overwritten.
-extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
-                             float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
-                             int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
-                             cudaStream_t stream) {
+// softcap / dropout_thr / seed: the values the forward call (llmt_attn_fwd_ex) was given.
+extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                                float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
+                                int hkv, int head_dim, int64_t qkv_stride, float scale, int window, float softcap,
+                                int dropout_thr, uint32_t seed, cudaStream_t stream) {
   LLMT_REQUIRE(tokens > 0 && hq > 0 && hkv > 0 && hq % hkv == 0, "attn_bwd: bad head counts %d/%d", hq, hkv);
   LLMT_REQUIRE(head_dim % 16 == 0 && head_dim <= 128, "attn_bwd: head_dim %d unsupported", head_dim);
   LLMT_REQUIRE(qkv_stride % 8 == 0, "attn_bwd: qkv stride must be a multiple of 8");
@@ -929,20 +971,35 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   p.seg_start = seg_start; p.seg_end = seg_end; p.lse = lse; p.delta = delta; p.dq_acc = dq_acc;
   p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
   p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f; p.window = window;
+  LLMT_REQUIRE(softcap >= 0.f && dropout_thr >= 0 && dropout_thr < 256, "attn_bwd: softcap must be >= 0 and the "
+               "dropout threshold in [0, 255] (got %f, %d)", softcap, dropout_thr);
+  p.softcap_in = softcap > 0.f ? scale / softcap : 0.f;
+  p.softcap_out = softcap * 1.4426950408889634f;
+  p.drop_thr = (uint32_t)dropout_thr;
+  p.seed = seed;
+  p.drop_scale = 256.f / (256.f - (float)dropout_thr);
+  const bool extras = softcap > 0.f || dropout_thr > 0;
   dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
   // LLMT_ATTN_BWD=ss selects the first-generation kernel (every MMA operand in shared memory); default: P^T / dS^T in
   // tensor memory
   static const bool use_ss = [] { const char* e = getenv("LLMT_ATTN_BWD"); return e && e[0] == 's'; }();
+  LLMT_REQUIRE(!(use_ss && extras), "attn_bwd: LLMT_ATTN_BWD=ss has no soft-capping / dropout");
   if (use_ss) {
     static bool configured[kMaxDevices] = {};
     rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
     if (rc) return rc;
     attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
   } else {
-    static bool configured[kMaxDevices] = {};
-    rc = ensure_smem_attr(attn_bwd_ts_kernel, BwdTsCfg::kSmemBytes, configured, "attn_bwd");
-    if (rc) return rc;
-    attn_bwd_ts_kernel<<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+    static bool configured[2][kMaxDevices] = {};
+    if (extras) {
+      rc = ensure_smem_attr(attn_bwd_ts_kernel<true>, BwdTsCfg::kSmemBytes, configured[1], "attn_bwd");
+      if (rc) return rc;
+      attn_bwd_ts_kernel<true><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+    } else {
+      rc = ensure_smem_attr(attn_bwd_ts_kernel<false>, BwdTsCfg::kSmemBytes, configured[0], "attn_bwd");
+      if (rc) return rc;
+      attn_bwd_ts_kernel<false><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+    }
   }
   rc = check_launch("attn_bwd");
   if (rc) return rc;
@@ -954,4 +1011,12 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
   attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, (__nv_bfloat16*)dqkv, tokens, width,
                                                                qkv_stride, use_ss ? 1.f : scale);
   return check_launch("attn_dq_convert");
+}
+
+extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
+                             float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
+                             int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
+                             cudaStream_t stream) {
+  return llmt_attn_bwd_ex(qkv, out, dout, lse, delta, dq_acc, dqkv, seg_start, seg_end, tokens, hq, hkv, head_dim,
+                          qkv_stride, scale, window, 0.f, 0, 0u, stream);
 }

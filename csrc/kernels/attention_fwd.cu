@@ -54,6 +54,11 @@ struct FwdParams {
   int tokens, hq, hkv, head_dim;
   float scale_log2;    // softmax scale * log2(e)
   int window;          // 0 = none
+  // extras (attn_fwd_kernel<DPAD, true> only)
+  float softcap_in;    // scale / softcap            (0 = no soft-capping)
+  float softcap_out;   // softcap * log2(e)
+  uint32_t drop_thr;   // an element is DROPPED when its random byte < drop_thr (p = drop_thr / 256; 0 = no dropout)
+  uint32_t seed;
 };
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -62,7 +67,13 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-template <int DPAD>
+__device__ __forceinline__ float fast_tanh(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int DPAD, bool kExtras>
 __global__ void __launch_bounds__(kFwdThreads, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 128} over [T][heads][D]
                 const __grid_constant__ CUtensorMap tmQKV_kv,  // box {64, 1, 64}
@@ -256,7 +267,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
 #pragma unroll
         for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sv[c]));
       }
-      const float m_blk = mx * p.scale_log2;
+      if constexpr (kExtras) {
+        // soft-capping (cap * tanh(s * scale / cap)) turns the scores into their final log2-domain values here;
+        // masked entries stay -inf
+        if (p.softcap_in > 0.f) {
+          mx = -INFINITY;
+#pragma unroll
+          for (int c = 0; c < 64; ++c) {
+            const float s = __uint_as_float(sv[c]);
+            const float x = (s == -INFINITY) ? -INFINITY : p.softcap_out * fast_tanh(s * p.softcap_in);
+            sv[c] = __float_as_uint(x);
+            mx = fmaxf(mx, x);
+          }
+        }
+      }
+      const bool capped = kExtras && p.softcap_in > 0.f;
+      const float sc = capped ? 1.f : p.scale_log2;         // capped scores are already scaled
+      const float m_blk = mx * sc;
       // lazy rescale: keep the stale max unless it is exceeded by more than 2^8
       float alpha = 1.f;
       if (m_blk > m + 8.f || m == -INFINITY) {
@@ -269,9 +296,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
       uint32_t pk[32];
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
-        const float e0 = fast_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -m_use));
-        const float e1 = fast_exp2(fmaf(__uint_as_float(sv[c + 1]), p.scale_log2, -m_use));
-        sum += e0 + e1;
+        float e0 = fast_exp2(fmaf(__uint_as_float(sv[c]), sc, -m_use));
+        float e1 = fast_exp2(fmaf(__uint_as_float(sv[c + 1]), sc, -m_use));
+        sum += e0 + e1;                                     // the normaliser is the UNdropped sum
+        if constexpr (kExtras) {
+          if (p.drop_thr != 0) {
+            const uint32_t rnd = dropout_bits(p.seed, head, q_idx, (kv0 + c) >> 2);   // c is even: same 4-group
+            e0 = (((rnd >> (8 * ((kv0 + c) & 3))) & 0xffu) < p.drop_thr) ? 0.f : e0;
+            e1 = (((rnd >> (8 * ((kv0 + c + 1) & 3))) & 0xffu) < p.drop_thr) ? 0.f : e1;
+          }
+        }
         __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
         pk[c >> 1] = *reinterpret_cast<uint32_t*>(&h);
       }
@@ -307,7 +341,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
     // ---- epilogue: O / l -> bf16 -> smem (Q region) -> TMA store; LSE
     mbar_wait(o_done, (nb - 1) & 1);
     tc_fence_after();
-    const float inv_l = (l > 0.f) ? 1.f / l : 0.f;
+    float inv_l = (l > 0.f) ? 1.f / l : 0.f;
+    if constexpr (kExtras) {
+      if (p.drop_thr != 0) inv_l *= 256.f / (256.f - (float)p.drop_thr);   // kept elements are scaled by 1 / (1 - p)
+    }
     uint8_t* o_stage = smem + C::kQOff;
 #pragma unroll
     for (int c0 = 0; c0 < DPAD; c0 += 32) {
@@ -401,11 +438,11 @@ int make_tmap_f32_2d(CUtensorMap* out, const void* ptr, int64_t rows, int64_t co
   return 0;
 }
 
-template <int DPAD>
+template <int DPAD, bool kExtras>
 int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap& to, const FwdParams& p,
                cudaStream_t stream) {
   using C = FwdCfg<DPAD>;
-  auto kern = attn_fwd_kernel<DPAD>;
+  auto kern = attn_fwd_kernel<DPAD, kExtras>;
   static bool configured[kMaxDevices] = {};
   if (int rc = ensure_smem_attr(kern, C::kSmemBytes, configured, "attn_fwd")) return rc;
   dim3 grid((p.tokens + kBlockQ - 1) / kBlockQ, p.hq);
@@ -421,9 +458,12 @@ using namespace llmt::attn;
 
 // qkv: bf16 [T, (Hq + 2*Hkv) * D] (row stride in elements), q heads | k heads | v heads.
 // out: bf16 [T, Hq*D] contiguous.  lse: fp32 [Hq, T] (log2 units).  seg_start: int32 [T].
-extern "C" int llmt_attn_fwd(const void* qkv, void* out, float* lse, const int* seg_start, int tokens, int hq,
-                             int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
-                             cudaStream_t stream) {
+// softcap > 0: scores become softcap * tanh(score * scale / softcap) before the softmax.  dropout_thr in [0, 255]:
+// attention probabilities are dropped with p = dropout_thr / 256 and the kept ones scaled by 1 / (1 - p); the mask is
+// a pure function of (seed, head, query, key) — see dropout_bits() — so the backward kernel regenerates it.
+extern "C" int llmt_attn_fwd_ex(const void* qkv, void* out, float* lse, const int* seg_start, int tokens, int hq,
+                                int hkv, int head_dim, int64_t qkv_stride, float scale, int window, float softcap,
+                                int dropout_thr, uint32_t seed, cudaStream_t stream) {
   LLMT_REQUIRE(tokens > 0 && hq > 0 && hkv > 0 && hq % hkv == 0, "attn_fwd: bad head counts %d/%d", hq, hkv);
   LLMT_REQUIRE(head_dim % 16 == 0 && head_dim <= 128, "attn_fwd: head_dim %d unsupported (multiple of 16, <= 128)",
                head_dim);
@@ -440,8 +480,22 @@ extern "C" int llmt_attn_fwd(const void* qkv, void* out, float* lse, const int* 
   p.seg_start = seg_start;
   p.lse = lse;
   p.tokens = tokens; p.hq = hq; p.hkv = hkv; p.head_dim = head_dim;
+  LLMT_REQUIRE(softcap >= 0.f && dropout_thr >= 0 && dropout_thr < 256, "attn_fwd: softcap must be >= 0 and the "
+               "dropout threshold in [0, 255] (got %f, %d)", softcap, dropout_thr);
   p.scale_log2 = scale * 1.4426950408889634f;
   p.window = window;
-  if (head_dim <= 64) return launch_fwd<64>(tq, tkv, to, p, stream);
-  return launch_fwd<128>(tq, tkv, to, p, stream);
+  p.softcap_in = softcap > 0.f ? scale / softcap : 0.f;
+  p.softcap_out = softcap * 1.4426950408889634f;
+  p.drop_thr = (uint32_t)dropout_thr;
+  p.seed = seed;
+  const bool extras = softcap > 0.f || dropout_thr > 0;
+  if (head_dim <= 64) return extras ? launch_fwd<64, true>(tq, tkv, to, p, stream) : launch_fwd<64, false>(tq, tkv, to, p, stream);
+  return extras ? launch_fwd<128, true>(tq, tkv, to, p, stream) : launch_fwd<128, false>(tq, tkv, to, p, stream);
+}
+
+extern "C" int llmt_attn_fwd(const void* qkv, void* out, float* lse, const int* seg_start, int tokens, int hq,
+                             int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
+                             cudaStream_t stream) {
+  return llmt_attn_fwd_ex(qkv, out, lse, seg_start, tokens, hq, hkv, head_dim, qkv_stride, scale, window, 0.f, 0, 0u,
+                          stream);
 }

@@ -84,6 +84,17 @@ __device__ __forceinline__ bf16x8 pack8(const float (&f)[8]) {
   return r;
 }
 
+// Attention dropout: 32 random bits for the four keys 4*kv_group .. 4*kv_group+3 of (head, query) — byte k decides
+// key 4*kv_group + k.  A stateless integer hash (lowbias32 finaliser over a linear combination of the coordinates), so
+// the forward and the backward kernel regenerate the same mask from (seed, head, query, key) with no stored state.
+__device__ __forceinline__ uint32_t dropout_bits(uint32_t seed, int head, int q, int kv_group) {
+  uint32_t x = seed + (uint32_t)head * 0xC2B2AE3Du + (uint32_t)q * 0x9E3779B1u + (uint32_t)kv_group * 0x85EBCA77u;
+  x ^= x >> 16; x *= 0x7feb352du;
+  x ^= x >> 15; x *= 0x846ca68bu;
+  x ^= x >> 16;
+  return x;
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -174,11 +174,15 @@ def attention_core(qkv: torch.Tensor, ctx: PackedContext, *, num_heads: int, num
                    selective_recompute: bool = False) -> torch.Tensor:
     """RoPE + attention on the fused ``q|k|v`` projection output ``[T, (Hq+2Hkv)*D]`` -> ``[T, Hq*D]``."""
     qkv = rope_qk_packed(qkv, ctx.positions, ctx.cos, ctx.sin, num_heads + num_kv_heads, head_dim)
-    use_kernel_path = impl == 'flash_attention_2' and not (training and dropout_p > 0.0)
+    use_kernel_path = impl == 'flash_attention_2'
+    p_drop = dropout_p if training else 0.0
+    # one seed per call, drawn on the host: activation recompute re-runs `core` with the same mask
+    seed = int(torch.randint(0, 2 ** 31 - 1, (1,)).item()) if (use_kernel_path and p_drop > 0.0) else None
 
     def core(t: torch.Tensor) -> torch.Tensor:
         if use_kernel_path:
-            return packed_attention(t, ctx.seg_start, ctx.seg_end, num_heads, num_kv_heads, head_dim, None, window)
+            return packed_attention(t, ctx.seg_start, ctx.seg_end, num_heads, num_kv_heads, head_dim, None, window,
+                                    dropout_p=p_drop, seed=seed)
         return _eager_or_sdpa_attention(t, ctx, num_heads, num_kv_heads, head_dim,
                                         'eager' if impl == 'flash_attention_2' else impl, window, dropout_p, training)
 

@@ -72,12 +72,33 @@ def attention_mask_from_bounds(seg_start: torch.Tensor, window: int | None = Non
     return allowed
 
 
+def dropout_keep_mask(seed: int, num_heads: int, tokens: int, drop_thr: int, device: torch.device | str = 'cpu'
+                      ) -> torch.Tensor:
+    """Boolean ``[Hq, T, T]`` keep-mask of attention dropout, bit-identical to the kernels' (csrc/kernels/common.cuh
+    ``dropout_bits``): element (head, q, kv) is dropped when byte ``kv % 4`` of the 32-bit hash of
+    ``(seed, head, q, kv // 4)`` is below ``drop_thr``."""
+    m = 0xffffffff
+    h = torch.arange(num_heads, dtype=torch.int64, device=device).view(-1, 1, 1)
+    q = torch.arange(tokens, dtype=torch.int64, device=device).view(1, -1, 1)
+    kv = torch.arange(tokens, dtype=torch.int64, device=device).view(1, 1, -1)
+    x = (seed + h * 0xC2B2AE3D + q * 0x9E3779B1 + (kv // 4) * 0x85EBCA77) & m
+    x = x ^ (x >> 16)
+    x = (x * 0x7feb352d) & m
+    x = x ^ (x >> 15)
+    x = (x * 0x846ca68b) & m
+    x = x ^ (x >> 16)
+    byte = (x >> (8 * (kv % 4))) & 0xff
+    return byte >= drop_thr
+
+
 def attention_ref(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, seg_start: torch.Tensor,
                   scale: float | None = None, window: int | None = None,
-                  softcap: float = 0.0) -> torch.Tensor:
+                  softcap: float = 0.0, dropout_keep: torch.Tensor | None = None,
+                  dropout_p: float = 0.0) -> torch.Tensor:
     """Packed causal attention with per-token document lower bounds.
 
-    q: [T, Hq, D]; k, v: [T, Hkv, D]; seg_start: int [T]. Returns [T, Hq, D].
+    q: [T, Hq, D]; k, v: [T, Hkv, D]; seg_start: int [T]. Returns [T, Hq, D].  ``dropout_keep``: boolean
+    ``[Hq, T, T]`` (True = keep), applied to the normalised probabilities with the usual ``1 / (1 - p)`` scaling.
     """
     t, hq, d = q.shape
     hkv = k.shape[1]
@@ -91,6 +112,8 @@ def attention_ref(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, seg_start: 
     allowed = attention_mask_from_bounds(seg_start, window)
     s = s.masked_fill(~allowed[None], float('-inf'))
     p = torch.softmax(s, dim=-1)
+    if dropout_keep is not None:
+        p = p * dropout_keep.to(p.dtype) / (1.0 - dropout_p)
     o = torch.matmul(p, vf)                                          # [Hq, T, D]
     return o.transpose(0, 1).to(q.dtype)
 

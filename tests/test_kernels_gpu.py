@@ -224,8 +224,8 @@ def test_adamw_and_sumsq():
     _close(p.cpu(), mr, rtol=1e-2, atol=1e-2)
 
 
-def _attn_case(tokens, hq, hkv, d, doc_lens=None, window=None, batch_rows=None):
-    from llm_training_b200.ops.attention_op import packed_attention
+def _attn_case(tokens, hq, hkv, d, doc_lens=None, window=None, batch_rows=None, softcap=0.0, dropout_p=0.0, seed=1234):
+    from llm_training_b200.ops.attention_op import dropout_threshold, packed_attention
     torch.manual_seed(0)
     width = (hq + 2 * hkv) * d
     qkv = (torch.randn(tokens, width, device=DEV) * 0.7).bfloat16().requires_grad_()
@@ -242,12 +242,14 @@ def _attn_case(tokens, hq, hkv, d, doc_lens=None, window=None, batch_rows=None):
         start = torch.tensor(s, dtype=torch.int32, device=DEV)
         end = torch.tensor(e, dtype=torch.int32, device=DEV)
     dout = torch.randn(tokens, hq * d, device=DEV).bfloat16()
-    out = packed_attention(qkv, start, end, hq, hkv, d, None, window)
+    out = packed_attention(qkv, start, end, hq, hkv, d, None, window, dropout_p=dropout_p, softcap=softcap, seed=seed)
     out.backward(dout)
     ref_in = qkv.detach().float().cpu().requires_grad_()
     q, k, v = ref_in.split([hq * d, hkv * d, hkv * d], dim=-1)
+    thr = dropout_threshold(dropout_p) if dropout_p else 0
+    keep = ref.dropout_keep_mask(seed, hq, tokens, thr) if thr else None     # the kernels' mask, restated in torch
     o_ref = ref.attention_ref(q.reshape(tokens, hq, d), k.reshape(tokens, hkv, d), v.reshape(tokens, hkv, d),
-                              start.cpu(), None, window).reshape(tokens, hq * d)
+                              start.cpu(), None, window, softcap, keep, thr / 256.0).reshape(tokens, hq * d)
     o_ref.backward(dout.float().cpu())
     _close(out.cpu(), o_ref, rtol=2e-2, atol=2e-2)
     g, gr = qkv.grad.cpu().float(), ref_in.grad
@@ -269,6 +271,22 @@ def test_attention_packed_documents():
 
 def test_attention_sliding_window():
     _attn_case(512, 2, 1, 128, doc_lens=[300, 212], window=96)
+
+
+def test_attention_softcap():
+    """cap * tanh(score / cap) before the softmax (the `softcap` argument of the reference's dispatcher,
+    ops/attention_op.py:550), forward and backward (d tanh in dS)."""
+    _attn_case(512, 4, 2, 128, doc_lens=[200, 312], softcap=15.0)
+    _attn_case(384, 2, 2, 64, softcap=30.0)
+
+
+@pytest.mark.parametrize('dropout_p', [0.125, 0.5])
+def test_attention_dropout_matches_oracle_with_the_same_mask(dropout_p):
+    """Attention dropout on the kernel path: the mask is a stateless hash of (seed, head, query, key), so the fp32
+    oracle can apply the identical mask; forward (normaliser from the UNdropped sum, 1/(1-p) scaling) and backward
+    (mask regenerated in the transposed kernel) must both match."""
+    _attn_case(640, 4, 2, 128, doc_lens=[100, 28, 200, 56, 256], dropout_p=dropout_p, seed=77)
+    _attn_case(256, 2, 1, 64, dropout_p=dropout_p, softcap=20.0, window=64, seed=3)
 
 
 def test_fused_norm_multi_linear_and_swiglu_down():
