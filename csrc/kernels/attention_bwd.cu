@@ -749,68 +749,103 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         const float* mD = meta(it) + 64 + c_base;
         // ---- P^T(it): registers -> tensor memory (bf16 pairs: column c/2 holds q columns c, c+1)
         mbar_wait(pds_empty, (it & 1) ^ 1);               // dV / dK / dQ MMAs of the previous step are done
-        uint32_t keep = 0xffffffffu;                       // bit c: P^T column c survives dropout
-        if constexpr (kExtras) {
-          if (p.drop_thr != 0) {
-            keep = 0;
-            const int qb = (i_lo + a_qi) * kBwdQ + c_base;
+        if constexpr (!kExtras) {
+          {
+            uint32_t pk[16];
 #pragma unroll
-            for (int c = 0; c < 32; ++c) {
-              const uint32_t rnd = dropout_bits(p.seed, a_h, qb + c, kvi >> 2);
-              keep |= (((rnd >> (8 * (kvi & 3))) & 0xffu) >= p.drop_thr ? 1u : 0u) << c;
-            }
+            for (int c = 0; c < 16; ++c)
+              pk[c] = pack_bf16x2(__uint_as_float(sv[2 * c]), __uint_as_float(sv[2 * c + 1]));
+            tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
           }
-        }
-        {
-          uint32_t pk[16];
+          // ---- dS^T(it) = P^T o (dP^T - delta)  (the softmax scale is applied to dK / dQ at the end)
+          {
+            uint32_t dp[32];
+            mbar_wait(dp_full, it & 1);
+            tc_fence_after();
+            tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(dp_empty);
+            uint32_t pk[16];
 #pragma unroll
-          for (int c = 0; c < 16; ++c) {
-            float p0 = __uint_as_float(sv[2 * c]), p1 = __uint_as_float(sv[2 * c + 1]);
-            if constexpr (kExtras) {
-              p0 = (keep >> (2 * c)) & 1u ? p0 : 0.f;      // dV sees the dropped probabilities (x 1/(1-p) at the end)
-              p1 = (keep >> (2 * c + 1)) & 1u ? p1 : 0.f;
+            for (int ch = 0; ch < 8; ++ch) {
+              const float4 d4 = *reinterpret_cast<const float4*>(mD + ch * 4);
+              const int c = ch * 4;
+              pk[ch * 2] = pack_bf16x2(__uint_as_float(sv[c]) * (__uint_as_float(dp[c]) - d4.x),
+                                       __uint_as_float(sv[c + 1]) * (__uint_as_float(dp[c + 1]) - d4.y));
+              pk[ch * 2 + 1] = pack_bf16x2(__uint_as_float(sv[c + 2]) * (__uint_as_float(dp[c + 2]) - d4.z),
+                                           __uint_as_float(sv[c + 3]) * (__uint_as_float(dp[c + 3]) - d4.w));
             }
-            pk[c] = pack_bf16x2(p0, p1);
+            tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch)
+              *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
+                  make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
           }
-          tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
-        }
-        // ---- dS^T(it) = P^T o (dP^T - delta)  (the softmax scale is applied to dK / dQ at the end)
-        {
-          uint32_t dp[32];
-          mbar_wait(dp_full, it & 1);
-          tc_fence_after();
-          tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
-          tmem_ld_wait();
-          tc_fence_before();
-          mbar_arrive(dp_empty);
-          uint32_t pk[16];
-#pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const float4 d4 = *reinterpret_cast<const float4*>(mD + ch * 4);
-            const float dl[4] = {d4.x, d4.y, d4.z, d4.w};
-            float ds[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const int c = ch * 4 + e;
-              float dpv = __uint_as_float(dp[c]);
-              if constexpr (kExtras) {
-                if (p.drop_thr != 0) dpv = (keep >> c) & 1u ? dpv * p.drop_scale : 0.f;
-              }
-              ds[e] = __uint_as_float(sv[c]) * (dpv - dl[e]);
-              if constexpr (kExtras) {
-                if (p.softcap_in > 0.f) ds[e] *= 1.f - tv[c] * tv[c];    // d tanh
+        } else {
+          uint32_t keep = 0xffffffffu;                       // bit c: P^T column c survives dropout
+          if constexpr (kExtras) {
+            if (p.drop_thr != 0) {
+              keep = 0;
+              const int qb = (i_lo + a_qi) * kBwdQ + c_base;
+  #pragma unroll
+              for (int c = 0; c < 32; ++c) {
+                const uint32_t rnd = dropout_bits(p.seed, a_h, qb + c, kvi >> 2);
+                keep |= (((rnd >> (8 * (kvi & 3))) & 0xffu) >= p.drop_thr ? 1u : 0u) << c;
               }
             }
-            pk[ch * 2] = pack_bf16x2(ds[0], ds[1]);
-            pk[ch * 2 + 1] = pack_bf16x2(ds[2], ds[3]);
           }
-          tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
-#pragma unroll
-          for (int ch = 0; ch < 4; ++ch)
-            *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
-                make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+          {
+            uint32_t pk[16];
+  #pragma unroll
+            for (int c = 0; c < 16; ++c) {
+              float p0 = __uint_as_float(sv[2 * c]), p1 = __uint_as_float(sv[2 * c + 1]);
+              if constexpr (kExtras) {
+                p0 = (keep >> (2 * c)) & 1u ? p0 : 0.f;      // dV sees the dropped probabilities (x 1/(1-p) at the end)
+                p1 = (keep >> (2 * c + 1)) & 1u ? p1 : 0.f;
+              }
+              pk[c] = pack_bf16x2(p0, p1);
+            }
+            tmem_st_32x32b_x16(t_lane + C::kColP + hf * 16, pk);
+          }
+          // ---- dS^T(it) = P^T o (dP^T - delta)  (the softmax scale is applied to dK / dQ at the end)
+          {
+            uint32_t dp[32];
+            mbar_wait(dp_full, it & 1);
+            tc_fence_after();
+            tmem_ld_32x32b_x32(t_lane + C::kColDPT + c_base, dp);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(dp_empty);
+            uint32_t pk[16];
+  #pragma unroll
+            for (int ch = 0; ch < 8; ++ch) {
+              const float4 d4 = *reinterpret_cast<const float4*>(mD + ch * 4);
+              const float dl[4] = {d4.x, d4.y, d4.z, d4.w};
+              float ds[4];
+  #pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const int c = ch * 4 + e;
+                float dpv = __uint_as_float(dp[c]);
+                if constexpr (kExtras) {
+                  if (p.drop_thr != 0) dpv = (keep >> c) & 1u ? dpv * p.drop_scale : 0.f;
+                }
+                ds[e] = __uint_as_float(sv[c]) * (dpv - dl[e]);
+                if constexpr (kExtras) {
+                  if (p.softcap_in > 0.f) ds[e] *= 1.f - tv[c] * tv[c];    // d tanh
+                }
+              }
+              pk[ch * 2] = pack_bf16x2(ds[0], ds[1]);
+              pk[ch * 2 + 1] = pack_bf16x2(ds[2], ds[3]);
+            }
+            tmem_st_32x32b_x16(t_lane + C::kColDS + hf * 16, pk);
+  #pragma unroll
+            for (int ch = 0; ch < 4; ++ch)
+              *reinterpret_cast<uint4*>(ds_row + (((hf * 4 + ch) ^ (r & 7)) << 4)) =
+                  make_uint4(pk[4 * ch], pk[4 * ch + 1], pk[4 * ch + 2], pk[4 * ch + 3]);
+          }
+          advance(a_h, a_qi);
         }
-        advance(a_h, a_qi);
         tmem_st_wait();
         fence_proxy_async_smem();
         tc_fence_before();
@@ -863,23 +898,48 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         tc_fence_before();
         mbar_arrive(s_empty);                              // S^T(it+2) may overwrite the columns now
         const uint32_t off0 = (uint32_t)(q0 + c_base - kvi);
-        const bool capped = kExtras && p.softcap_in > 0.f;
+        if constexpr (kExtras) {
+          const bool capped = p.softcap_in > 0.f;
 #pragma unroll
-        for (int ch = 0; ch < 8; ++ch) {
-          const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
-          const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const int c = ch * 4 + e;
-            float pv;
-            if (capped) {
-              tv[c] = bwd_tanh(__uint_as_float(sv[c]) * p.softcap_in);
-              pv = bwd_exp2(fmaf(tv[c], p.softcap_out, -l[e]));
-            } else {
-              pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              float pv;
+              if (capped) {
+                tv[c] = bwd_tanh(__uint_as_float(sv[c]) * p.softcap_in);
+                pv = bwd_exp2(fmaf(tv[c], p.softcap_out, -l[e]));
+              } else {
+                pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
+              }
+              if (need_mask) pv = (off0 + (uint32_t)c < valid_len) ? pv : 0.f;
+              sv[c] = __float_as_uint(pv);
             }
-            if (need_mask) pv = (off0 + (uint32_t)c < valid_len) ? pv : 0.f;
-            sv[c] = __float_as_uint(pv);
+          }
+        } else if (need_mask) {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              const float pv = bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e]));
+              sv[c] = (off0 + (uint32_t)c < valid_len) ? __float_as_uint(pv) : 0u;
+            }
+          }
+        } else {
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 l4 = *reinterpret_cast<const float4*>(mL + ch * 4);
+            const float l[4] = {l4.x, l4.y, l4.z, l4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int c = ch * 4 + e;
+              sv[c] = __float_as_uint(bwd_exp2(fmaf(__uint_as_float(sv[c]), p.scale_log2, -l[e])));
+            }
           }
         }
       }
