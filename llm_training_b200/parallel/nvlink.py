@@ -37,6 +37,7 @@ class SymmetricBuffer:
         self.tensor = tensor
         self.handle = handle
         self.peer_ptrs: list[int] = [int(p) for p in handle.buffer_ptrs]
+        self._ptr_cache: dict[int, Any] = {}      # byte offset -> ctypes array of the peers' addresses
         # NVSwitch multicast mapping of the same buffer (0 when the fabric / driver does not offer one)
         try:
             self.multicast_ptr = int(getattr(handle, 'multicast_ptr', 0) or 0)
@@ -44,7 +45,12 @@ class SymmetricBuffer:
             self.multicast_ptr = 0
 
     def peer_ptrs_at(self, byte_offset: int):
-        return _ptr_array([p + byte_offset for p in self.peer_ptrs])
+        arr = self._ptr_cache.get(byte_offset)
+        if arr is None:
+            if len(self._ptr_cache) > 4096:
+                self._ptr_cache.clear()
+            arr = self._ptr_cache[byte_offset] = _ptr_array([p + byte_offset for p in self.peer_ptrs])
+        return arr
 
 
 class NVLinkComm(Comm):

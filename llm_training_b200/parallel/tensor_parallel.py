@@ -222,16 +222,27 @@ class _SymmetricRing:
     """Two alternating symmetric buffers per shape: buffer k is rewritten only after the barrier of use k+1, i.e.
     after every peer has finished reading it (see the protocol note in ``parallel/nvlink.py``)."""
 
+    MAX_SHAPES = 16     # distinct (rows, cols) kept alive; variable-length batches would otherwise grow the heap forever
+
     def __init__(self, comm: Any) -> None:
         self.comm = comm
-        self.buffers: dict[tuple, list] = {}
+        self.buffers: dict[tuple, list] = {}     # insertion order = least recently used first
         self.turn: dict[tuple, int] = {}
 
     def next(self, rows: int, cols: int):
         key = (rows, cols)
         if key not in self.buffers:
+            while len(self.buffers) >= self.MAX_SHAPES:
+                # every rank sees the same sequence of shapes, so every rank evicts the same entry; a barrier makes
+                # sure no peer is still reading the buffers that are about to be unmapped
+                oldest = next(iter(self.buffers))
+                self.comm.barrier()
+                torch.cuda.current_stream().synchronize()
+                del self.buffers[oldest], self.turn[oldest]
             self.buffers[key] = [self.comm.alloc(rows * cols, torch.bfloat16) for _ in range(2)]
             self.turn[key] = 0
+        else:
+            self.buffers[key] = self.buffers.pop(key)      # mark as most recently used
         self.turn[key] ^= 1
         buf = self.buffers[key][self.turn[key]]
         return buf, buf.tensor.view(rows, cols)
