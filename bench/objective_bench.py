@@ -30,6 +30,7 @@ def main() -> None:
     ap.add_argument('--seq-len', type=int, default=4096)
     ap.add_argument('--pairs', type=int, default=2, help='preference pairs per GPU per step')
     ap.add_argument('--layers', type=int, default=0)
+    ap.add_argument('--reshard', action='store_true', help='ZeRO-3: policy AND frozen reference model sharded')
     ap.add_argument('--loss', default='fused', choices=['fused', 'materialized'],
                     help="'materialized' computes the sequence log-probs the reference's way (full [B, T, V] logits -> "
                          'fp32 log_softmax -> gather; /root/reference/src/llm_training/lms/dpo/dpo.py:110-114, '
@@ -48,7 +49,9 @@ def main() -> None:
                   model=dict(model_class='llm_training.models.Phi3', model_config=cfg),
                   optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=1e-6)))
     lm = DPO(DPOConfig.model_validate(common)) if args.objective == 'dpo' else ORPO(ORPOConfig.model_validate(common))
-    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world), precision='bf16-true', logger=False,
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=world,
+                                             reshard_after_forward=True if args.reshard else 'auto'),
+                      precision='bf16-true', logger=False,
                       enable_progress_bar=False, enable_checkpointing=False, gradient_clip_val=1.0)
     lm.trainer = trainer
     trainer.lightning_module = lm
@@ -106,7 +109,9 @@ def main() -> None:
                           'dtype': 'bf16', 'data': 'synthetic',
                           'config': {'model': 'phi-3-mini' + (f'-{args.layers}layers' if args.layers else ''),
                                      'pairs_per_gpu': args.pairs, 'seq_len': args.seq_len,
-                                     'parallelism': f'dp{world}', 'objective': args.objective, 'loss': args.loss},
+                                     'parallelism': f'dp{world}', 'objective': args.objective, 'loss': args.loss,
+                                     'reshard': args.reshard,
+                                     'frozen_engines': len(trainer.strategy.frozen_engines)},
                           'peak_mem_gib': round(torch.cuda.max_memory_allocated() / 2**30, 1),
                           'last_loss': float(loss)}))
     if dist.is_initialized():

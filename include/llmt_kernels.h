@@ -101,6 +101,17 @@ int llmt_attn_fwd(const void* qkv, void* out, float* lse, const int* seg_start, 
 int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc,
                   void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq, int hkv, int head_dim,
                   int64_t qkv_stride, float scale, int window, cudaStream_t stream);
+/* Same with the remaining arguments of the reference's dispatcher (ops/attention_op.py:545-551):
+ * softcap > 0: scores become softcap * tanh(score * scale / softcap); dropout_thr in [0, 255]: probabilities are
+ * dropped with p = dropout_thr / 256 and the kept ones scaled by 1 / (1 - p).  The mask is a stateless hash of
+ * (seed, head, query, key): pass the SAME softcap / dropout_thr / seed to the backward call. */
+int llmt_attn_fwd_ex(const void* qkv, void* out, float* lse, const int* seg_start, int tokens, int hq, int hkv,
+                     int head_dim, int64_t qkv_stride, float scale, int window, float softcap, int dropout_thr,
+                     uint32_t seed, cudaStream_t stream);
+int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc,
+                     void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq, int hkv, int head_dim,
+                     int64_t qkv_stride, float scale, int window, float softcap, int dropout_thr, uint32_t seed,
+                     cudaStream_t stream);
 
 /* ---- RMSNorm (src/llm_training/ops/liger_kernel/rms_norm_op.py:15-19) -------------------------------------
  * bwd scratch: dw_partial fp32 [llmt_rmsnorm_bwd_num_partials(rows), cols]. */

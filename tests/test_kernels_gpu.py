@@ -586,3 +586,78 @@ def test_direct_wgrad_accumulation_with_deferred_zeroing_matches_autograd_accumu
     assert abs(n0 - n1) < 5e-3 * max(1.0, n0)
     for a, b in zip(p0, p1):
         assert float((a - b).abs().max()) <= 2e-2 * max(1e-2, float(a.abs().max()))
+
+
+def test_bf16_mixed_trains_on_the_kernel_path():
+    """`precision: bf16-mixed` must run the same sm_100a kernels as `bf16-true` (bf16 compute copy + fp32 masters), not
+    a PyTorch fallback: the library's launch counter moves and the loss goes down."""
+    from llm_training_b200.lightning import FSDP2Strategy, Trainer
+    from llm_training_b200.lms import CLM, CLMConfig
+    from llm_training_b200.ops import _lib
+    import ctypes
+    _lib.lib().llmt_launch_count.restype = ctypes.c_ulonglong
+    torch.manual_seed(0)
+    lm = CLM(CLMConfig.model_validate(dict(
+        init_weights=True, load_weights=False,
+        model=dict(model_class='llm_training.models.Llama',
+                   model_config=dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                                     num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=512)),
+        optim=dict(optimizer_class='torch.optim.AdamW', optimizer_kwargs=dict(lr=3e-3)))))
+    trainer = Trainer(strategy=FSDP2Strategy(data_parallel_size=1), precision='bf16-mixed', logger=False,
+                      enable_progress_bar=False, enable_checkpointing=False, gradient_clip_val=1.0)
+    lm.trainer = trainer
+    trainer.lightning_module = lm
+    trainer.strategy.setup_environment(trainer)
+    assert trainer.strategy.precision_plugin.native and trainer.strategy.precision_plugin.param_dtype == torch.bfloat16
+    with trainer.strategy.model_init_context():
+        lm.configure_model()
+    trainer.strategy.setup(trainer)
+    assert all(p.dtype == torch.bfloat16 for p in lm.model.parameters())
+    assert all('master' in st and st['master'].dtype == torch.float32 for st in trainer.optimizers[0].unit_state)
+    ids = torch.randint(0, 1024, (2, 256), device=DEV)
+    batch = dict(input_ids=ids, attention_mask=torch.ones_like(ids), position_ids=torch.arange(256, device=DEV)[None],
+                 labels=ids)
+    before = _lib.lib().llmt_launch_count()
+    losses = []
+    for _ in range(6):
+        loss = trainer.strategy.training_step(batch, 0)
+        trainer.strategy.backward(loss)
+        trainer.strategy.optimizer_step(trainer.optimizers[0])
+        trainer.optimizers[0].zero_grad()
+        losses.append(float(loss))
+    assert _lib.lib().llmt_launch_count() - before > 100
+    assert losses[-1] < losses[0] - 0.1, losses
+
+
+def test_hf_causal_lm_packed_attention_hook_on_gpu():
+    """HF Llama through `HFCausalLM` with `attn_implementation: flash_attention_2`: its attention layers call the
+    in-tree packed attention kernel through HF's AttentionInterface; packed documents + pads against the sdpa path
+    with the block-diagonal 4-D mask."""
+    from transformers import LlamaConfig as HFLlamaConfig
+    from llm_training_b200.models import HFCausalLM, HFCausalLMConfig
+    from llm_training_b200.ops import _lib
+    import ctypes
+    _lib.lib().llmt_launch_count.restype = ctypes.c_ulonglong
+    hf_cfg = dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                  num_key_value_heads=2, head_dim=64)
+    torch.manual_seed(0)
+    dense = HFCausalLM(HFCausalLMConfig(hf_config=HFLlamaConfig(**hf_cfg), attn_implementation='sdpa'))
+    hooked = HFCausalLM(HFCausalLMConfig(hf_config=HFLlamaConfig(**hf_cfg), attn_implementation='flash_attention_2'))
+    hooked.load_state_dict(dense.state_dict())
+    dense, hooked = dense.to(DEV, torch.bfloat16), hooked.to(DEV, torch.bfloat16)
+    ids = torch.randint(0, 512, (2, 256), device=DEV)
+    seg = torch.ones(2, 256, dtype=torch.long, device=DEV)
+    seg[0, 100:180] = 2
+    seg[0, 180:] = 0
+    pos = torch.arange(256, device=DEV).repeat(2, 1)
+    pos[0, 100:180] = torch.arange(80, device=DEV)
+    before = _lib.lib().llmt_launch_count()
+    a = dense(input_ids=ids, attention_mask=seg, position_ids=pos).logits.float()
+    b = hooked(input_ids=ids, attention_mask=seg, position_ids=pos).logits.float()
+    assert _lib.lib().llmt_launch_count() - before >= 2          # one attention kernel per layer
+    keep = seg > 0
+    _close(b[keep], a[keep], rtol=3e-2, atol=3e-2)
+    a[keep].pow(2).mean().backward()
+    b[keep].pow(2).mean().backward()
+    for (n, p), (_, q) in zip(dense.named_parameters(), hooked.named_parameters()):
+        _close(q.grad, p.grad, rtol=5e-2, atol=5e-2 * max(1e-3, float(p.grad.float().abs().max())))
