@@ -44,8 +44,11 @@ def _run_pair(lib, rows, cols, seed):
     assert rc == 0, lib.llmt_last_error().decode()
     torch.cuda.synchronize()
     assert torch.equal(dx, dx_ref)                     # same kernel, same per-row math
-    err = (dw - dw_ref).abs().max().item()             # only the partial-sum grouping differs
-    bound = 0.15 + 3e-2 * dw_ref.abs().max().item()    # tolerance used for dw in test_kernels_gpu.py::test_rmsnorm
+    # both results are fp32 sums of the same per-row fp32 terms; only the grouping into partial rows differs
+    # (148 vs up to 592 partials), so they agree to fp32 summation-order error — far inside the bf16-level tolerance
+    # test_kernels_gpu.py::test_rmsnorm uses against the PyTorch oracle
+    err = (dw - dw_ref).abs().max().item()
+    bound = 1e-3 * max(1.0, dw_ref.abs().max().item())
     assert err <= bound, f'dw max abs err {err} > {bound}'
 
 
