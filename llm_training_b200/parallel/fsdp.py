@@ -561,7 +561,25 @@ class FlatParamEngine:
     def _alloc_grad(self, u: ShardedUnit) -> None:
         if not u.grad_live and u.with_grad:
             u._set_storage(u.flat_grad, True)
-            u.flat_grad.zero_()
+            direct = [getattr(p, '_llmt_direct_grad', False) and p.requires_grad for _, p in u.params]
+            if self.require_sync and self.world_is_cuda and any(direct):
+                # fresh storage: the weights whose first wgrad GEMM overwrites need no clearing (see zero_grad); the
+                # rest of the buffer — other parameters, alignment gaps, tail padding — does, because the
+                # reduce-scatter and the optimizer read every element of the slice
+                pos = 0
+                for (_, p), o, d in zip(u.params, u.offsets, direct):
+                    end = o + p.numel()
+                    if d:
+                        p._llmt_grad_fresh = True
+                        if o > pos:
+                            u.flat_grad[pos:o].zero_()
+                    else:
+                        u.flat_grad[pos:end].zero_()
+                    pos = end
+                if pos < u.padded_numel:
+                    u.flat_grad[pos:].zero_()
+            else:
+                u.flat_grad.zero_()
             u.grad_live = True
             u.grad_zeroed = True
 

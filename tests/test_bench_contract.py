@@ -35,9 +35,9 @@ def test_bench_honours_gpus_and_records_the_data_plane():
     out = _run('--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64', '--gpus', '2')
     assert out['n_gpus'] == 2 and out['config']['parallelism'] == 'dp2' and out['config']['global_batch'] == 2
     assert {'comm', 'reshard', 'multicast'} <= set(out['config'])
-    assert out['config']['reshard'] is False
-    out = _run('--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64', '--gpus', '2', '--reshard')
-    assert out['n_gpus'] == 2 and out['config']['reshard'] is True and 'ZeRO-3' in out['config']['sharding']
+    assert out['config']['reshard'] is True and 'ZeRO-3' in out['config']['sharding']     # the default is FSDP / ZeRO-3
+    out = _run('--model', 'llama-tiny', '--steps', '2', '--warmup', '3', '--seq-len', '64', '--gpus', '2', '--resident')
+    assert out['n_gpus'] == 2 and out['config']['reshard'] is False
 
 
 def test_bench_rejects_a_world_size_that_differs_from_gpus():

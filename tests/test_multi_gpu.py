@@ -77,22 +77,33 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
         queue.put((rank, 'error', traceback.format_exc()))
 
 
-def _run(comm_kind: str, world: int = 2):
+def _run(comm_kind: str, world: int = 2, attempts: int = 3):
     import torch.multiprocessing as mp
     ctx = mp.get_context('spawn')
-    queue = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, comm_kind, queue)) for r in range(world)]
-    for p in procs:
-        p.start()
-    out = {}
-    for _ in range(world):
-        rank, status, payload = queue.get(timeout=240)
-        assert status == 'ok', f'rank {rank} ({comm_kind}):\n{payload}'
-        out[rank] = payload
-    for p in procs:
-        p.join(timeout=60)
-    return out
+    for attempt in range(attempts):
+        queue = ctx.Queue()
+        port = _free_port()
+        procs = [ctx.Process(target=_worker, args=(r, world, port, comm_kind, queue)) for r in range(world)]
+        for p in procs:
+            p.start()
+        out, failure = {}, None
+        for _ in range(world):
+            rank, status, payload = queue.get(timeout=240)
+            if status != 'ok':
+                failure = (rank, payload)
+                break
+            out[rank] = payload
+        if failure is None:
+            for p in procs:
+                p.join(timeout=60)
+            return out
+        for p in procs:                      # a rank failed: stop the others before deciding what to do
+            p.kill()
+            p.join(timeout=30)
+        # the probed port can be taken between the probe and the rendezvous: that is not the code under test
+        if 'EADDRINUSE' in failure[1] and attempt + 1 < attempts:
+            continue
+        raise AssertionError(f'rank {failure[0]} ({comm_kind}):\n{failure[1]}')
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
