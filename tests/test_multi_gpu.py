@@ -77,18 +77,19 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
         queue.put((rank, 'error', traceback.format_exc()))
 
 
-def _run(comm_kind: str, world: int = 2, attempts: int = 3):
+def _run(comm_kind: str, world: int = 2, attempts: int = 3, worker=None, timeout: int = 240):
     import torch.multiprocessing as mp
+    worker = worker or _worker
     ctx = mp.get_context('spawn')
     for attempt in range(attempts):
         queue = ctx.Queue()
         port = _free_port()
-        procs = [ctx.Process(target=_worker, args=(r, world, port, comm_kind, queue)) for r in range(world)]
+        procs = [ctx.Process(target=worker, args=(r, world, port, comm_kind, queue)) for r in range(world)]
         for p in procs:
             p.start()
         out, failure = {}, None
         for _ in range(world):
-            rank, status, payload = queue.get(timeout=240)
+            rank, status, payload = queue.get(timeout=timeout)
             if status != 'ok':
                 failure = (rank, payload)
                 break
@@ -240,25 +241,7 @@ def _tp_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs 2 GPUs')
 def test_fused_tensor_parallel_kernels_match_nccl_path():
-    import torch.multiprocessing as mp
-
-    def run(kind):
-        ctx = mp.get_context('spawn')
-        queue = ctx.Queue()
-        port = _free_port()
-        procs = [ctx.Process(target=_tp_worker, args=(r, 2, port, kind, queue)) for r in range(2)]
-        for p in procs:
-            p.start()
-        out = {}
-        for _ in range(2):
-            rank, status, payload = queue.get(timeout=240)
-            assert status == 'ok', f'rank {rank} ({kind}):\n{payload}'
-            out[rank] = payload
-        for p in procs:
-            p.join(timeout=60)
-        return out
-
-    ref, got = run('torch'), run('nvlink')
+    ref, got = _run('torch', worker=_tp_worker), _run('nvlink', worker=_tp_worker)
     for rank in (0, 1):
         assert abs(ref[rank][0] - got[rank][0]) < 2e-2, (ref[rank][0], got[rank][0])
         for a, b in zip(ref[rank][1], got[rank][1]):
@@ -314,16 +297,6 @@ def _flag_stress_worker(rank: int, world: int, port: int, comm_kind: str, queue)
 def test_symmetric_memory_flag_protocol_stress():
     """1500 rounds of write -> flag barrier -> peer read -> barrier -> one-shot all-reduce with skewed ranks: the
     epoch flags must never let a reader run ahead of a writer."""
-    import torch.multiprocessing as mp
-    ctx = mp.get_context('spawn')
-    queue = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_flag_stress_worker, args=(r, 2, port, 'nvlink', queue)) for r in range(2)]
-    for p in procs:
-        p.start()
-    for _ in range(2):
-        rank, status, payload = queue.get(timeout=300)
-        assert status == 'ok', f'rank {rank}:\n{payload}'
+    out = _run('nvlink', worker=_flag_stress_worker, timeout=300)
+    for rank, payload in out.items():
         assert payload == 0, f'rank {rank}: {payload} stale reads / wrong sums'
-    for p in procs:
-        p.join(timeout=60)
