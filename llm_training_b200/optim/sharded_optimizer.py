@@ -190,6 +190,8 @@ class ShardedOptimizer(Optimizer):
             self.last_step_skipped = True          # overflow under fp16 loss scaling: leave weights and state alone
             return loss
         self.step_count += 1
+        for e in self.engines:
+            e._slices_dirty = True        # ZeRO-3: the next parameter gather needs one cross-rank barrier first
         max_norm = float(self.max_grad_norm) if self.max_grad_norm else 0.0
         pushed_all: dict[int, bool] = {}
         if self.fused:
@@ -221,7 +223,8 @@ class ShardedOptimizer(Optimizer):
                     u.param_shard.copy_(st['master'])
         for e in self.engines:
             if e.reshard:
-                continue                  # ZeRO-3: the slices are gathered again right before their next use
+                e._slices_dirty = True    # ZeRO-3: the slices are gathered again right before their next use; the
+                continue                  # first gather after this step carries the one cross-rank barrier
             if e.nvlink and pushed_all.get(id(e), False):
                 e.comm.barrier()          # every unit's new slice was pushed by its update kernel and has landed
             else:
@@ -319,6 +322,8 @@ class ShardedOptimizer(Optimizer):
 
     def load_state_dict(self, state_dict: dict) -> None:
         self.synchronize()
+        for e in self.engines:
+            e._slices_dirty = True
         self.step_count = int(state_dict.get('step', 0))
         for _, u, st in self._units():
             saved = state_dict['units'].get(u.name, {})

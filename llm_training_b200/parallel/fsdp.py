@@ -201,6 +201,10 @@ class FlatParamEngine:
         self.nvlink_grads = self.nvlink and (not self.reshard or getattr(self, 'grad_ring', None) is not None)
         import os
         self.fused_first_gemm = os.environ.get('LLMT_FUSED_FIRST_GEMM', '1') != '0'
+        # ZeRO-3 on NVLink: the persistent slices change only in the optimizer step (and when weights are loaded), so
+        # ONE cross-rank barrier after such a write covers every gather until the next one — a barrier per unit would
+        # couple the ranks' forward and backward passes layer by layer
+        self._slices_dirty = True
         self._forward_order: list[ShardedUnit] = []      # hooked units in the order the last forward used them
         self._norm_accumulating = False
         self.require_sync = True
@@ -483,19 +487,21 @@ class FlatParamEngine:
     def _gather_into_full(self, u: ShardedUnit) -> None:
         if self.shard_arena is not None:
             esize = u.flat_param.element_size()
+            need_barrier, self._slices_dirty = self._slices_dirty, False
             if u.head_pending:
                 # everything except the lazy groups: the ranges between them, one launch each, one barrier in front
                 pos, first = 0, True
                 spans = sorted((h['off'] * esize, (h['off'] + h['n'] * h['k']) * esize)
                                for h in u.lazy_heads.values() if h['pending'])
                 for lo, hi in spans + [(u.padded_numel * esize, u.padded_numel * esize)]:
-                    if lo > pos or first:
+                    if lo > pos or (first and need_barrier):
                         self.comm.gather_range(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize,
-                                               u.flat_param, pos, max(lo, pos), barrier=first)
+                                               u.flat_param, pos, max(lo, pos), barrier=first and need_barrier)
                         first = False
                     pos = max(pos, hi)
                 return
-            self.comm.gather_shards(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param)
+            self.comm.gather_shards(self.shard_arena, u.arena_offset * esize, u.shard_numel * esize, u.flat_param,
+                                    barrier=need_barrier)
         else:
             self.comm.all_gather_into(u.flat_param, u.param_shard)
 
@@ -700,6 +706,7 @@ class FlatParamEngine:
         broadcast): refresh the persistent owned slices.  No-op in resident mode."""
         if not self.reshard:
             return
+        self._slices_dirty = True
         for u in self.units:
             if not u.is_sharded:
                 s = u.shard_numel

@@ -122,10 +122,12 @@ class NVLinkComm(Comm):
                                                       _lib.c_int(self.size), _lib.c_i64(shard_bytes), _lib.stream()),
                    'comm_allgather_pull')
 
-    def gather_shards(self, arena: SymmetricBuffer, byte_offset: int, shard_bytes: int, full: torch.Tensor) -> None:
+    def gather_shards(self, arena: SymmetricBuffer, byte_offset: int, shard_bytes: int, full: torch.Tensor,
+                      barrier: bool = True) -> None:
         """ZeRO-3 parameter gather: ``full`` (local, not symmetric) <- every rank's slice at ``byte_offset`` of the
-        symmetric shard arena."""
-        self.barrier()                                           # every owner's slice is final
+        symmetric shard arena.  ``barrier``: the slices may have been written since the last cross-rank barrier."""
+        if barrier:
+            self.barrier()                                       # every owner's slice is final
         _lib.check(self._lib.llmt_comm_gather_shards(arena.peer_ptrs_at(byte_offset), _lib.ptr(full),
                                                      _lib.c_int(self.rank), _lib.c_int(self.size),
                                                      _lib.c_i64(shard_bytes), _lib.stream()), 'comm_gather_shards')
