@@ -17,18 +17,31 @@ __global__ void __launch_bounds__(256)
 silu_mul_fwd_kernel(const __nv_bfloat16* __restrict__ gate, const __nv_bfloat16* __restrict__ up,
                     __nv_bfloat16* __restrict__ out, int rows, int cols, int64_t in_stride,
                     int64_t out_stride) {
-  const int vec_per_row = cols >> 3;
-  const int64_t total = (int64_t)rows * vec_per_row;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / vec_per_row;
-    const int c = (int)(i - r * vec_per_row) << 3;
+  // flat grid-stride walk over 16-byte vectors, TWO vectors per operand in flight per thread; 32-bit index math
+  // (the launcher guarantees rows * cols / 8 < 2^31)
+  const uint32_t vec_per_row = (uint32_t)cols >> 3;
+  const uint32_t total = (uint32_t)rows * vec_per_row;
+  const uint32_t stride = gridDim.x * blockDim.x;
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += 2 * stride) {
+    const uint32_t i1 = i + stride;
+    const bool two = i1 < total;
+    const uint32_t r0 = i / vec_per_row, c0 = (i - r0 * vec_per_row) << 3;
+    const uint32_t r1 = two ? i1 / vec_per_row : r0, c1 = two ? (i1 - r1 * vec_per_row) << 3 : c0;
+    const bf16x8 ga = ld_bf16x8_stream(gate + (int64_t)r0 * in_stride + c0);
+    const bf16x8 ua = ld_bf16x8_stream(up + (int64_t)r0 * in_stride + c0);
+    const bf16x8 gb = ld_bf16x8_stream(gate + (int64_t)r1 * in_stride + c1);
+    const bf16x8 ub = ld_bf16x8_stream(up + (int64_t)r1 * in_stride + c1);
     float g[8], u[8], o[8];
-    unpack8(ld_bf16x8_stream(gate + r * in_stride + c), g);
-    unpack8(ld_bf16x8_stream(up + r * in_stride + c), u);
+    unpack8(ga, g); unpack8(ua, u);
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = g[j] / (1.f + __expf(-g[j])) * u[j];
-    st_bf16x8(out + r * out_stride + c, pack8(o));
+    for (int j = 0; j < 8; ++j) o[j] = __fdividef(g[j], 1.f + __expf(-g[j])) * u[j];
+    st_bf16x8(out + (int64_t)r0 * out_stride + c0, pack8(o));
+    if (two) {
+      unpack8(gb, g); unpack8(ub, u);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = __fdividef(g[j], 1.f + __expf(-g[j])) * u[j];
+      st_bf16x8(out + (int64_t)r1 * out_stride + c1, pack8(o));
+    }
   }
 }
 
@@ -191,7 +204,8 @@ extern "C" int llmt_silu_mul_fwd(const void* gate, const void* up, void* out, in
                                  int64_t in_stride, int64_t out_stride, cudaStream_t stream) {
   LLMT_REQUIRE(cols % 8 == 0 && in_stride % 8 == 0 && out_stride % 8 == 0, "silu_mul: cols/strides must be multiples of 8");
   if (rows == 0) return 0;
-  silu_mul_fwd_kernel<<<ew_grid((int64_t)rows * cols / 8, 256), 256, 0, stream>>>(
+  LLMT_REQUIRE((int64_t)rows * (cols / 8) < (1ll << 31), "silu_mul: too many elements for 32-bit vector indexing");
+  silu_mul_fwd_kernel<<<ew_grid((int64_t)rows * cols / 16, 256), 256, 0, stream>>>(
       (const __nv_bfloat16*)gate, (const __nv_bfloat16*)up, (__nv_bfloat16*)out, rows, cols, in_stride, out_stride);
   return check_launch("silu_mul_fwd");
 }

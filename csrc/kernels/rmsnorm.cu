@@ -31,19 +31,31 @@ rmsnorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __r
     const int v = threadIdx.x + i * kNormThreads;
     if (v < nvec) unpack8(ld_bf16x8(w + (size_t)v * 8), wreg[i]);
   }
-  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+  // the next row's vectors are requested before this row's reduction: one row of loads is always in flight behind the
+  // block-wide sum (the un-pipelined loop reached 49% of the HBM copy bandwidth in ncu)
+  bf16x8 nxt[MAXV];
+  auto load_row = [&](int row) {
     const __nv_bfloat16* xr = x + (size_t)row * cols;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) nxt[i] = ld_bf16x8_stream(xr + (size_t)v * 8);
+    }
+  };
+  if ((int)blockIdx.x < rows) load_row(blockIdx.x);
+  for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     float xv[MAXV][8];
     float ss = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
       const int v = threadIdx.x + i * kNormThreads;
       if (v < nvec) {
-        unpack8(ld_bf16x8_stream(xr + (size_t)v * 8), xv[i]);
+        unpack8(nxt[i], xv[i]);
 #pragma unroll
         for (int j = 0; j < 8; ++j) ss += xv[i][j] * xv[i][j];
       }
     }
+    if (row + (int)gridDim.x < rows) load_row(row + gridDim.x);
     ss = block_sum(ss, red);
     const float rstd = rsqrtf(ss / (float)cols + eps);
     if (threadIdx.x == 0 && rstd_out != nullptr) rstd_out[row] = rstd;
@@ -77,6 +89,19 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
 #pragma unroll
     for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
   }
+  bf16x8 nx[MAXV], ndy[MAXV];
+  auto load_row = [&](int row) {
+    const size_t off = (size_t)row * cols;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = threadIdx.x + i * kNormThreads;
+      if (v < nvec) {
+        nx[i] = ld_bf16x8_stream(x + off + (size_t)v * 8);
+        ndy[i] = ld_bf16x8_stream(dy + off + (size_t)v * 8);
+      }
+    }
+  };
+  if ((int)blockIdx.x < rows) load_row(blockIdx.x);
   for (int row = blockIdx.x; row < rows; row += gridDim.x) {
     const size_t off = (size_t)row * cols;
     const float rstd = rstd_in[row];
@@ -87,8 +112,8 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
       const int v = threadIdx.x + i * kNormThreads;
       if (v < nvec) {
         float dyv[8];
-        unpack8(ld_bf16x8_stream(x + off + (size_t)v * 8), xh[i]);
-        unpack8(ld_bf16x8_stream(dy + off + (size_t)v * 8), dyv);
+        unpack8(nx[i], xh[i]);
+        unpack8(ndy[i], dyv);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] *= rstd;
@@ -98,6 +123,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
         }
       }
     }
+    if (row + (int)gridDim.x < rows) load_row(row + gridDim.x);   // in flight behind the block-wide sum below
     dot = block_sum(dot, red) / (float)cols;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
