@@ -37,8 +37,10 @@ def main():
         out = packed_attention(qkv, start, end, hq, hkv, d)
         ms_f = timeit(lambda: packed_attention(qkv, start, end, hq, hkv, d))
         ms_b = timeit(lambda: torch.autograd.grad(out, qkv, dout, retain_graph=True))
+        out_det = packed_attention(qkv, start, end, hq, hkv, d, deterministic=True)
+        ms_bd = timeit(lambda: torch.autograd.grad(out_det, qkv, dout, retain_graph=True))
         r = dict(tokens=tokens, hq=hq, hkv=hkv, d=d, fwd_ms=ms_f, fwd_tflops=fl_fwd / ms_f / 1e9, bwd_ms=ms_b,
-                 bwd_tflops=2.5 * fl_fwd / ms_b / 1e9)
+                 bwd_tflops=2.5 * fl_fwd / ms_b / 1e9, bwd_deterministic_ms=ms_bd)
         try:
             from flash_attn import flash_attn_func
             q, k, v = qkv.detach().split([hq * d, hkv * d, hkv * d], dim=-1)
@@ -49,6 +51,8 @@ def main():
             r['fa2_fwd_ms'] = timeit(lambda: flash_attn_func(q, k, v, causal=True))
             do2 = dout.view(1, tokens, hq, d)
             r['fa2_bwd_ms'] = timeit(lambda: torch.autograd.grad(o2, (q, k, v), do2, retain_graph=True))
+            o2d = flash_attn_func(q, k, v, causal=True, deterministic=True)
+            r['fa2_bwd_deterministic_ms'] = timeit(lambda: torch.autograd.grad(o2d, (q, k, v), do2, retain_graph=True))
             r['max_diff_vs_fa2'] = (o2.view(tokens, -1).float() - out.float()).abs().max().item()
             ours = torch.autograd.grad(out, qkv, dout, retain_graph=True)[0]
             theirs = torch.cat([t.reshape(tokens, -1) for t in torch.autograd.grad(o2, (q, k, v), do2, retain_graph=True)],

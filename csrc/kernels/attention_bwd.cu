@@ -108,6 +108,10 @@ struct BwdParams {
   float softcap_in, softcap_out;   // scale / softcap, softcap * log2(e); 0 = no soft-capping
   uint32_t drop_thr, seed;         // dropped when the element's random byte < drop_thr; 0 = no dropout
   float drop_scale;                // 1 / (1 - p)
+  // deterministic mode: dq_order[h * n_qblk + qb] = kv block whose dQ contribution to (head h, q block qb) is next;
+  // zero on entry.  nullptr = unordered reduce-adds.
+  int* dq_order;
+  int n_qblk;
 };
 
 __device__ __forceinline__ float bwd_exp2(float x) {
@@ -734,6 +738,21 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     float tv[32];                                        // soft-capping only: tanh(s * scale / cap) of the same step
     int a_h = g * G, a_qi = 0;                           // (head, q block) of the step whose P^T / dS^T is being built
 
+    // Deterministic mode: the kv blocks that touch one dQ tile add to it in ascending order.  The contributors of a
+    // q block are a contiguous run of kv blocks (q_hi is non-decreasing in the kv block), so this CTA waits for
+    // "next = my kv block" on every q block its predecessor also covers and publishes "next = mine + 1" once its own
+    // reduce-add has COMPLETED (wait_group without .read).  CTAs are dispatched in block order and a CTA only ever
+    // waits for a lower block index, so the wait cannot deadlock.
+    int prev_hi_blk = -1;                                // last q block of kv block blockIdx.y - 1
+    int* pend_order = nullptr;                           // thread 0: counter to publish after the reduce in flight
+    if constexpr (kExtras) {
+      if (p.dq_order != nullptr && blockIdx.y > 0) {
+        int q_hi_prev = p.seg_end[k0 - 1] - 1;
+        if (p.window > 0) q_hi_prev = min(q_hi_prev, k0 - 1 + p.window - 1);
+        prev_hi_blk = min(q_hi_prev, p.tokens - 1) / kBwdQ;
+      }
+    }
+
     meta_fetch();
     meta_store(0);
     if (n_total > 1) { meta_fetch(); meta_store(1); }
@@ -864,7 +883,18 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
           tmem_ld_wait();
           tc_fence_before();
           mbar_arrive(dq_empty);
-          if (threadIdx.x == 0) tma_store_wait_read<0>();   // previous reduce has finished reading the staging tile
+          if (threadIdx.x == 0) {
+            bool published = false;
+            if constexpr (kExtras) {
+              if (pend_order != nullptr) {
+                tma_store_wait<0>();                        // previous reduce-add has been performed in memory
+                st_release_gpu_s32(pend_order, (int)blockIdx.y + 1);
+                pend_order = nullptr;
+                published = true;
+              }
+            }
+            if (!published) tma_store_wait_read<0>();       // previous reduce has finished reading the staging tile
+          }
         }
         asm volatile("bar.sync 2, 256;" ::: "memory");
         if (j >= 0) {
@@ -877,6 +907,16 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         asm volatile("bar.sync 2, 256;" ::: "memory");
         if (j >= 0) {
           if (threadIdx.x == 0) {
+            if constexpr (kExtras) {
+              if (p.dq_order != nullptr) {
+                int* ctr = p.dq_order + (size_t)d_h * p.n_qblk + (i_lo + d_qi);
+                if (i_lo + d_qi <= prev_hi_blk) {
+                  while (ld_acquire_gpu_s32(ctr) != (int)blockIdx.y) __nanosleep(64);
+                  fence_proxy_async_all();                  // the earlier blocks' adds precede this async-proxy add
+                }
+                pend_order = ctr;
+              }
+            }
             tma_reduce_add_2d(&tmDQ, sbase + C::kDQOff, d_h * p.head_dim, (i_lo + d_qi) * kBwdQ);
             tma_store_commit();
           }
@@ -944,7 +984,12 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
         }
       }
     }
-    if (threadIdx.x == 0) tma_store_wait<0>();
+    if (threadIdx.x == 0) {
+      tma_store_wait<0>();
+      if constexpr (kExtras) {
+        if (pend_order != nullptr) st_release_gpu_s32(pend_order, (int)blockIdx.y + 1);
+      }
+    }
 
     // ---- dK (x softmax scale) / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
     mbar_wait(acc_done, 0);
@@ -1003,7 +1048,7 @@ using namespace llmt::attn;
 extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                                 float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
                                 int hkv, int head_dim, int64_t qkv_stride, float scale, int window, float softcap,
-                                int dropout_thr, uint32_t seed, cudaStream_t stream) {
+                                int dropout_thr, uint32_t seed, int* dq_order, cudaStream_t stream) {
   LLMT_REQUIRE(tokens > 0 && hq > 0 && hkv > 0 && hq % hkv == 0, "attn_bwd: bad head counts %d/%d", hq, hkv);
   LLMT_REQUIRE(head_dim % 16 == 0 && head_dim <= 128, "attn_bwd: head_dim %d unsupported", head_dim);
   LLMT_REQUIRE(qkv_stride % 8 == 0, "attn_bwd: qkv stride must be a multiple of 8");
@@ -1038,12 +1083,19 @@ extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* do
   p.drop_thr = (uint32_t)dropout_thr;
   p.seed = seed;
   p.drop_scale = 256.f / (256.f - (float)dropout_thr);
-  const bool extras = softcap > 0.f || dropout_thr > 0;
+  // dq_order != nullptr: bit-reproducible dQ (int scratch of hq * ceil(tokens / 64) entries, zeroed here)
+  p.dq_order = dq_order;
+  p.n_qblk = (tokens + kBwdQ - 1) / kBwdQ;
+  if (dq_order != nullptr) {
+    cudaError_t e = cudaMemsetAsync(dq_order, 0, sizeof(int) * (size_t)hq * p.n_qblk, stream);
+    LLMT_REQUIRE(e == cudaSuccess, "attn_bwd: clearing the dQ order counters failed: %s", cudaGetErrorString(e));
+  }
+  const bool extras = softcap > 0.f || dropout_thr > 0 || dq_order != nullptr;
   dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
   // LLMT_ATTN_BWD=ss selects the first-generation kernel (every MMA operand in shared memory); default: P^T / dS^T in
   // tensor memory
   static const bool use_ss = [] { const char* e = getenv("LLMT_ATTN_BWD"); return e && e[0] == 's'; }();
-  LLMT_REQUIRE(!(use_ss && extras), "attn_bwd: LLMT_ATTN_BWD=ss has no soft-capping / dropout");
+  LLMT_REQUIRE(!(use_ss && extras), "attn_bwd: LLMT_ATTN_BWD=ss has no soft-capping / dropout / deterministic mode");
   if (use_ss) {
     static bool configured[kMaxDevices] = {};
     rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
@@ -1078,5 +1130,5 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
                              int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
                              cudaStream_t stream) {
   return llmt_attn_bwd_ex(qkv, out, dout, lse, delta, dq_acc, dqkv, seg_start, seg_end, tokens, hq, hkv, head_dim,
-                          qkv_stride, scale, window, 0.f, 0, 0u, stream);
+                          qkv_stride, scale, window, 0.f, 0, 0u, nullptr, stream);
 }

@@ -190,6 +190,31 @@ embedding_bwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __res
   }
 }
 
+// Order-independent variant: the caller passes the token ids sorted (stable) with the permutation that sorted them.
+// The CTA of sorted position i owns the whole run of equal ids that STARTS at i: it sums the run's dout rows in
+// fp32, in run order, and writes the bf16 row once.  No atomics, so the result does not depend on scheduling; rows
+// no token selects are left as the caller initialised them (zero).
+__global__ void __launch_bounds__(256)
+embedding_bwd_sorted_kernel(const int64_t* __restrict__ sorted_ids, const int64_t* __restrict__ perm,
+                            const __nv_bfloat16* __restrict__ dout, __nv_bfloat16* __restrict__ dweight, int tokens,
+                            int dim, int vocab, int64_t padding_idx) {
+  const int i = blockIdx.x;
+  const int64_t id = sorted_ids[i];
+  if (id < 0 || id >= vocab || id == padding_idx) return;
+  if (i > 0 && sorted_ids[i - 1] == id) return;          // not the first token of its run
+  for (int v = threadIdx.x; v < (dim >> 3); v += blockDim.x) {
+    float acc[8];
+    unpack8(ld_bf16x8(dout + perm[i] * dim + v * 8), acc);
+    for (int j = i + 1; j < tokens && sorted_ids[j] == id; ++j) {
+      float f[8];
+      unpack8(ld_bf16x8(dout + perm[j] * dim + v * 8), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) acc[e] += f[e];
+    }
+    st_bf16x8(dweight + id * dim + v * 8, pack8(acc));
+  }
+}
+
 static int ew_grid(int64_t work_items, int threads) {
   int64_t blocks = (work_items + threads - 1) / threads;
   const int64_t cap = (int64_t)num_sms() * 8;
@@ -253,4 +278,17 @@ extern "C" int llmt_embedding_bwd(const int64_t* ids, const void* dout, void* dw
                                                                   (__nv_bfloat16*)dweight, tokens, dim, vocab,
                                                                   padding_idx);
   return check_launch("embedding_bwd");
+}
+
+// dweight (bf16 [vocab, dim]) is fully overwritten: zero, then one row per distinct token id.
+extern "C" int llmt_embedding_bwd_sorted(const int64_t* sorted_ids, const int64_t* perm, const void* dout,
+                                         void* dweight, int tokens, int dim, int vocab, int64_t padding_idx,
+                                         cudaStream_t stream) {
+  LLMT_REQUIRE(dim % 8 == 0, "embedding_bwd: dim must be a multiple of 8");
+  cudaError_t e = cudaMemsetAsync(dweight, 0, sizeof(__nv_bfloat16) * (size_t)vocab * dim, stream);
+  LLMT_REQUIRE(e == cudaSuccess, "embedding_bwd: clearing the gradient failed: %s", cudaGetErrorString(e));
+  if (tokens == 0) return 0;
+  embedding_bwd_sorted_kernel<<<tokens, 256, 0, stream>>>(sorted_ids, perm, (const __nv_bfloat16*)dout,
+                                                          (__nv_bfloat16*)dweight, tokens, dim, vocab, padding_idx);
+  return check_launch("embedding_bwd_sorted");
 }

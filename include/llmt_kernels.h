@@ -111,7 +111,10 @@ int llmt_attn_fwd_ex(const void* qkv, void* out, float* lse, const int* seg_star
 int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc,
                      void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq, int hkv, int head_dim,
                      int64_t qkv_stride, float scale, int window, float softcap, int dropout_thr, uint32_t seed,
-                     cudaStream_t stream);
+                     int* dq_order, cudaStream_t stream);
+/* dq_order: NULL, or an int scratch of hq * ceil(tokens / 64) entries: the kv blocks then add their dQ contributions
+ * in ascending order, which makes the backward bit-reproducible (the reference's `deterministic` flag,
+ * src/llm_training/ops/attention_op.py:551,590-592). */
 
 /* ---- RMSNorm (src/llm_training/ops/liger_kernel/rms_norm_op.py:15-19) -------------------------------------
  * bwd scratch: dw_partial fp32 [llmt_rmsnorm_bwd_num_partials(rows), cols]. */
@@ -145,6 +148,9 @@ int llmt_embedding_fwd(const int64_t* ids, const void* weight, void* out, const 
                        int dim, int vocab, uint64_t seed, cudaStream_t stream);
 int llmt_embedding_bwd(const int64_t* ids, const void* dout, void* dweight, int tokens, int dim, int vocab,
                        int64_t padding_idx, int grad_is_fp32, cudaStream_t stream);
+/* Scheduling-independent variant (no atomics): ids sorted (stable) + the permutation; dweight bf16, fully overwritten. */
+int llmt_embedding_bwd_sorted(const int64_t* sorted_ids, const int64_t* perm, const void* dout, void* dweight,
+                              int tokens, int dim, int vocab, int64_t padding_idx, cudaStream_t stream);
 
 /* ---- cross-entropy / token log-prob on bf16 logits (ops/liger_kernel/cross_entropy_op.py:29-33,
  *      lms/dpo/dpo.py:110-114) ---------------------------------------------------------------------------- */

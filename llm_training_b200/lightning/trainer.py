@@ -67,7 +67,7 @@ class Trainer:
                  limit_train_batches: int | float | None = None, limit_val_batches: int | float | None = None,
                  log_every_n_steps: int = 50, enable_checkpointing: bool = True, enable_progress_bar: bool = True,
                  default_root_dir: str | None = None, num_sanity_val_steps: int = 0,
-                 enable_model_summary: bool = False, deterministic: bool | None = None, benchmark: bool | None = None,
+                 enable_model_summary: bool = False, deterministic: bool | str | None = None, benchmark: bool | None = None,
                  use_distributed_sampler: bool = True, **unused: Any) -> None:
         if unused:
             logger_ = logging.getLogger(__name__)
@@ -110,6 +110,15 @@ class Trainer:
         self.log_every_n_steps = max(1, log_every_n_steps)
         self.default_root_dir = default_root_dir or os.getcwd()
         self.use_distributed_sampler = use_distributed_sampler
+        # Lightning semantics: True -> torch.use_deterministic_algorithms(True), 'warn' -> warn_only.  The in-tree
+        # kernels read the same switch: attention backward orders its dQ reduce-adds, the gradient reduce-scatter sums
+        # the ranks in rank order instead of inside the switch; everything else is order-independent by construction.
+        self.deterministic = deterministic
+        if deterministic:
+            os.environ.setdefault('CUBLAS_WORKSPACE_CONFIG', ':4096:8')
+            torch.use_deterministic_algorithms(True, warn_only=(deterministic == 'warn'))
+        if benchmark is not None:
+            torch.backends.cudnn.benchmark = bool(benchmark)
 
         self.fit_loop = FitLoop()
         self.lightning_module: LightningModule | None = None

@@ -7,6 +7,7 @@ packed-sequence mask (:286-314), segment ids -> cu_seqlens (:375-412), ``flash_a
 """
 import ctypes
 import math
+import os
 
 import torch
 
@@ -18,7 +19,8 @@ from .segments import segment_bounds
 class _PackedAttentionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.Tensor, hq: int, hkv: int,
-                head_dim: int, scale: float, window: int, softcap: float, drop_thr: int, seed: int) -> torch.Tensor:
+                head_dim: int, scale: float, window: int, softcap: float, drop_thr: int, seed: int,
+                deterministic: bool = False) -> torch.Tensor:
         L = _lib.lib()
         tokens = qkv.shape[0]
         out = torch.empty((tokens, hq * head_dim), dtype=qkv.dtype, device=qkv.device)
@@ -29,13 +31,13 @@ class _PackedAttentionFn(torch.autograd.Function):
                                       _lib.c_f32(softcap), _lib.c_int(drop_thr), ctypes.c_uint32(seed),
                                       _lib.stream()), 'attn_fwd')
         ctx.save_for_backward(qkv, out, lse, seg_start, seg_end)
-        ctx.meta = (hq, hkv, head_dim, scale, window, softcap, drop_thr, seed)
+        ctx.meta = (hq, hkv, head_dim, scale, window, softcap, drop_thr, seed, deterministic)
         return out
 
     @staticmethod
     def backward(ctx, dout: torch.Tensor):
         qkv, out, lse, seg_start, seg_end = ctx.saved_tensors
-        hq, hkv, head_dim, scale, window, softcap, drop_thr, seed = ctx.meta
+        hq, hkv, head_dim, scale, window, softcap, drop_thr, seed, deterministic = ctx.meta
         L = _lib.lib()
         tokens = qkv.shape[0]
         dout = dout.contiguous()
@@ -43,13 +45,23 @@ class _PackedAttentionFn(torch.autograd.Function):
         delta = torch.empty((hq, tokens), dtype=torch.float32, device=qkv.device)
         # fp32 dQ accumulator [T, Hq*D] (scratch), converted into dqkv by the kernel's final pass
         dq_acc = torch.zeros((tokens, hq * head_dim), dtype=torch.float32, device=qkv.device)
+        # deterministic: per (head, 64-query block) turn counters, so the kv blocks add into dq_acc in a fixed order
+        order = torch.empty(hq * ((tokens + 63) // 64), dtype=torch.int32, device=qkv.device) if deterministic else None
         _lib.check(L.llmt_attn_bwd_ex(_lib.ptr(qkv), _lib.ptr(out), _lib.ptr(dout), _lib.ptr(lse), _lib.ptr(delta),
                                       _lib.ptr(dq_acc), _lib.ptr(dqkv), _lib.ptr(seg_start), _lib.ptr(seg_end),
                                       _lib.c_int(tokens), _lib.c_int(hq), _lib.c_int(hkv), _lib.c_int(head_dim),
                                       _lib.c_i64(qkv.stride(0)), _lib.c_f32(scale), _lib.c_int(window),
                                       _lib.c_f32(softcap), _lib.c_int(drop_thr), ctypes.c_uint32(seed),
+                                      _lib.ptr(order) if deterministic else ctypes.c_void_p(0),
                                       _lib.stream()), 'attn_bwd')
-        return (dqkv,) + (None,) * 10
+        return (dqkv,) + (None,) * 11
+
+
+def deterministic_default() -> bool:
+    """The reference reads ``FLASH_ATTENTION_DETERMINISTIC=1`` when the caller passes ``deterministic=None``
+    (attention_op.py:590-591); ``torch.use_deterministic_algorithms(True)`` (what ``Trainer(deterministic=True)`` sets)
+    asks for the same thing."""
+    return os.environ.get('FLASH_ATTENTION_DETERMINISTIC', '0') == '1' or torch.are_deterministic_algorithms_enabled()
 
 
 def dropout_threshold(dropout_p: float) -> int:
@@ -64,7 +76,7 @@ def dropout_threshold(dropout_p: float) -> int:
 def packed_attention(qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.Tensor, num_heads: int,
                      num_kv_heads: int, head_dim: int, scale: float | None = None,
                      window: int | None = None, dropout_p: float = 0.0, softcap: float = 0.0,
-                     seed: int | None = None) -> torch.Tensor:
+                     seed: int | None = None, deterministic: bool | None = None) -> torch.Tensor:
     """Causal attention over a packed token stream.
 
     ``qkv`` is ``[T, (Hq + 2*Hkv) * D]`` laid out ``q heads | k heads | v heads`` per row (the output
@@ -74,7 +86,9 @@ def packed_attention(qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.
     attention_op.py:160-161,588).  ``softcap`` > 0 replaces the scaled scores by ``softcap * tanh(score / softcap)``;
     ``dropout_p`` drops attention probabilities (the caller passes 0 outside training) with a mask that is a pure
     function of ``(seed, head, query, key)``, regenerated by the backward kernel — the arguments of the reference's
-    dispatcher (attention_op.py:545-551).  Returns ``[T, Hq*D]``.
+    dispatcher (attention_op.py:545-551).  ``deterministic`` (default: ``deterministic_default()``) makes the backward
+    bit-reproducible: the kv blocks add their dQ contributions in ascending order instead of in arrival order (the
+    forward, dK and dV are reproducible either way).  Returns ``[T, Hq*D]``.
     """
     scale = (1.0 / math.sqrt(head_dim)) if scale is None else scale
     w = int(window) if window else 0
@@ -85,7 +99,8 @@ def packed_attention(qkv: torch.Tensor, seg_start: torch.Tensor, seg_end: torch.
     if _lib.use_kernels(qkv):
         # the kernels count the visible keys INCLUDING the query's own position
         return _PackedAttentionFn.apply(qkv.contiguous(), seg_start, seg_end, num_heads, num_kv_heads, head_dim,
-                                        scale, w + 1 if w else 0, float(softcap or 0.0), thr, seed)
+                                        scale, w + 1 if w else 0, float(softcap or 0.0), thr, seed,
+                                        deterministic_default() if deterministic is None else bool(deterministic))
     t = qkv.shape[0]
     q, k, v = qkv.split([num_heads * head_dim, num_kv_heads * head_dim, num_kv_heads * head_dim], dim=-1)
     keep = dropout_keep_mask(seed, num_heads, t, thr, qkv.device) if thr else None
@@ -201,7 +216,8 @@ def prepare_fa2_from_position_ids(query: torch.Tensor, key: torch.Tensor, value:
 def flash_attention_forward(query_states: torch.Tensor, key_states: torch.Tensor, value_states: torch.Tensor,
                             attention_mask: torch.Tensor | None, query_length: int, is_causal: bool = True,
                             dropout: float = 0.0, softmax_scale: float | None = None,
-                            sliding_window: int | None = None, softcap: float | None = None, **_) -> torch.Tensor:
+                            sliding_window: int | None = None, softcap: float | None = None,
+                            deterministic: bool | None = None, **_) -> torch.Tensor:
     """Reference-compatible entry point: q/k/v ``[B, S, H, D]``, ``attention_mask [B, S]`` of segment ids.
     Routes to the packed kernel; segment ids are always honoured (fixes SURVEY Appendix B2)."""
     assert is_causal, 'only causal attention is implemented'
@@ -211,5 +227,5 @@ def flash_attention_forward(query_states: torch.Tensor, key_states: torch.Tensor
     qkv = torch.cat((query_states.reshape(bsz * seq, hq * d), key_states.reshape(bsz * seq, hkv * d),
                      value_states.reshape(bsz * seq, hkv * d)), dim=-1)
     out = packed_attention(qkv, start, end, hq, hkv, d, softmax_scale, sliding_window, dropout_p=dropout,
-                           softcap=softcap or 0.0)
+                           softcap=softcap or 0.0, deterministic=deterministic)
     return out.view(bsz, seq, hq, d)

@@ -42,12 +42,15 @@ class _EmbeddingFn(torch.autograd.Function):
         (flat,) = ctx.saved_tensors
         vocab, dim, padding_idx, wdtype = ctx.meta
         d2 = dout.reshape(-1, dim).contiguous()
-        dw = torch.zeros((vocab, dim), dtype=torch.float32, device=dout.device)
-        _lib.check(_lib.lib().llmt_embedding_bwd(_lib.ptr(flat), _lib.ptr(d2), _lib.ptr(dw),
-                                                 _lib.c_int(flat.numel()), _lib.c_int(dim), _lib.c_int(vocab),
-                                                 _lib.c_i64(padding_idx), _lib.c_int(1), _lib.stream()),
+        # Tokens sorted by id: every distinct id's rows are summed in fp32 by one CTA, in a fixed order, and written
+        # once as bf16 — no atomics (reproducible), no fp32 [vocab, dim] scratch and no conversion pass.
+        sorted_ids, perm = torch.sort(flat, stable=True)
+        dw = torch.empty((vocab, dim), dtype=wdtype, device=dout.device)
+        _lib.check(_lib.lib().llmt_embedding_bwd_sorted(_lib.ptr(sorted_ids), _lib.ptr(perm), _lib.ptr(d2),
+                                                        _lib.ptr(dw), _lib.c_int(flat.numel()), _lib.c_int(dim),
+                                                        _lib.c_int(vocab), _lib.c_i64(padding_idx), _lib.stream()),
                    'embedding_bwd')
-        return None, dw.to(wdtype), None, None, None
+        return None, dw, None, None, None
 
 
 def embedding(ids: torch.Tensor, weight: torch.Tensor, padding_idx: int | None = None,

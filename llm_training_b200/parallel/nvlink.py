@@ -159,7 +159,9 @@ class NVLinkComm(Comm):
     def reduce_scatter_sumsq(self, arena: SymmetricBuffer, byte_offset: int, shard_numel: int, out_shard: torch.Tensor,
                              norm_sq: torch.Tensor, accumulate_norm: bool) -> None:
         self.barrier()                                           # every rank finished writing this unit's grads
-        if self.use_multimem_rs and arena.multicast_ptr and out_shard.dtype == torch.bfloat16:
+        # the switch's summation order is not specified: deterministic mode sums the ranks' copies in rank order
+        if (self.use_multimem_rs and arena.multicast_ptr and out_shard.dtype == torch.bfloat16
+                and not torch.are_deterministic_algorithms_enabled()):
             # one multimem.ld_reduce per 16 bytes: the NVSwitch sums every rank's copy, this GPU receives 1/world of
             # what the pull version reads
             self.last_rs_kind = 'multimem'

@@ -661,3 +661,112 @@ def test_hf_causal_lm_packed_attention_hook_on_gpu():
     b[keep].pow(2).mean().backward()
     for (n, p), (_, q) in zip(dense.named_parameters(), hooked.named_parameters()):
         _close(q.grad, p.grad, rtol=5e-2, atol=5e-2 * max(1e-3, float(p.grad.float().abs().max())))
+
+
+def _docs_bounds(doc_lens, tokens):
+    s, e, pos = [], [], 0
+    for n in doc_lens:
+        s += [pos] * n
+        e += [pos + n] * n
+        pos += n
+    assert pos == tokens
+    return (torch.tensor(s, dtype=torch.int32, device=DEV), torch.tensor(e, dtype=torch.int32, device=DEV))
+
+
+@pytest.mark.parametrize('tokens,hq,hkv,doc_lens,window', [
+    (4096, 8, 2, None, None),                            # dense causal: every kv block waits for its predecessor
+    (4096, 4, 1, [1000, 72, 1500, 1524], None),          # documents that end inside a kv block
+    (4096, 4, 2, [3000, 1096], 200),                     # sliding window: short runs of contributors
+    (1000, 2, 1, None, None),                            # token count that is not a multiple of the tiles
+])
+def test_attention_backward_deterministic_mode(tokens, hq, hkv, doc_lens, window):
+    """`deterministic=True` (the reference dispatcher's flag, ops/attention_op.py:551,590-592): the kv blocks add their
+    dQ contributions in ascending order, so repeated backward passes are bit-identical, and the result still matches
+    the unordered kernel to rounding (and through it the fp32 oracle of the tests above)."""
+    from llm_training_b200.ops.attention_op import packed_attention
+    d = 128
+    g = torch.Generator(device=DEV).manual_seed(tokens + hq)
+    qkv = (torch.randn(tokens, (hq + 2 * hkv) * d, device=DEV, generator=g) * 0.7).bfloat16()
+    if doc_lens is None:
+        start = torch.zeros(tokens, dtype=torch.int32, device=DEV)
+        end = torch.full((tokens,), tokens, dtype=torch.int32, device=DEV)
+    else:
+        start, end = _docs_bounds(doc_lens, tokens)
+    dout = torch.randn(tokens, hq * d, device=DEV, generator=g).bfloat16()
+
+    def grads(deterministic):
+        x = qkv.clone().requires_grad_()
+        packed_attention(x, start, end, hq, hkv, d, None, window, deterministic=deterministic).backward(dout)
+        return x.grad
+
+    first = grads(True)
+    for _ in range(4):
+        assert torch.equal(grads(True), first), 'deterministic backward changed between identical calls'
+    free = grads(False).float()
+    err = (first.float() - free).abs()
+    assert (err <= 2.0 ** -7 * free.abs() + 1e-3).all(), f'ordered vs unordered dQ: {err.max().item()}'
+
+
+def test_attention_deterministic_mode_follows_the_global_switches(monkeypatch):
+    from llm_training_b200.ops import attention_op
+    assert attention_op.deterministic_default() is False
+    monkeypatch.setenv('FLASH_ATTENTION_DETERMINISTIC', '1')
+    assert attention_op.deterministic_default() is True
+    monkeypatch.delenv('FLASH_ATTENTION_DETERMINISTIC')
+    torch.use_deterministic_algorithms(True)
+    try:
+        assert attention_op.deterministic_default() is True
+    finally:
+        torch.use_deterministic_algorithms(False)
+
+
+def test_embedding_backward_is_order_independent_and_exact():
+    """Many tokens share few ids: each id's rows are summed in fp32 by one CTA in sorted order (no atomics), so the
+    gradient is bit-identical across calls and equals the fp32 index_add rounded once to bf16."""
+    g = torch.Generator(device=DEV).manual_seed(11)
+    vocab, dim, pad = 64, 512, 3
+    w = torch.randn(vocab, dim, device=DEV, generator=g).bfloat16().requires_grad_()
+    ids = torch.randint(0, vocab, (4, 2048), device=DEV, generator=g)
+    dy = torch.randn(4, 2048, dim, device=DEV, generator=g).bfloat16()
+    runs = []
+    for _ in range(3):
+        w.grad = None
+        embedding(ids, w, padding_idx=pad).backward(dy)
+        runs.append(w.grad.clone())
+    assert torch.equal(runs[0], runs[1]) and torch.equal(runs[0], runs[2])
+    expect = torch.zeros(vocab, dim, device=DEV)
+    flat = ids.reshape(-1)
+    live = flat != pad
+    expect.index_add_(0, flat[live], dy.reshape(-1, dim).float()[live])
+    assert runs[0][pad].abs().max().item() == 0
+    err = (runs[0].float() - expect).abs()
+    assert (err <= 2.0 ** -8 * expect.abs() + 1e-4).all(), err.max().item()      # fp32 sums, one bf16 rounding
+
+
+def test_training_step_is_bit_reproducible_in_deterministic_mode():
+    """Two identical forward + backward passes of the model under torch.use_deterministic_algorithms(True) (what
+    `Trainer(deterministic=True)` sets) give bit-identical gradients for every parameter."""
+    from llm_training_b200.models import Llama, LlamaConfig
+    from llm_training_b200.ops import fused_linear_cross_entropy, shift_labels
+    torch.manual_seed(0)
+    cfg = LlamaConfig(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
+                      num_attention_heads=4, num_key_value_heads=2, attn_implementation='flash_attention_2')
+    model = Llama(cfg).to(DEV, torch.bfloat16)
+    ids = torch.randint(0, 64, (2, 1024), device=DEV)          # few distinct ids: the embedding rows collide
+    mask = torch.ones_like(ids)
+    mask[0, 700:] = 2
+    labels = shift_labels(ids).flatten()
+
+    def run():
+        model.zero_grad(set_to_none=True)
+        out = model(input_ids=ids, attention_mask=mask, skip_logits=True)
+        fused_linear_cross_entropy(out.normed_hidden_states, model.lm_head.weight, labels).backward()
+        return [p.grad.clone() for p in model.parameters()]
+
+    torch.use_deterministic_algorithms(True)
+    try:
+        a, b = run(), run()
+    finally:
+        torch.use_deterministic_algorithms(False)
+    for (name, _), x, y in zip(model.named_parameters(), a, b):
+        assert torch.equal(x, y), f'{name}: gradient differs between two identical deterministic passes'
