@@ -45,18 +45,21 @@ silu_mul_fwd_kernel(const __nv_bfloat16* __restrict__ gate, const __nv_bfloat16*
   }
 }
 
+// kAct: also write act = silu(gate) * up (contiguous [rows, cols]) — the recomputed input of the down projection's
+// wgrad GEMM — in the same pass over gate / up, instead of a second kernel that reads them again.
+template <bool kAct>
 __global__ void __launch_bounds__(256)
 silu_mul_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ gate,
                     const __nv_bfloat16* __restrict__ up, __nv_bfloat16* __restrict__ dgate,
-                    __nv_bfloat16* __restrict__ dup, int rows, int cols, int64_t in_stride,
-                    int64_t dout_stride, int64_t dgu_stride) {
+                    __nv_bfloat16* __restrict__ dup, __nv_bfloat16* __restrict__ act, int rows, int cols,
+                    int64_t in_stride, int64_t dout_stride, int64_t dgu_stride) {
   const int vec_per_row = cols >> 3;
   const int64_t total = (int64_t)rows * vec_per_row;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / vec_per_row;
     const int c = (int)(i - r * vec_per_row) << 3;
-    float g[8], u[8], d[8], dg[8], du[8];
+    float g[8], u[8], d[8], dg[8], du[8], a[8];
     unpack8(ld_bf16x8_stream(gate + r * in_stride + c), g);
     unpack8(ld_bf16x8_stream(up + r * in_stride + c), u);
     unpack8(ld_bf16x8_stream(dout + r * dout_stride + c), d);
@@ -66,9 +69,11 @@ silu_mul_bwd_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16*
       const float silu = g[j] * sig;
       du[j] = d[j] * silu;
       dg[j] = d[j] * u[j] * sig * (1.f + g[j] * (1.f - sig));
+      if constexpr (kAct) a[j] = __fdividef(g[j], 1.f + __expf(-g[j])) * u[j];   // bit-identical to the forward kernel
     }
     st_bf16x8(dgate + r * dgu_stride + c, pack8(dg));
     st_bf16x8(dup + r * dgu_stride + c, pack8(du));
+    if constexpr (kAct) st_bf16x8(act + r * (int64_t)cols + c, pack8(a));
   }
 }
 
@@ -241,10 +246,24 @@ extern "C" int llmt_silu_mul_bwd(const void* dout, const void* gate, const void*
   LLMT_REQUIRE(cols % 8 == 0 && in_stride % 8 == 0 && dout_stride % 8 == 0 && dgu_stride % 8 == 0,
                "silu_mul_bwd: cols/strides must be multiples of 8");
   if (rows == 0) return 0;
-  silu_mul_bwd_kernel<<<ew_grid((int64_t)rows * cols / 8, 256), 256, 0, stream>>>(
+  silu_mul_bwd_kernel<false><<<ew_grid((int64_t)rows * cols / 8, 256), 256, 0, stream>>>(
       (const __nv_bfloat16*)dout, (const __nv_bfloat16*)gate, (const __nv_bfloat16*)up, (__nv_bfloat16*)dgate,
-      (__nv_bfloat16*)dup, rows, cols, in_stride, dout_stride, dgu_stride);
+      (__nv_bfloat16*)dup, nullptr, rows, cols, in_stride, dout_stride, dgu_stride);
   return check_launch("silu_mul_bwd");
+}
+
+// Backward of silu(gate) * up that ALSO returns the forward product act = silu(gate) * up (contiguous [rows, cols]):
+// callers that recompute act for the down projection's wgrad get it from the pass that already reads gate / up.
+extern "C" int llmt_silu_mul_bwd_act(const void* dout, const void* gate, const void* up, void* dgate, void* dup,
+                                     void* act, int rows, int cols, int64_t in_stride, int64_t dout_stride,
+                                     int64_t dgu_stride, cudaStream_t stream) {
+  LLMT_REQUIRE(cols % 8 == 0 && in_stride % 8 == 0 && dout_stride % 8 == 0 && dgu_stride % 8 == 0,
+               "silu_mul_bwd_act: cols/strides must be multiples of 8");
+  if (rows == 0) return 0;
+  silu_mul_bwd_kernel<true><<<ew_grid((int64_t)rows * cols / 8, 256), 256, 0, stream>>>(
+      (const __nv_bfloat16*)dout, (const __nv_bfloat16*)gate, (const __nv_bfloat16*)up, (__nv_bfloat16*)dgate,
+      (__nv_bfloat16*)dup, (__nv_bfloat16*)act, rows, cols, in_stride, dout_stride, dgu_stride);
+  return check_launch("silu_mul_bwd_act");
 }
 
 extern "C" int llmt_rope_inplace(void* x, const int* pos, const float* cos_t, const float* sin_t, int tokens,

@@ -77,6 +77,7 @@ template <int MAXV>
 __global__ void __launch_bounds__(kNormThreads)
 rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                    const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd_in,
+                   const __nv_bfloat16* __restrict__ dres,      // nullable: gradient of the residual branch, added to dx
                    __nv_bfloat16* __restrict__ dx, float* __restrict__ dw_partial, int rows, int cols) {
   __shared__ float red[32];
   const int nvec = cols >> 3;
@@ -89,7 +90,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
 #pragma unroll
     for (int j = 0; j < 8; ++j) dwacc[i][j] = 0.f;
   }
-  bf16x8 nx[MAXV], ndy[MAXV];
+  bf16x8 nx[MAXV], ndy[MAXV], nres[MAXV];
   auto load_row = [&](int row) {
     const size_t off = (size_t)row * cols;
 #pragma unroll
@@ -98,6 +99,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
       if (v < nvec) {
         nx[i] = ld_bf16x8_stream(x + off + (size_t)v * 8);
         ndy[i] = ld_bf16x8_stream(dy + off + (size_t)v * 8);
+        if (dres != nullptr) nres[i] = ld_bf16x8_stream(dres + off + (size_t)v * 8);
       }
     }
   };
@@ -106,6 +108,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
     const size_t off = (size_t)row * cols;
     const float rstd = rstd_in[row];
     float xh[MAXV][8], g[MAXV][8];
+    bf16x8 cres[MAXV];                                   // this row's dres: the prefetch below reuses nres
     float dot = 0.f;
 #pragma unroll
     for (int i = 0; i < MAXV; ++i) {
@@ -114,6 +117,7 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
         float dyv[8];
         unpack8(nx[i], xh[i]);
         unpack8(ndy[i], dyv);
+        if (dres != nullptr) cres[i] = nres[i];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           xh[i][j] *= rstd;
@@ -132,6 +136,12 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = rstd * (g[i][j] - xh[i][j] * dot);
+        if (dres != nullptr) {
+          float r[8];
+          unpack8(cres[i], r);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) o[j] += r[j];           // fp32 add, one rounding
+        }
         st_bf16x8(dx + off + (size_t)v * 8, pack8(o));
       }
     }
@@ -225,9 +235,11 @@ extern "C" int llmt_rmsnorm_fwd(const void* x, const void* w, void* y, float* rs
 
 // dw_partial: fp32 scratch [llmt_rmsnorm_bwd_num_partials(rows), cols]. dw_is_fp32 selects the output
 // type of dw; accumulate_dw adds into the existing dw (gradient accumulation).
-extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx,
-                                void* dw, float* dw_partial, int rows, int cols, int dw_is_fp32,
-                                int accumulate_dw, cudaStream_t stream) {
+// dres (nullable, bf16 [rows, cols]): gradient arriving through the residual connection around the norm; the kernel
+// returns dx = norm backward + dres, so the pre-norm block's input gradient needs no separate add pass.
+extern "C" int llmt_rmsnorm_bwd_res(const void* dy, const void* x, const void* w, const float* rstd, const void* dres,
+                                    void* dx, void* dw, float* dw_partial, int rows, int cols, int dw_is_fp32,
+                                    int accumulate_dw, cudaStream_t stream) {
   LLMT_REQUIRE(cols % 8 == 0 && cols <= kNormThreads * 8 * kNormMaxVec,
                "rmsnorm_bwd: cols=%d must be a multiple of 8 and <= %d", cols, kNormThreads * 8 * kNormMaxVec);
   if (rows == 0) return 0;
@@ -235,18 +247,26 @@ extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, co
   auto DY = (const __nv_bfloat16*)dy;
   auto X = (const __nv_bfloat16*)x;
   auto W = (const __nv_bfloat16*)w;
+  auto R = (const __nv_bfloat16*)dres;
   auto DX = (__nv_bfloat16*)dx;
   const int nvec = cols / 8;
   if (nvec <= kNormThreads * 2)
-    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, R, DX, dw_partial, rows, cols);
   else if (nvec <= kNormThreads * 4)
-    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, R, DX, dw_partial, rows, cols);
   else
-    rmsnorm_bwd_kernel<8><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, dw_partial, rows, cols);
+    rmsnorm_bwd_kernel<8><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, R, DX, dw_partial, rows, cols);
   int rc = check_launch("rmsnorm_bwd");
   if (rc) return rc;
   launch_colsum(dw_partial, dw, grid, cols, dw_is_fp32, accumulate_dw, stream);
   return check_launch("rmsnorm_bwd_colsum");
+}
+
+extern "C" int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx,
+                                void* dw, float* dw_partial, int rows, int cols, int dw_is_fp32,
+                                int accumulate_dw, cudaStream_t stream) {
+  return llmt_rmsnorm_bwd_res(dy, x, w, rstd, nullptr, dx, dw, dw_partial, rows, cols, dw_is_fp32, accumulate_dw,
+                              stream);
 }
 
 // -------------------------------------------------------------------------------------------------------
@@ -326,9 +346,9 @@ extern "C" int llmt_rmsnorm_bwd_noalloc(const void* dy, const void* x, const voi
   auto DX = (__nv_bfloat16*)dx;
   const int nvec = cols / 8;
   if (nvec <= kNormThreads * 2)
-    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, partial, rows, cols);
+    rmsnorm_bwd_kernel<2><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, partial, rows, cols);
   else
-    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, DX, partial, rows, cols);
+    rmsnorm_bwd_kernel<4><<<grid, kNormThreads, 0, stream>>>(DY, X, W, rstd, nullptr, DX, partial, rows, cols);
   rc = check_launch("rmsnorm_bwd_noalloc");
   if (rc) return rc;
   launch_colsum(partial, dw, grid, cols, dw_is_fp32, accumulate_dw, stream);

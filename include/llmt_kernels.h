@@ -123,6 +123,11 @@ int llmt_rmsnorm_fwd(const void* x, const void* w, void* y, float* rstd, int row
 int llmt_rmsnorm_bwd_num_partials(int rows);
 int llmt_rmsnorm_bwd(const void* dy, const void* x, const void* w, const float* rstd, void* dx, void* dw,
                      float* dw_partial, int rows, int cols, int dw_is_fp32, int accumulate_dw, cudaStream_t stream);
+/* Same, plus dres (nullable, bf16 [rows, cols]): dx = norm backward + dres (the gradient of the residual connection
+ * around a pre-norm block), added in fp32 inside the kernel. */
+int llmt_rmsnorm_bwd_res(const void* dy, const void* x, const void* w, const float* rstd, const void* dres, void* dx,
+                         void* dw, float* dw_partial, int rows, int cols, int dw_is_fp32, int accumulate_dw,
+                         cudaStream_t stream);
 
 /* RMSNorm backward without a scratch argument.  This entry point has no counterpart in the reference.
  * It is for hosts that cannot allocate device memory or lend a buffer (all device memory pre-planned by
@@ -142,6 +147,11 @@ int llmt_silu_mul_fwd(const void* gate, const void* up, void* out, int rows, int
                       int64_t out_stride, cudaStream_t stream);
 int llmt_silu_mul_bwd(const void* dout, const void* gate, const void* up, void* dgate, void* dup, int rows, int cols,
                       int64_t in_stride, int64_t dout_stride, int64_t dgu_stride, cudaStream_t stream);
+/* Same pass, plus act = silu(gate) * up written to a contiguous [rows, cols] buffer (bit-identical to
+ * llmt_silu_mul_fwd): the recomputed wgrad input of the down projection without a second read of gate | up. */
+int llmt_silu_mul_bwd_act(const void* dout, const void* gate, const void* up, void* dgate, void* dup, void* act,
+                          int rows, int cols, int64_t in_stride, int64_t dout_stride, int64_t dgu_stride,
+                          cudaStream_t stream);
 int llmt_rope_inplace(void* x, const int* pos, const float* cos_t, const float* sin_t, int tokens, int heads,
                       int head_dim, int64_t row_stride, int backward, cudaStream_t stream);
 int llmt_embedding_fwd(const int64_t* ids, const void* weight, void* out, const float* noise_scale, int tokens,

@@ -55,8 +55,10 @@ class LlamaMLP(nn.Module):
         """``pre_norm``: the RMSNorm to apply to ``x`` first, fused with the gate|up projection."""
         no_bias = self.gate_proj.bias is None and self.down_proj.bias is None
         if pre_norm is not None:
-            gate_up = norm_multi_linear(x, pre_norm.weight, pre_norm.variance_epsilon,
-                                        [self.gate_proj.weight, self.up_proj.weight])
+            gate_up, x_pass = norm_multi_linear(x, pre_norm.weight, pre_norm.variance_epsilon,
+                                                [self.gate_proj.weight, self.up_proj.weight], return_residual=True)
+            if residual is x:
+                residual = x_pass       # both gradient branches of x meet in the fused block's backward
         elif tp is not None:
             gate_up = tp.column_linear(x, [self.gate_proj.weight, self.up_proj.weight],
                                        [self.gate_proj.bias, self.up_proj.bias])
@@ -104,8 +106,11 @@ class LlamaAttention(nn.Module):
         tp = ctx.tp
         shards = 1 if tp is None else tp.size
         if pre_norm is not None:
-            qkv = norm_multi_linear(hidden_states, pre_norm.weight, pre_norm.variance_epsilon,
-                                    [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight])
+            qkv, x_pass = norm_multi_linear(hidden_states, pre_norm.weight, pre_norm.variance_epsilon,
+                                            [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
+                                            return_residual=True)
+            if residual is hidden_states:
+                residual = x_pass       # both gradient branches of the layer input meet in the fused block's backward
         elif tp is not None:
             qkv = tp.column_linear(hidden_states, [self.q_proj.weight, self.k_proj.weight, self.v_proj.weight],
                                    [self.q_proj.bias, self.k_proj.bias, self.v_proj.bias])

@@ -8,15 +8,20 @@ lms/dpo/dpo.py:73-114 and lms/orpo/orpo.py:61-93 (log-prob gather).
 CUDA path: logits are produced in bf16 by the tcgen05 GEMM in row chunks, reduced by
 ``csrc/kernels/cross_entropy.cu`` and turned into dlogits IN PLACE, so neither fp32 logits
 (reference: ``logits.float()``, lms/clm/clm.py:147) nor a [T, V] log-softmax tensor ever exist.
-The backward GEMMs (dH = dlogits W, dW += dlogits^T H) run inside the forward call (the gradient of
-a scalar loss w.r.t. the logits does not depend on the upstream gradient except for a scale), which
-is what lets the chunk buffer be recycled; the saved dH / dW are scaled in backward.
+Up to ``_CHUNK_ROWS`` tokens (the usual micro-batch) the bf16 logits chunk is simply kept until backward: the
+upstream gradient is folded into the per-row scale of the in-place dlogits kernel, dH = dlogits W comes from one GEMM
+and dW = dlogits^T H goes through ``ops.linear_op.wgrad``, i.e. straight into the sharding engine's flat gradient
+buffer when it allows that — no dW temporary, no scaling pass, no AccumulateGrad pass over [V, d].
+Longer inputs run chunk by chunk with the backward GEMMs inside the forward call (the gradient of a scalar loss
+w.r.t. the logits does not depend on the upstream gradient except for a scale), which lets one chunk buffer be
+recycled; the saved dH / dW are scaled in backward.
 """
 import torch
 import torch.nn.functional as F
 
 from . import _lib
 from .gemm_op import gemm
+from .linear_op import wgrad
 from .reference import cross_entropy_ref, token_logprob_ref
 
 
@@ -123,6 +128,29 @@ class _FusedLinearCEFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor, ignore_index: int):
         need_grads = hidden.requires_grad or weight.requires_grad
+        rows = hidden.shape[0]
+        ctx.deferred = rows <= _CHUNK_ROWS
+        if ctx.deferred:
+            L = _lib.lib()
+            vocab = weight.shape[0]
+            vpad = (vocab + 7) // 8 * 8
+            buf = torch.empty((rows, vpad), dtype=torch.bfloat16, device=hidden.device)
+            logits = buf[:, :vocab]
+            gemm(hidden, weight, out=logits)
+            lse = torch.empty(rows, dtype=torch.float32, device=hidden.device)
+            tgt = torch.empty_like(lse)
+            out2 = torch.empty(2, dtype=torch.float32, device=hidden.device)      # [sum of token losses, valid tokens]
+            _lib.check(L.llmt_ce_fwd(_lib.ptr(logits), _lib.ptr(labels), _lib.ptr(lse), _lib.ptr(tgt),
+                                     _lib.c_int(rows), _lib.c_int(vocab), _lib.c_i64(vpad), _lib.c_i64(ignore_index),
+                                     _lib.c_f32(0.0), _lib.stream()), 'ce_fwd')
+            _lib.check(L.llmt_ce_reduce(_lib.ptr(lse), _lib.ptr(tgt), _lib.ptr(labels), _lib.ptr(out2),
+                                        _lib.c_int(rows), _lib.c_i64(ignore_index), _lib.stream()), 'ce_reduce')
+            if need_grads:
+                ctx.save_for_backward(hidden, weight, labels, lse, buf, out2)
+                ctx.weights = (weight,)
+                ctx.ignore_index = ignore_index
+                ctx.consumed = False
+            return out2[0] / out2[1].clamp_min(1.0)
         n_valid = labels.ne(ignore_index).sum().clamp_min(1).float()
         inv = (1.0 / n_valid)
 
@@ -139,6 +167,22 @@ class _FusedLinearCEFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_out: torch.Tensor):
+        if ctx.deferred:
+            hidden, weight, labels, lse, buf, out2 = ctx.saved_tensors
+            if ctx.consumed:
+                raise RuntimeError('fused_linear_cross_entropy: the logits were turned into their gradient in place by '
+                                   'the first backward pass; a second backward through the same loss is not supported')
+            ctx.consumed = True
+            rows, vocab = hidden.shape[0], weight.shape[0]
+            logits = buf[:, :vocab]
+            scale = (grad_out.float() / out2[1].clamp_min(1.0)).expand(rows).contiguous()
+            _lib.check(_lib.lib().llmt_ce_bwd_inplace(_lib.ptr(logits), _lib.ptr(labels), _lib.ptr(lse),
+                                                      _lib.ptr(scale), _lib.c_int(rows), _lib.c_int(vocab),
+                                                      _lib.c_i64(buf.shape[1]), _lib.c_i64(ctx.ignore_index),
+                                                      _lib.c_f32(0.0), _lib.stream()), 'ce_bwd')
+            dh = gemm(logits, weight, b_mn_major=True) if ctx.needs_input_grad[0] else None     # dlogits @ W
+            dw = wgrad(logits, hidden, ctx.weights)[0] if ctx.needs_input_grad[1] else None     # dlogits^T @ H
+            return dh, dw, None, None
         dh, dw = ctx.saved_tensors
         g = grad_out.float()
         return (dh * g.to(dh.dtype)), (dw * g.to(dw.dtype)).to(ctx.weight_dtype), None, None

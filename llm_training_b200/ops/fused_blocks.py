@@ -6,7 +6,8 @@
 The reference saves the normalised activations and the SwiGLU product for backward (Liger ops feeding
 ``nn.Linear``; models/llama/llama_model.py:283,427).  Here only the GEMM *inputs that cannot be rebuilt cheaply*
 are saved — the layer input ``x`` + ``rstd`` and the ``gate|up`` GEMM output — and the bandwidth-bound
-RMSNorm / SiLU·mul forward kernels are re-run in backward.  Per LLaMA-3-8B layer at 8192 tokens this drops
+RMSNorm forward kernel is re-run in backward; the SwiGLU product is rebuilt by the SiLU·mul BACKWARD kernel in the
+pass that already reads ``gate|up``.  Per LLaMA-3-8B layer at 8192 tokens this drops
 352 MB of saved activations (2 x 64 MB normed inputs + 224 MB SwiGLU output) for ~0.1 ms of recompute, which is
 what lets the 8B model train on ONE 180 GB GPU without layer-level activation checkpointing.
 """
@@ -16,7 +17,7 @@ from . import _lib
 from .gemm_op import gemm
 from .linear_op import _adjacent_rows_view, _as_2d, complete_lazy_gather, linear, multi_linear, wgrad
 from .rms_norm_op import rms_norm, rmsnorm_bwd_raw, rmsnorm_fwd_raw
-from .swiglu_op import silu_mul_bwd_raw, silu_mul_fused, silu_mul_fwd_raw
+from .swiglu_op import silu_mul_bwd_act_raw, silu_mul_bwd_raw, silu_mul_fused, silu_mul_fwd_raw
 
 
 class _NormMultiLinearFn(torch.autograd.Function):
@@ -46,11 +47,18 @@ class _NormMultiLinearFn(torch.autograd.Function):
         ctx.splits = [w.shape[0] for w in weights]
         ctx.weights = weights
         ctx.norm_dtype = norm_weight.dtype
-        return y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])
+        ctx.norm_param = norm_weight
+        ctx.set_materialize_grads(False)
+        # second output: `x` itself, for the residual connection around this block.  Its gradient then comes back to
+        # THIS node together with dy, and the norm-backward kernel adds it while it writes dx (instead of autograd
+        # summing the two branches of x in a separate pass over [T, d]).
+        return (y if x.dim() == 2 else y.view(*x.shape[:-1], fused.shape[0])), x
 
     @staticmethod
-    def backward(ctx, dy: torch.Tensor):
+    def backward(ctx, dy: torch.Tensor | None, dres: torch.Tensor | None):
         x2, nw, rstd, fused = ctx.saved_tensors
+        if dy is None:                                                      # only the pass-through output was used
+            return (dres, None, None, *([None] * len(ctx.splits)))
         dy2 = _as_2d(dy)
         xn, _ = rmsnorm_fwd_raw(x2, nw, ctx.eps, want_rstd=False)          # recompute (bandwidth-bound, cheap)
         dws: list = [None] * len(ctx.splits)
@@ -58,17 +66,29 @@ class _NormMultiLinearFn(torch.autograd.Function):
             dws = wgrad(dy2, xn, ctx.weights)
         del xn
         dxn = gemm(dy2, fused, b_mn_major=True)
-        dx, dnw = rmsnorm_bwd_raw(dxn, x2, nw, rstd)
-        return (dx.view(ctx.x_shape), dnw.to(ctx.norm_dtype), None, *dws)
+        r2 = None
+        if dres is not None:
+            r2 = dres.reshape(x2.shape)
+            if not r2.is_contiguous() or r2.dtype != x2.dtype:
+                r2 = r2.to(x2.dtype).contiguous()
+        dx, dnw = rmsnorm_bwd_raw(dxn, x2, nw, rstd, dres=r2,
+                                  weight=ctx.norm_param if ctx.needs_input_grad[1] else None)
+        return (dx.view(ctx.x_shape), None if dnw is None else dnw.to(ctx.norm_dtype), None, *dws)
 
 
-def norm_multi_linear(x: torch.Tensor, norm_weight: torch.Tensor, eps: float, weights: list[torch.Tensor]
-                      ) -> torch.Tensor:
-    """``concat_i(rms_norm(x) @ W_i^T)``; the normalised activations are not kept for backward."""
+def norm_multi_linear(x: torch.Tensor, norm_weight: torch.Tensor, eps: float, weights: list[torch.Tensor],
+                      return_residual: bool = False) -> torch.Tensor | tuple[torch.Tensor, torch.Tensor]:
+    """``concat_i(rms_norm(x) @ W_i^T)``; the normalised activations are not kept for backward.
+
+    ``return_residual=True`` also returns ``x`` for the residual connection around the block (``h = x + f(norm(x))``):
+    use the returned tensor as the residual and the two gradient branches of ``x`` are summed inside the norm-backward
+    kernel."""
     if (_lib.use_kernels(x) and all(w.dtype == torch.bfloat16 for w in weights) and x.shape[-1] % 8 == 0
             and x.shape[-1] <= 16384):
-        return _NormMultiLinearFn.apply(x, norm_weight, eps, *weights)
-    return multi_linear(rms_norm(x, norm_weight, eps), weights)     # completes a pending lazy gather itself
+        y, x_pass = _NormMultiLinearFn.apply(x, norm_weight, eps, *weights)
+        return (y, x_pass) if return_residual else y
+    y = multi_linear(rms_norm(x, norm_weight, eps), weights)        # completes a pending lazy gather itself
+    return (y, x) if return_residual else y
 
 
 class _SwiGLUDownFn(torch.autograd.Function):
@@ -92,12 +112,15 @@ class _SwiGLUDownFn(torch.autograd.Function):
         gu, w = ctx.saved_tensors
         dy2 = _as_2d(dy)
         dw = None
+        dact = gemm(dy2, w, b_mn_major=True)
         if ctx.needs_input_grad[1]:
-            act = silu_mul_fwd_raw(gu)                                       # recompute
+            # one pass over gate | up gives both d(gate | up) and the recomputed SwiGLU product for the wgrad GEMM
+            dgu, act = silu_mul_bwd_act_raw(dact, gu)
+            del dact
             dw = wgrad(dy2, act, ctx.weights)[0]
             del act
-        dact = gemm(dy2, w, b_mn_major=True)
-        dgu = silu_mul_bwd_raw(dact, gu)
+        else:
+            dgu = silu_mul_bwd_raw(dact, gu)
         return dgu.view(ctx.shape), dw, (dy if ctx.has_residual else None)
 
 

@@ -17,18 +17,45 @@ def rmsnorm_fwd_raw(x2: torch.Tensor, w: torch.Tensor, eps: float, want_rstd: bo
     return y, rstd
 
 
-def rmsnorm_bwd_raw(dy2: torch.Tensor, x2: torch.Tensor, w: torch.Tensor, rstd: torch.Tensor
-                    ) -> tuple[torch.Tensor, torch.Tensor]:
-    """-> (dx bf16 [rows, cols], dw fp32 [cols])."""
+def _direct_grad_target(weight: torch.Tensor | None) -> torch.Tensor | None:
+    """The weight's view inside the sharding engine's flat gradient buffer when the kernel may write its dw straight
+    there (``FlatParamEngine.enable_direct_grad_accumulation``; same contract as ``ops.linear_op.wgrad``)."""
+    if weight is None or not getattr(weight, '_llmt_direct_grad', False):
+        return None
+    g = weight.grad
+    if g is None or not g.is_contiguous() or g.dtype not in (torch.bfloat16, torch.float32):
+        return None
+    return g
+
+
+def rmsnorm_bwd_raw(dy2: torch.Tensor, x2: torch.Tensor, w: torch.Tensor, rstd: torch.Tensor,
+                    dres: torch.Tensor | None = None, weight: torch.Tensor | None = None
+                    ) -> tuple[torch.Tensor, torch.Tensor | None]:
+    """-> (dx bf16 [rows, cols], dw fp32 [cols]).
+
+    ``dres``: gradient of the residual connection around the norm, added to dx inside the kernel (fp32 add, one
+    rounding, no separate pass).  ``weight``: the norm's parameter; when the sharding engine lets its gradient be
+    written in place, dw goes (or is added) straight into ``weight.grad``, the engine is notified and the returned dw
+    is ``None`` — no fp32 temporary, no dtype conversion, no AccumulateGrad launch."""
     rows, cols = x2.shape
     L = _lib.lib()
     dx = torch.empty_like(x2)
     nparts = L.llmt_rmsnorm_bwd_num_partials(_lib.c_int(rows))
     partial = torch.empty((nparts, cols), dtype=torch.float32, device=x2.device)
-    dw = torch.empty(cols, dtype=torch.float32, device=x2.device)
-    _lib.check(L.llmt_rmsnorm_bwd(_lib.ptr(dy2), _lib.ptr(x2), _lib.ptr(w), _lib.ptr(rstd), _lib.ptr(dx), _lib.ptr(dw),
-                                  _lib.ptr(partial), _lib.c_int(rows), _lib.c_int(cols), _lib.c_int(1), _lib.c_int(0),
-                                  _lib.stream()), 'rmsnorm_bwd')
+    target = _direct_grad_target(weight)
+    if target is not None:
+        fresh = getattr(weight, '_llmt_grad_fresh', False)       # first gradient of the step: overwrite, else add
+        dw, is_fp32, accumulate = target, target.dtype == torch.float32, not fresh
+    else:
+        dw, is_fp32, accumulate = torch.empty(cols, dtype=torch.float32, device=x2.device), True, False
+    _lib.check(L.llmt_rmsnorm_bwd_res(_lib.ptr(dy2), _lib.ptr(x2), _lib.ptr(w), _lib.ptr(rstd), _lib.ptr(dres),
+                                      _lib.ptr(dx), _lib.ptr(dw), _lib.ptr(partial), _lib.c_int(rows),
+                                      _lib.c_int(cols), _lib.c_int(int(is_fp32)), _lib.c_int(int(accumulate)),
+                                      _lib.stream()), 'rmsnorm_bwd')
+    if target is not None:
+        weight._llmt_grad_fresh = False
+        weight._llmt_grad_ready(weight)
+        return dx, None
     return dx, dw
 
 
@@ -50,6 +77,7 @@ class _RMSNormFn(torch.autograd.Function):
         ctx.save_for_backward(x2, w, rstd)
         ctx.shape = shape
         ctx.weight_dtype = weight.dtype
+        ctx.weight = weight
         return y.view(shape)
 
     @staticmethod
@@ -59,15 +87,8 @@ class _RMSNormFn(torch.autograd.Function):
         dy2 = dy.reshape(rows, cols)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        L = _lib.lib()
-        dx = torch.empty_like(x2)
-        nparts = L.llmt_rmsnorm_bwd_num_partials(_lib.c_int(rows))
-        partial = torch.empty((nparts, cols), dtype=torch.float32, device=x2.device)
-        dw = torch.empty(cols, dtype=torch.float32, device=x2.device)
-        _lib.check(L.llmt_rmsnorm_bwd(_lib.ptr(dy2), _lib.ptr(x2), _lib.ptr(w), _lib.ptr(rstd), _lib.ptr(dx),
-                                      _lib.ptr(dw), _lib.ptr(partial), _lib.c_int(rows), _lib.c_int(cols),
-                                      _lib.c_int(1), _lib.c_int(0), _lib.stream()), 'rmsnorm_bwd')
-        return dx.view(ctx.shape), dw.to(ctx.weight_dtype), None
+        dx, dw = rmsnorm_bwd_raw(dy2, x2, w, rstd, weight=ctx.weight if ctx.needs_input_grad[1] else None)
+        return dx.view(ctx.shape), (None if dw is None else dw.to(ctx.weight_dtype)), None
 
 
 def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:

@@ -30,6 +30,20 @@ def silu_mul_bwd_raw(d: torch.Tensor, gu: torch.Tensor) -> torch.Tensor:
     return dgu
 
 
+def silu_mul_bwd_act_raw(d: torch.Tensor, gu: torch.Tensor) -> tuple[torch.Tensor, torch.Tensor]:
+    """-> (d(gate | up) [rows, 2F], silu(gate) * up [rows, F]) from ONE pass over ``gu``."""
+    rows, f2 = gu.shape
+    f = f2 // 2
+    dgu = torch.empty_like(gu)
+    act = torch.empty((rows, f), dtype=gu.dtype, device=gu.device)
+    c = _lib.ctypes.c_void_p
+    _lib.check(_lib.lib().llmt_silu_mul_bwd_act(_lib.ptr(d), _lib.ptr(gu), c(gu.data_ptr() + 2 * f), _lib.ptr(dgu),
+                                                c(dgu.data_ptr() + 2 * f), _lib.ptr(act), _lib.c_int(rows),
+                                                _lib.c_int(f), _lib.c_i64(f2), _lib.c_i64(f), _lib.c_i64(f2),
+                                                _lib.stream()), 'silu_mul_bwd_act')
+    return dgu, act
+
+
 class _SiluMulFn(torch.autograd.Function):
     """Operates on a fused ``[rows, 2F]`` tensor (gate | up) so the GEMM before it is one launch and
     the gradient comes back as one ``[rows, 2F]`` tensor for one dgrad GEMM."""

@@ -316,7 +316,7 @@ class FlatParamEngine:
 
         for u in self.units:
             for _, p in u.params:
-                if p.requires_grad and p.dim() == 2:
+                if p.requires_grad and p.dim() in (1, 2):          # GEMM weights and norm weights
                     p._llmt_direct_grad = flag
                     p._llmt_grad_ready = self._on_grad_ready
                     if flag and not getattr(p, '_llmt_settle_hook', False):

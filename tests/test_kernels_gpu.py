@@ -49,6 +49,38 @@ def test_rmsnorm(rows, cols):
     _close(w.grad, wr.grad, rtol=3e-2, atol=0.15)
 
 
+def test_silu_backward_also_returns_the_forward_product():
+    from llm_training_b200.ops.swiglu_op import silu_mul_bwd_act_raw, silu_mul_bwd_raw, silu_mul_fwd_raw
+    g = torch.Generator(device=DEV).manual_seed(9)
+    gu = (torch.randn(777, 2 * 1024, device=DEV, generator=g) * 2).bfloat16()
+    d = torch.randn(777, 1024, device=DEV, generator=g).bfloat16()
+    dgu, act = silu_mul_bwd_act_raw(d, gu)
+    assert torch.equal(act, silu_mul_fwd_raw(gu))
+    assert torch.equal(dgu, silu_mul_bwd_raw(d, gu))
+
+
+def test_rmsnorm_backward_adds_the_residual_gradient_in_fp32():
+    from llm_training_b200.ops.rms_norm_op import rmsnorm_bwd_raw, rmsnorm_fwd_raw
+    g = torch.Generator(device=DEV).manual_seed(4)
+    rows, cols = 1000, 4096
+    x = torch.randn(rows, cols, device=DEV, generator=g).bfloat16()
+    w = (1 + 0.1 * torch.randn(cols, device=DEV, generator=g)).bfloat16()
+    dy = torch.randn(rows, cols, device=DEV, generator=g).bfloat16()
+    dres = torch.randn(rows, cols, device=DEV, generator=g).bfloat16()
+    _, rstd = rmsnorm_fwd_raw(x, w, 1e-5)
+    dx_plain, dw_plain = rmsnorm_bwd_raw(dy, x, w, rstd)
+    dx_res, dw_res = rmsnorm_bwd_raw(dy, x, w, rstd, dres=dres)
+    assert torch.equal(dw_plain, dw_res)
+    xr = x.float().requires_grad_()
+    ref.rms_norm_ref(xr, w.float(), 1e-5).backward(dy.float())
+    want = xr.grad + dres.float()
+    err = (dx_res.float() - want).abs()
+    assert (err <= 2.0 ** -8 * want.abs() + 2e-3 * xr.grad.abs().max()).all(), err.max().item()
+    # one rounding: at least as close to the fp32 sum as "round(dx) + dres, rounded again"
+    two_step = (dx_plain.float() + dres.float()).bfloat16().float()
+    assert err.mean().item() <= (two_step - want).abs().mean().item() * 1.001
+
+
 def test_silu_mul():
     torch.manual_seed(0)
     gu = torch.randn(300, 2 * 1024, device=DEV).bfloat16().requires_grad_()
@@ -289,7 +321,10 @@ def test_attention_dropout_matches_oracle_with_the_same_mask(dropout_p):
     _attn_case(256, 2, 1, 64, dropout_p=dropout_p, softcap=20.0, window=64, seed=3)
 
 
-def test_fused_norm_multi_linear_and_swiglu_down():
+@pytest.mark.parametrize('passthrough', [False, True])
+def test_fused_norm_multi_linear_and_swiglu_down(passthrough):
+    """`passthrough`: the residual connection uses the block's second output, so both gradient branches of x reach
+    the fused block's backward and are summed inside the norm-backward kernel (no separate add pass)."""
     from llm_training_b200.ops import norm_multi_linear, swiglu_down_linear
     torch.manual_seed(0)
     t, d, f = 300, 256, 512
@@ -299,8 +334,12 @@ def test_fused_norm_multi_linear_and_swiglu_down():
     w2 = (torch.randn(f, d, device=DEV) * 0.05).bfloat16().requires_grad_()
     wd = (torch.randn(d, f, device=DEV) * 0.05).bfloat16().requires_grad_()
     dy = torch.randn(t, d, device=DEV).bfloat16()
-    gu = norm_multi_linear(x, nw, 1e-5, [w1, w2])
-    y = swiglu_down_linear(gu, wd, x)
+    if passthrough:
+        gu, x_res = norm_multi_linear(x, nw, 1e-5, [w1, w2], return_residual=True)
+        assert x_res.data_ptr() == x.data_ptr()                 # an alias, not a copy
+    else:
+        gu, x_res = norm_multi_linear(x, nw, 1e-5, [w1, w2]), x
+    y = swiglu_down_linear(gu, wd, x_res)
     y.backward(dy)
     xr, nwr, w1r, w2r, wdr = (v.detach().float().requires_grad_() for v in (x, nw, w1, w2, wd))
     xn = ref.rms_norm_ref(xr, nwr, 1e-5)
