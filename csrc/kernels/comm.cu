@@ -326,6 +326,72 @@ static int fill_peers(Peers* out, const void* const* ptrs, int world) {
   return 0;
 }
 
+// ---- vocabulary-parallel loss statistics: every rank holds {lse_local[rows], tgt_local[rows]} (fp32, symmetric
+// memory) of its vocabulary shard; the global statistics are lse = logsumexp_r(lse_local_r), tgt = sum_r tgt_local_r
+// (the label's logit lives on exactly one rank, the others hold 0).  One pass, 4 rows per thread, every peer's
+// values loaded before any arithmetic.  Replaces all_gather + logsumexp + all_reduce (reference: loss_parallel(),
+// src/llm_training/lms/clm/clm.py:114-120).
+__global__ void __launch_bounds__(256)
+vocab_loss_combine_kernel(Peers stats, int world, int rows, const int64_t* __restrict__ labels, int64_t ignore_index,
+                          float* __restrict__ lse_out, float* __restrict__ nll_out) {
+  const int nvec = rows >> 2;
+  for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += gridDim.x * blockDim.x) {
+    uint4 l[kMaxRanks], t[kMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {
+      if (r < world) {
+        const float* base = reinterpret_cast<const float*>(stats.ptr[r]);
+        l[r] = ld_peer_16_fresh(base + 4 * v);
+        t[r] = ld_peer_16_fresh(base + rows + 4 * v);
+      }
+    }
+    float lse[4], tgt[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float m = -INFINITY, sum = 0.f, tg = 0.f;
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < world) m = fmaxf(m, __uint_as_float((&l[r].x)[e]));
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < world) {
+          sum += __expf(__uint_as_float((&l[r].x)[e]) - m);
+          tg += __uint_as_float((&t[r].x)[e]);
+        }
+      }
+      lse[e] = m + logf(sum);
+      tgt[e] = tg;
+    }
+    float nll[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) nll[e] = labels[4 * v + e] != ignore_index ? lse[e] - tgt[e] : 0.f;
+    *reinterpret_cast<float4*>(lse_out + 4 * v) = make_float4(lse[0], lse[1], lse[2], lse[3]);
+    *reinterpret_cast<float4*>(nll_out + 4 * v) = make_float4(nll[0], nll[1], nll[2], nll[3]);
+  }
+}
+
+// ---- vocabulary-parallel embedding: each token's row lives on exactly one rank (the owner of its id) and is needed
+// by exactly one rank (the owner of its sequence shard), so the "masked lookup + reduce-scatter" of the reference
+// (RowwiseParallel embedding, models/llama/llama_model.py:205-208) is a scatter: the id's owner stores the row
+// straight into the sequence owner's [rows_per_rank, dim] buffer.  No zero-filled partial results, no reduction.
+__global__ void __launch_bounds__(256)
+vocab_embedding_scatter_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ weight, Peers out,
+                               int tokens, int dim, int64_t v0, int v_local, int rows_per_rank, int64_t pad_local) {
+  const int vec_per_row = dim >> 3;
+  const int64_t total = (int64_t)tokens * vec_per_row;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t t = i / vec_per_row;
+    const int c = (int)(i - t * vec_per_row) << 3;
+    const int64_t id = ids[t] - v0;
+    if (id < 0 || id >= v_local) continue;                       // another rank's row
+    uint4 row = make_uint4(0u, 0u, 0u, 0u);                      // the padding row embeds to zero
+    if (id != pad_local) row = *reinterpret_cast<const uint4*>(weight + id * dim + c);
+    const int dst = (int)(t / rows_per_rank);
+    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out.ptr[dst]) + (t - (int64_t)dst * rows_per_rank) * dim + c;
+    st_peer_16(o, row);
+  }
+}
+
 }  // namespace comm
 }  // namespace llmt
 
@@ -475,4 +541,36 @@ extern "C" int llmt_comm_adamw_push(float* master, float* m, float* v, const voi
   return llmt_comm_adamw_push_mc(master, m, v, grad_shard, param_ptrs, nullptr, rank, world, shard_elems,
                                  grad_is_fp32, lr, beta1, beta2, eps, weight_decay, step, grad_scale, max_norm,
                                  norm_sq, stream);
+}
+
+// stats_ptrs: every rank's {lse_local[rows], tgt_local[rows]} fp32 block in symmetric memory (HOST array of this
+// rank's mappings); the caller puts a barrier between the writers and this call.  rows % 4 == 0.
+extern "C" int llmt_comm_vocab_loss_combine(const void* const* stats_ptrs, int world, int rows, const int64_t* labels,
+                                            int64_t ignore_index, float* lse_out, float* nll_out,
+                                            cudaStream_t stream) {
+  LLMT_REQUIRE(rows % 4 == 0 && world >= 1 && world <= kMaxRanks, "vocab_loss_combine: rows=%d must be a multiple of 4, "
+               "world=%d at most %d", rows, world, kMaxRanks);
+  Peers stats;
+  if (fill_peers(&stats, stats_ptrs, world)) return 1;
+  if (rows == 0) return 0;
+  vocab_loss_combine_kernel<<<grid_for(rows / 4, 256, 1), 256, 0, stream>>>(stats, world, rows, labels, ignore_index,
+                                                                         lse_out, nll_out);
+  return check_launch("comm_vocab_loss_combine");
+}
+
+// out_ptrs: every rank's [rows_per_rank, dim] bf16 output buffer in symmetric memory.  ids: all `tokens` ids (the
+// same on every rank); weight: this rank's rows [v0, v0 + v_local) of the embedding table.  The caller follows the
+// call with a barrier before anybody reads its output buffer.
+extern "C" int llmt_comm_vocab_embedding_scatter(const int64_t* ids, const void* weight, const void* const* out_ptrs,
+                                                 int world, int tokens, int dim, int64_t v0, int v_local,
+                                                 int rows_per_rank, int64_t pad_local, cudaStream_t stream) {
+  LLMT_REQUIRE(dim % 8 == 0 && rows_per_rank > 0 && (int64_t)rows_per_rank * world >= tokens,
+               "vocab_embedding_scatter: dim=%d must be a multiple of 8 and %d ranks x %d rows must cover %d tokens", dim,
+               world, rows_per_rank, tokens);
+  Peers out;
+  if (fill_peers(&out, out_ptrs, world)) return 1;
+  if (tokens == 0) return 0;
+  vocab_embedding_scatter_kernel<<<grid_for((int64_t)tokens * dim / 8, 256, 4), 256, 0, stream>>>(
+      ids, (const __nv_bfloat16*)weight, out, tokens, dim, v0, v_local, rows_per_rank, pad_local);
+  return check_launch("comm_vocab_embedding_scatter");
 }

@@ -167,12 +167,30 @@ class _VocabParallelLoss(torch.autograd.Function):
             else:
                 logits = gemm(hidden.contiguous(), weight)
             rows = logits.shape[0]
-            lse_local = torch.empty(rows, dtype=torch.float32, device=hidden.device)
-            tgt_local = torch.empty_like(lse_local)
+            on_nvlink = tp is not None and tp.ring is not None and rows % 4 == 0
+            if on_nvlink:
+                # the loss kernel writes this shard's statistics straight into symmetric memory; ONE kernel then reads
+                # every rank's block over NVLink and combines them (no all_gather / logsumexp / all_reduce launches)
+                stats_buf, stats = tp.ring.next_f32(2 * rows)
+                lse_local, tgt_local = stats[:rows], stats[rows:]
+            else:
+                lse_local = torch.empty(rows, dtype=torch.float32, device=hidden.device)
+                tgt_local = torch.empty_like(lse_local)
             _lib.check(_lib.lib().llmt_ce_fwd(_lib.ptr(logits), _lib.ptr(local_labels), _lib.ptr(lse_local),
                                               _lib.ptr(tgt_local), _lib.c_int(rows), _lib.c_int(v_local),
                                               _lib.c_i64(logits.stride(0)), _lib.c_i64(ignore_index),
                                               _lib.c_f32(0.0), _lib.stream()), 'ce_fwd')
+            if on_nvlink:
+                tp.comm.barrier()                   # every rank's statistics are in place
+                lse = torch.empty(rows, dtype=torch.float32, device=hidden.device)
+                nll = torch.empty_like(lse)
+                _lib.check(_lib.lib().llmt_comm_vocab_loss_combine(
+                    stats_buf.peer_ptrs_at(0), _lib.c_int(tp.size), _lib.c_int(rows), _lib.ptr(labels),
+                    _lib.c_i64(ignore_index), _lib.ptr(lse), _lib.ptr(nll), _lib.stream()), 'comm_vocab_loss_combine')
+                ctx.save_for_backward(hidden, weight, logits, local_labels, lse)
+                ctx.meta = (ignore_index, use_k, v_local)
+                ctx.tp = tp
+                return nll
         else:
             logits = F.linear(hidden, weight).float()
             lse_local = torch.logsumexp(logits, dim=-1)
@@ -246,6 +264,11 @@ class _SymmetricRing:
         self.turn[key] ^= 1
         buf = self.buffers[key][self.turn[key]]
         return buf, buf.tensor.view(rows, cols)
+
+    def next_f32(self, numel: int):
+        """A symmetric fp32 vector of ``numel`` elements (its own ring entry: two bf16 elements per float)."""
+        buf, view = self.next(2 * numel, 1)
+        return buf, view.view(-1).view(torch.float32)
 
 
 def _gemm_dist(mode: int, a: torch.Tensor | None, a_ptrs, b: torch.Tensor, c: torch.Tensor | None, c_ptrs, world: int,
@@ -360,6 +383,48 @@ class _FusedLinearReduceScatter(torch.autograd.Function):
         return dx, dw, (dy_local if ctx.has_residual else None), None
 
 
+class _VocabParallelEmbedding(torch.autograd.Function):
+    """Vocabulary-sharded embedding -> sequence-sharded activations without a reduction: the rank that owns a token's
+    id stores its row straight into the buffer of the rank that owns the token's sequence shard
+    (csrc/kernels/comm.cu, vocab_embedding_scatter_kernel).  Backward gathers the sequence shards of the gradient over
+    NVLink (pull) and sums each local id's rows in sorted order (no atomics)."""
+
+    @staticmethod
+    def forward(ctx, flat_ids: torch.Tensor, weight: torch.Tensor, tp: 'TensorParallelContext', pad_local: int
+                ) -> torch.Tensor:
+        tokens, (v_local, dim) = flat_ids.numel(), weight.shape
+        rows = tokens // tp.size
+        buf, view = tp.ring.next(rows, dim)
+        tp.comm.barrier()                   # nobody still reads this ring slot's previous contents
+        _lib.check(_lib.lib().llmt_comm_vocab_embedding_scatter(
+            _lib.ptr(flat_ids), _lib.ptr(weight), buf.peer_ptrs_at(0), _lib.c_int(tp.size), _lib.c_int(tokens),
+            _lib.c_int(dim), _lib.c_i64(tp.rank * v_local), _lib.c_int(v_local), _lib.c_int(rows),
+            _lib.c_i64(pad_local), _lib.stream()), 'comm_vocab_embedding_scatter')
+        tp.comm.barrier()                   # every owner's rows have landed
+        ctx.save_for_backward(flat_ids)
+        ctx.tp, ctx.meta = tp, (v_local, dim, pad_local, weight.dtype)
+        return view.clone()
+
+    @staticmethod
+    def backward(ctx, g: torch.Tensor):
+        (flat_ids,) = ctx.saved_tensors
+        tp = ctx.tp
+        v_local, dim, pad_local, wdtype = ctx.meta
+        tokens = flat_ids.numel()
+        rows = tokens // tp.size
+        buf, full = tp.ring.next(tokens, dim)
+        full[tp.rank * rows:(tp.rank + 1) * rows].copy_(g.reshape(rows, dim))
+        tp.comm.allgather_pull(buf, 0, rows * dim * 2)          # barrier + pull of every peer's shard
+        local = flat_ids - tp.rank * v_local                     # ids of other shards fall outside [0, v_local)
+        sorted_ids, perm = torch.sort(local, stable=True)
+        dw = torch.empty((v_local, dim), dtype=wdtype, device=g.device)
+        _lib.check(_lib.lib().llmt_embedding_bwd_sorted(_lib.ptr(sorted_ids), _lib.ptr(perm), _lib.ptr(full),
+                                                        _lib.ptr(dw), _lib.c_int(tokens), _lib.c_int(dim),
+                                                        _lib.c_int(v_local), _lib.c_i64(pad_local), _lib.stream()),
+                   'embedding_bwd')
+        return None, dw, None, None
+
+
 # ---------------------------------------------------------------------------------------------------
 # the context object handed to the models
 # ---------------------------------------------------------------------------------------------------
@@ -419,6 +484,12 @@ class TensorParallelContext:
         computed from the global sequence length (fixes SURVEY Appendix B5)."""
         v_local = weight.shape[0]
         flat = input_ids.reshape(-1)
+        rows_per_rank = flat.numel() // self.size
+        if (self.ring is not None and _lib.use_kernels(weight) and weight.dtype == torch.bfloat16
+                and weight.shape[1] % 8 == 0 and flat.numel() % self.size == 0 and weight.is_contiguous()):
+            pad_local = -1 if padding_idx is None else padding_idx - self.rank * v_local
+            out = _VocabParallelEmbedding.apply(flat.contiguous(), weight, self, pad_local)
+            return self._add_neftune_noise(out, noise_scale, seed)
         local = flat - self.rank * v_local
         ok = (local >= 0) & (local < v_local)
         local_pad = None
@@ -427,6 +498,9 @@ class TensorParallelContext:
         rows = embedding(local.clamp(0, v_local - 1), weight, local_pad)
         rows = rows * ok.unsqueeze(1).to(rows.dtype)
         out = _ReduceScatterSeq.apply(rows, self.axis)
+        return self._add_neftune_noise(out, noise_scale, seed)
+
+    def _add_neftune_noise(self, out: torch.Tensor, noise_scale: torch.Tensor | None, seed: int) -> torch.Tensor:
         if noise_scale is not None:
             shard = noise_scale.chunk(self.size)[self.rank]
             gen = torch.Generator(device=out.device).manual_seed(seed * 1009 + self.rank)

@@ -209,7 +209,26 @@ def _tp_worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
         loss.backward()
         grads = [float(p.grad.float().abs().sum()) for p in model.parameters()]
         extra = None
-        if comm_kind == 'nvlink':       # the fused all-gather -> GEMM kernel against NCCL all-gather + GEMM
+        if comm_kind == 'nvlink':
+            # vocabulary-parallel embedding as a scatter over NVLink: bit-equal to a lookup in the whole table
+            shard = model.embed_tokens.weight.detach()
+            table = torch.empty(shard.shape[0] * world, shard.shape[1], dtype=shard.dtype, device='cuda')
+            dist.all_gather_into_tensor(table, shard.contiguous())
+            want = table[ids.flatten()]
+            want[ids.flatten() == cfg.pad_token_id] = 0
+            for _ in range(3):          # repeated use walks the symmetric buffer ring
+                got = tp.vocab_parallel_embedding(ids, model.embed_tokens.weight, cfg.pad_token_id, None, 0)
+            assert torch.equal(got, want.chunk(world)[rank]), 'vocab-parallel embedding differs from the table lookup'
+            # loss statistics combined by the NVLink kernel against the NCCL + torch combination
+            from llm_training_b200.parallel.tensor_parallel import _VocabParallelLoss
+            labels = shift_labels(ids).flatten()
+            h = out.normed_hidden_states.detach()
+            nll_fused = _VocabParallelLoss.apply(h, model.lm_head.weight.detach(), labels, -100, tp.axis, tp)
+            nll_nccl = _VocabParallelLoss.apply(tp.gather_sequence(h), model.lm_head.weight.detach(), labels, -100,
+                                                tp.axis)
+            assert float((nll_fused - nll_nccl).abs().max()) < 1e-4, float((nll_fused - nll_nccl).abs().max())
+            assert float(nll_fused[labels == -100].abs().max()) == 0.0
+            # the fused all-gather -> GEMM kernel against NCCL all-gather + GEMM
             x = torch.randn(256, 256, device='cuda', generator=torch.Generator('cuda').manual_seed(rank)).bfloat16()
             w = (torch.randn(384, 256, device='cuda', generator=torch.Generator('cuda').manual_seed(7)) * 0.05).bfloat16()
             y = _FusedGatherLinear.apply(x, tp, w)
