@@ -34,6 +34,13 @@ MODELS = {
     'llama-3.1-70b': dict(vocab_size=128256, hidden_size=8192, intermediate_size=28672, num_hidden_layers=80,
                           num_attention_heads=64, num_key_value_heads=8, max_position_embeddings=131072,
                           rope_theta=500000.0, rms_norm_eps=1e-5, bos_token_id=128000, eos_token_id=128001),
+    # development proxy: at --tp 2 every rank holds the same weight shapes as one rank of llama-3-8b at --tp 8 (4 query
+    # heads, 1 kv head, 1792 MLP columns, 16032 vocabulary rows), so host-launch-bound behaviour of the tensor-parallel
+    # path can be studied on 2 GPUs
+    'llama-3-8b-tp8-rank-slice-x2': dict(vocab_size=32064, hidden_size=4096, intermediate_size=3584,
+                                         num_hidden_layers=32, num_attention_heads=8, num_key_value_heads=2,
+                                         head_dim=128, max_position_embeddings=8192, rope_theta=500000.0,
+                                         rms_norm_eps=1e-5),
     # for smoke runs on small memory / CPU
     'llama-tiny': dict(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
                        num_attention_heads=4, num_key_value_heads=2, max_position_embeddings=8192),
@@ -135,6 +142,10 @@ def main() -> None:
                          'document, prompt tokens carry no loss)')
     ap.add_argument('--neftune', type=float, default=0.0, help='NEFTune alpha (config 3 uses 5)')
     ap.add_argument('--phases', action='store_true', help='also report forward / backward / optimizer device time')
+    ap.add_argument('--kernel-profile', default='', help='write rank 0\'s per-kernel device time of the timed steps '
+                    '(torch.profiler / CUPTI) to this file; the printed numbers of such a run are NOT benchmark values')
+    ap.add_argument('--host-profile', default='', help='write rank 0\'s cProfile of the timed steps (top functions by '
+                    'own time) to this file; the printed numbers of such a run are NOT benchmark values')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     env_world = int(os.environ.get('WORLD_SIZE', '1'))
@@ -314,9 +325,39 @@ def main() -> None:
     if cuda:
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         start.record()
+    if cuda and os.environ.get('LLMT_SYNC_DEBUG'):      # development: warn (with a stack) on every host-blocking op
+        torch.cuda.set_sync_debug_mode(1)
     t0 = time.perf_counter()
+    prof = None
+    if args.host_profile and rank == 0:
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
+    kprof = None
+    if args.kernel_profile and rank == 0 and cuda:
+        from torch.profiler import ProfilerActivity, profile
+        kprof = profile(activities=[ProfilerActivity.CUDA])
+        kprof.__enter__()
     for _ in range(args.steps):
         step()
+    if kprof is not None:
+        torch.cuda.synchronize()
+        kprof.__exit__(None, None, None)
+        os.makedirs(os.path.dirname(os.path.abspath(args.kernel_profile)), exist_ok=True)
+        open(args.kernel_profile, 'w').write(
+            f'{args.steps} steps\n' + kprof.key_averages().table(sort_by='cuda_time_total', row_limit=40,
+                                                                  max_name_column_width=90))
+    if prof is not None:
+        import io
+        import pstats
+        prof.disable()
+        out = io.StringIO()
+        pstats.Stats(prof, stream=out).sort_stats('tottime').print_stats(45)
+        os.makedirs(os.path.dirname(os.path.abspath(args.host_profile)), exist_ok=True)
+        open(args.host_profile, 'w').write(f'host wall {1e3 * (time.perf_counter() - t0) / args.steps:.2f} ms/step '
+                                           f'(enqueue only)\n' + out.getvalue())
+    if cuda and os.environ.get('LLMT_SYNC_DEBUG'):
+        torch.cuda.set_sync_debug_mode(0)
     trainer.strategy.synchronize_optimizer()     # the last step's overlapped optimizer update is inside the timing
     if cuda:
         end.record()
@@ -332,7 +373,7 @@ def main() -> None:
 
     # model FLOPs per token: 6*N_layer_params + 6*d*V + 6*L*d*T (causal attention, fwd+bwd)
     c = model_cfg
-    hd = c['hidden_size'] // c['num_attention_heads']
+    hd = c.get('head_dim') or c['hidden_size'] // c['num_attention_heads']
     layer_params = c['hidden_size'] * (c['num_attention_heads'] + 2 * c['num_key_value_heads']) * hd \
         + c['hidden_size'] * c['hidden_size'] + 3 * c['hidden_size'] * c['intermediate_size']
     # effective attended length: the whole sequence for pre-training packs, sum(len_i^2) / T for packed documents

@@ -57,7 +57,15 @@ def ptr(t: torch.Tensor | None) -> ctypes.c_void_p:
     return ctypes.c_void_p(0 if t is None else t.data_ptr())
 
 
+_raw_stream = getattr(torch._C, '_cuda_getCurrentRawStream', None)
+_raw_device = getattr(torch._C, '_cuda_getDevice', None)
+
+
 def stream() -> ctypes.c_void_p:
+    """The current stream's handle.  Called once per kernel launch (~1200 times per step under tensor parallelism):
+    the two raw accessors cost ~0.3 us, `torch.cuda.current_stream().cuda_stream` ~15 us."""
+    if _raw_stream is not None and _raw_device is not None:
+        return ctypes.c_void_p(_raw_stream(_raw_device()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

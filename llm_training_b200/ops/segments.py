@@ -29,11 +29,12 @@ def segment_bounds(attention_mask: torch.Tensor | None, batch_size: int, seq_len
         return start, start + seq_len
     seg = attention_mask.reshape(t).to(device=device, dtype=torch.int32)
     prev = torch.roll(seg, 1)
+    # position 0 is a row start, so is_start[0] is already True and the roll below wraps it into the last slot: no
+    # element assignment (a scalar written into a CUDA tensor is a pageable host-to-device copy that BLOCKS the host
+    # until the stream drains — one lost step of launch run-ahead)
     is_start = (seg != prev) | (idx % seq_len == 0)
-    is_start[0] = True
     start = torch.where(is_start, idx, torch.zeros_like(idx)).cummax(0).values.to(torch.int32)
     nxt_is_start = torch.roll(is_start, -1)
-    nxt_is_start[-1] = True
     end_marks = torch.where(nxt_is_start, idx + 1, torch.full_like(idx, t))
     end = end_marks.flip(0).cummin(0).values.flip(0).to(torch.int32)
     return start, end

@@ -278,13 +278,13 @@ class FlatParamEngine:
             self._after_unit_backward(u)
 
     def _reduce(self, u: ShardedUnit) -> None:
-        if self.tp_axis is not None:
+        if self.tp_axis is not None and self.world > 1:
             import torch.distributed as dist
             for _, p in u.params:
                 if getattr(p, '_tp_replicated', False) and p.grad is not None:
                     dist.all_reduce(p.grad, group=self.tp_axis.group)
         if self.world == 1:
-            return
+            return                      # pure tensor parallel: the replicas are summed once, in finish_backward
         if self.nvlink_grads and self.reshard:
             slot = self.grad_ring[self._ring_next]
             self._ring_next ^= 1
@@ -344,11 +344,28 @@ class FlatParamEngine:
                 self._launch_reduce(u)
         if self._comm_stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
+        self._replica_flat = None
+        if self.tp_axis is not None and self.world == 1:
+            self._allreduce_tp_replicas()
         if self.reshard:
             for u in self.units:
                 u.in_backward = False
                 self.reshard_unit(u)
                 self._free_grad(u)
+
+    def _allreduce_tp_replicas(self) -> None:
+        """Pure tensor parallel (no data-parallel sharding): the gradients of the parameters replicated over the tp
+        axis (norm weights, biases of row-parallel layers) are partial sums.  ONE all-reduce over their concatenation
+        instead of one per parameter (65 for a 32-layer model); the summed copy also serves the norm correction."""
+        import torch.distributed as dist
+        views = [p.grad.view(-1) for u in self.units for _, p in u.params
+                 if getattr(p, '_tp_replicated', False) and p.grad is not None]
+        if not views:
+            return
+        flat = torch.cat(views)
+        dist.all_reduce(flat, group=self.tp_axis.group)
+        torch._foreach_copy_(views, list(flat.split([v.numel() for v in views])))
+        self._replica_flat = flat
 
     def _rearm(self) -> None:
         for u in self.units:
@@ -664,11 +681,17 @@ class FlatParamEngine:
         """The norm is summed over the tp axis too; parameters replicated across it must count once."""
         if self.tp_axis is None or self.tp_axis.rank == 0:
             return
-        for u in self.units:
-            g = u.local_grad()
-            for _, p, _, start, length in u.shard_slices():
-                if getattr(p, '_tp_replicated', False):
-                    self._norm_sq -= g[start:start + length].float().pow(2).sum()
+        flat = getattr(self, '_replica_flat', None)
+        if flat is None:                 # sharded over dp as well: collect this rank's slices of the replicas
+            parts = []
+            for u in self.units:
+                g = u.local_grad()
+                parts += [g[start:start + length] for _, p, _, start, length in u.shard_slices()
+                          if getattr(p, '_tp_replicated', False)]
+            if not parts:
+                return
+            flat = torch.cat(parts)
+        self._norm_sq -= flat.float().pow(2).sum()       # one pass instead of four launches per parameter
 
     # ------------------------------------------------------------------ parameters
     def gather_unit(self, u: ShardedUnit) -> None:

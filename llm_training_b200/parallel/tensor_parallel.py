@@ -329,6 +329,7 @@ class _FusedGatherLinear(torch.autograd.Function):
         ctx.save_for_backward(x_local if ctx.regather else x_full, weight)
         ctx.tp = tp
         ctx.splits = [w.shape[0] for w in weights]
+        ctx.weights = weights
         return out
 
     @staticmethod
@@ -340,7 +341,8 @@ class _FusedGatherLinear(torch.autograd.Function):
             x_full = torch.empty((shard.shape[0] * tp.size, shard.shape[1]), dtype=shard.dtype, device=shard.device)
             dist.all_gather_into_tensor(x_full, shard, group=tp.axis.group)
         dy = dy.contiguous()
-        dws = gemm(dy, x_full, a_mn_major=True, b_mn_major=True).split(ctx.splits, dim=0)
+        from ..ops.linear_op import wgrad
+        dws = wgrad(dy, x_full, ctx.weights)       # straight into the flat gradient buffer when the engine allows it
         dx = _fused_linear_reduce_scatter(tp, dy, weight, None, b_mn_major=True)   # dy @ W, reduce-scattered
         return (dx, None, *dws)
 
@@ -372,6 +374,7 @@ class _FusedLinearReduceScatter(torch.autograd.Function):
         ctx.save_for_backward(x, weight)
         ctx.tp = tp
         ctx.has_residual = residual is not None
+        ctx.weights = (weight,)
         return _fused_linear_reduce_scatter(tp, x.contiguous(), weight, residual, b_mn_major=False)
 
     @staticmethod
@@ -379,7 +382,8 @@ class _FusedLinearReduceScatter(torch.autograd.Function):
         x, weight = ctx.saved_tensors
         tp = ctx.tp
         dx, dy_full = _gather_gemm(tp, dy_local.contiguous(), weight, b_mn_major=True)   # dy @ W, gathered dy kept
-        dw = gemm(dy_full, x.contiguous(), a_mn_major=True, b_mn_major=True)
+        from ..ops.linear_op import wgrad
+        dw = wgrad(dy_full, x.contiguous(), ctx.weights)[0]
         return dx, dw, (dy_local if ctx.has_residual else None), None
 
 
