@@ -112,6 +112,11 @@ struct BwdParams {
   // zero on entry.  nullptr = unordered reduce-adds.
   int* dq_order;
   int n_qblk;
+  // attn_bwd_ts_kernel only.  splits > 1: blockIdx.x = kv_head * splits + z, and CTA z takes the (head, q block)
+  // steps z, z + splits, ... of its kv block; the CTAs of one kv block then ADD their fp32 dK / dV tiles into dkv_acc
+  // ([T, 2*Hkv*D], zero on entry) instead of storing bf16.  For few kv heads per GPU (tensor parallel shards) the
+  // grid would otherwise be 64 CTAs whose longest one walks G * 128 steps alone.
+  int splits;
 };
 
 __device__ __forceinline__ float bwd_exp2(float x) {
@@ -514,6 +519,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
                    const __grid_constant__ CUtensorMap tmDO,    // dO [T][Hq][D], box {64,1,64}
                    const __grid_constant__ CUtensorMap tmDKV,   // dqkv, box {64,1,128} (store)
                    const __grid_constant__ CUtensorMap tmDQ,    // dq_acc fp32 [T][Hq*D], box {128, 64}, no swizzle
+                   const __grid_constant__ CUtensorMap tmDKVacc,  // dkv_acc fp32 [T][2*Hkv*D], same box (splits > 1)
                    BwdParams p) {
   using C = BwdTsCfg;
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -533,7 +539,9 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 16);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const int g = blockIdx.x;                       // kv head (fast axis: longest jobs of every head start first)
+  const int S = p.splits;
+  const int g = (int)blockIdx.x / S;              // kv head (fast axis: longest jobs of every head start first)
+  const int z = (int)blockIdx.x - g * S;          // this CTA's share of the kv block's steps: z, z + S, ...
   const int G = p.hq / p.hkv;
   const int k0 = (int)blockIdx.y * kBwdKV;
   const int k_last = min(k0 + kBwdKV, p.tokens) - 1;
@@ -542,7 +550,14 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   q_hi = min(q_hi, p.tokens - 1);
   const int i_lo = k0 / kBwdQ;
   const int nq = q_hi / kBwdQ - i_lo + 1;
-  const int n_total = G * nq;
+  const int n_total = (G * nq - z + S - 1) / S;
+  if (n_total <= 0) return;                       // more CTAs than steps (short kv block): nothing to add
+  const int h0 = g * G + z / nq, qi0 = z % nq;    // first step of this CTA
+  // every cursor over the (head, q block) steps moves S steps at a time
+  auto advance = [&](int& h, int& qi) {
+    qi += S;
+    while (qi >= nq) { qi -= nq; ++h; }
+  };
 
   if (warp == kBwdMmaWarp && lane == 0) {
     mbar_init(kv_full, 1);
@@ -568,6 +583,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       tma_prefetch_desc(&tmDO);
       tma_prefetch_desc(&tmDKV);
       tma_prefetch_desc(&tmDQ);
+      if (S > 1) tma_prefetch_desc(&tmDKVacc);
     }
     tmem_alloc<1>(tmem_ptr_smem, 512);
     tmem_relinquish<1>();
@@ -588,7 +604,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       }
     }
     __syncwarp();
-    int st = 0, h = g * G, qi = 0;
+    int st = 0, h = h0, qi = qi0;
     uint32_t ph = 0;
 #pragma unroll 1
     for (int it = 0; it < n_total; ++it) {
@@ -604,7 +620,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       }
       __syncwarp();
       if (++st == C::kStages) { st = 0; ph ^= 1; }
-      if (++qi == nq) { qi = 0; ++h; }
+      advance(h, qi);
     }
   } else if (warp == kBwdMmaWarp) {
     // ===== MMA issuer: the WHOLE warp walks the loop (uniform control flow, waits included); one elected lane
@@ -718,8 +734,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     auto meta = [&](int it) { return reinterpret_cast<float*>(smem + C::kMetaOff) + (it % 3) * 128; };
     float pre = 0.f;
     // (head, q block) of steps it+2 [metadata fetch], it+1 [P^T] and it-1 [dQ^T drain], advanced once per iteration
-    int f_h = g * G, f_qi = 0, n_qi = 0, d_h = g * G, d_qi = 0;
-    auto advance = [&](int& h, int& qi) { if (++qi == nq) { qi = 0; ++h; } };
+    int f_h = h0, f_qi = qi0, n_qi = qi0, d_h = h0, d_qi = qi0;
     auto meta_fetch = [&]() {                            // fetches step (f_h, f_qi), then advances the cursor
       if (hf == 0) {                                     // warps 0-3 fetch for everybody
         const int q = (i_lo + f_qi) * kBwdQ + (r & 63);
@@ -736,7 +751,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 
     uint32_t sv[32];                                     // P^T of the current step, fp32 bit patterns
     float tv[32];                                        // soft-capping only: tanh(s * scale / cap) of the same step
-    int a_h = g * G, a_qi = 0;                           // (head, q block) of the step whose P^T / dS^T is being built
+    int a_h = h0, a_qi = qi0;                            // (head, q block) of the step whose P^T / dS^T is being built
 
     // Deterministic mode: the kv blocks that touch one dQ tile add to it in ascending order.  The contributors of a
     // q block are a contiguous run of kv blocks (q_hi is non-decreasing in the kv block), so this CTA waits for
@@ -928,7 +943,8 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       if (it + 1 < n_total) {
         const int nx = it + 1;
         const int q0 = (i_lo + n_qi) * kBwdQ;
-        if (++n_qi == nq) n_qi = 0;
+        n_qi += S;
+        while (n_qi >= nq) n_qi -= nq;
         const float* mL = meta(nx) + c_base;
         const bool need_mask = tail_tile || (q0 < k0 + kBwdKV - 1) || (q0 + kBwdQ > q_end_first);
         mbar_wait(s_full, nx & 1);
@@ -994,6 +1010,40 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
     // ---- dK (x softmax scale) / dV : TMEM -> bf16 -> smem (K / V tile regions) -> TMA store
     mbar_wait(acc_done, 0);
     tc_fence_after();
+    if (S > 1) {
+      // several CTAs share this kv block: fp32 tiles [128 kv][128 d] (dK over the K | V tile regions, dV over the
+      // Q / dO ring: every operand has been consumed) are reduce-ADDED into dkv_acc, two 64-row boxes each
+      const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
+      float* stage = reinterpret_cast<float*>(smem + (which == 0 ? C::kKOff : C::kQOff)) + r * kBwdD;
+      const uint32_t col = which == 0 ? C::kColDK : C::kColDV;
+      float mul = which == 0 ? p.scale : 1.f;
+      if constexpr (kExtras) {
+        if (which == 1 && p.drop_thr != 0) mul = p.drop_scale;
+      }
+#pragma unroll 1
+      for (int c0 = 0; c0 < kBwdD; c0 += 32) {
+        uint32_t o[32];
+        tmem_ld_32x32b_x32(t_lane + col + c0, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int c = 0; c < 32; c += 4)
+          *reinterpret_cast<float4*>(stage + c0 + c) =
+              make_float4(__uint_as_float(o[c]) * mul, __uint_as_float(o[c + 1]) * mul,
+                          __uint_as_float(o[c + 2]) * mul, __uint_as_float(o[c + 3]) * mul);
+      }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) {
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+          tma_reduce_add_2d(&tmDKVacc, sbase + C::kKOff + b * (kBwdQ * kBwdD * 4), g * p.head_dim, k0 + b * kBwdQ);
+          tma_reduce_add_2d(&tmDKVacc, sbase + C::kQOff + b * (kBwdQ * kBwdD * 4), (p.hkv + g) * p.head_dim,
+                            k0 + b * kBwdQ);
+        }
+        tma_store_commit();
+        tma_store_wait<0>();
+      }
+    } else {
     {
       const int which = hf;                                // warps 0-3 drain dK, warps 4-7 drain dV
       uint8_t* stage = smem + (which == 0 ? C::kKOff : C::kVOff);
@@ -1029,6 +1079,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
       tma_store_commit();
       tma_store_wait<0>();
     }
+    }
   }
 
   tc_fence_before();
@@ -1042,13 +1093,24 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
 using namespace llmt;
 using namespace llmt::attn;
 
+// How many CTAs should share one kv block's steps (see BwdParams::splits): enough to put ~2 CTAs on every SM when the
+// plain grid (kv heads x kv blocks) is smaller than that, at most 8.  1 = no split (no dkv_acc needed).
+extern "C" int llmt_attn_bwd_splits(int tokens, int hkv) {
+  const int ctas = hkv * ((tokens + kBwdKV - 1) / kBwdKV);
+  const int want = 2 * num_sms();
+  if (ctas <= 0 || ctas >= want) return 1;
+  const int s = (want + ctas - 1) / ctas;
+  return s > 8 ? 8 : s;
+}
+
 // Backward of llmt_attn_fwd.  delta: fp32 [Hq, T] scratch; dq_acc: fp32 [T, Hq*D] scratch, must be ZERO on
 // entry; dqkv: bf16 [T, (Hq+2Hkv)*D] (same row stride as qkv), fully overwritten.
 // softcap / dropout_thr / seed: the values the forward call (llmt_attn_fwd_ex) was given.
 extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                                 float* dq_acc, void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq,
                                 int hkv, int head_dim, int64_t qkv_stride, float scale, int window, float softcap,
-                                int dropout_thr, uint32_t seed, int* dq_order, cudaStream_t stream) {
+                                int dropout_thr, uint32_t seed, int* dq_order, float* dkv_acc,
+                                cudaStream_t stream) {
   LLMT_REQUIRE(tokens > 0 && hq > 0 && hkv > 0 && hq % hkv == 0, "attn_bwd: bad head counts %d/%d", hq, hkv);
   LLMT_REQUIRE(head_dim % 16 == 0 && head_dim <= 128, "attn_bwd: head_dim %d unsupported", head_dim);
   LLMT_REQUIRE(qkv_stride % 8 == 0, "attn_bwd: qkv stride must be a multiple of 8");
@@ -1091,6 +1153,19 @@ extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* do
     LLMT_REQUIRE(e == cudaSuccess, "attn_bwd: clearing the dQ order counters failed: %s", cudaGetErrorString(e));
   }
   const bool extras = softcap > 0.f || dropout_thr > 0 || dq_order != nullptr;
+  // dkv_acc != nullptr (fp32 [T, 2*Hkv*D] scratch, zeroed here): the steps of a kv block may be shared by several
+  // CTAs.  Not in deterministic mode: the CTAs' dK / dV tiles would be added in arrival order.
+  p.splits = 1;
+  CUtensorMap tdkvacc = tdq;
+  if (dkv_acc != nullptr && dq_order == nullptr) {
+    p.splits = llmt_attn_bwd_splits(tokens, hkv);
+    if (p.splits > 1) {
+      cudaError_t e = cudaMemsetAsync(dkv_acc, 0, sizeof(float) * (size_t)tokens * 2 * hkv * head_dim, stream);
+      LLMT_REQUIRE(e == cudaSuccess, "attn_bwd: clearing the dK/dV accumulator failed: %s", cudaGetErrorString(e));
+      rc = make_tmap_f32_2d(&tdkvacc, dkv_acc, tokens, (int64_t)2 * hkv * head_dim, kBwdD, kBwdQ);
+      if (rc) return rc;
+    }
+  }
   dim3 grid(hkv, (tokens + kBwdKV - 1) / kBwdKV);
   // LLMT_ATTN_BWD=ss selects the first-generation kernel (every MMA operand in shared memory); default: P^T / dS^T in
   // tensor memory
@@ -1100,17 +1175,21 @@ extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* do
     static bool configured[kMaxDevices] = {};
     rc = ensure_smem_attr(attn_bwd_kernel, BwdCfg::kSmemBytes, configured, "attn_bwd");
     if (rc) return rc;
+    p.splits = 1;
     attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
   } else {
+    grid.x = hkv * p.splits;
     static bool configured[2][kMaxDevices] = {};
     if (extras) {
       rc = ensure_smem_attr(attn_bwd_ts_kernel<true>, BwdTsCfg::kSmemBytes, configured[1], "attn_bwd");
       if (rc) return rc;
-      attn_bwd_ts_kernel<true><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+      attn_bwd_ts_kernel<true><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq,
+                                                                                    tdkvacc, p);
     } else {
       rc = ensure_smem_attr(attn_bwd_ts_kernel<false>, BwdTsCfg::kSmemBytes, configured[0], "attn_bwd");
       if (rc) return rc;
-      attn_bwd_ts_kernel<false><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
+      attn_bwd_ts_kernel<false><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq,
+                                                                                     tdkvacc, p);
     }
   }
   rc = check_launch("attn_bwd");
@@ -1122,7 +1201,15 @@ extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* do
   // the TS kernel accumulates unscaled dS^T K; the softmax scale is folded into this pass
   attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dq_acc, (__nv_bfloat16*)dqkv, tokens, width,
                                                                qkv_stride, use_ss ? 1.f : scale);
-  return check_launch("attn_dq_convert");
+  rc = check_launch("attn_dq_convert");
+  if (rc || use_ss || p.splits == 1) return rc;
+  // shared kv blocks: dK | dV were accumulated in fp32 (softmax scale already applied)
+  const int kv_width = 2 * hkv * head_dim;
+  blocks = ((int64_t)tokens * kv_width / 8 + 255) / 256;
+  if (blocks > cap) blocks = cap;
+  attn_dq_convert_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dkv_acc, (__nv_bfloat16*)dqkv + (int64_t)hq * head_dim,
+                                                               tokens, kv_width, qkv_stride, 1.f);
+  return check_launch("attn_dkv_convert");
 }
 
 extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
@@ -1130,5 +1217,5 @@ extern "C" int llmt_attn_bwd(const void* qkv, const void* out, const void* dout,
                              int hkv, int head_dim, int64_t qkv_stride, float scale, int window,
                              cudaStream_t stream) {
   return llmt_attn_bwd_ex(qkv, out, dout, lse, delta, dq_acc, dqkv, seg_start, seg_end, tokens, hq, hkv, head_dim,
-                          qkv_stride, scale, window, 0.f, 0, 0u, nullptr, stream);
+                          qkv_stride, scale, window, 0.f, 0, 0u, nullptr, nullptr, stream);
 }

@@ -111,7 +111,10 @@ int llmt_attn_fwd_ex(const void* qkv, void* out, float* lse, const int* seg_star
 int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, float* dq_acc,
                      void* dqkv, const int* seg_start, const int* seg_end, int tokens, int hq, int hkv, int head_dim,
                      int64_t qkv_stride, float scale, int window, float softcap, int dropout_thr, uint32_t seed,
-                     int* dq_order, cudaStream_t stream);
+                     int* dq_order, float* dkv_acc, cudaStream_t stream);
+/* dkv_acc: NULL, or an fp32 scratch [tokens, 2*hkv*head_dim] when llmt_attn_bwd_splits(tokens, hkv) > 1: with few kv
+ * heads on a GPU (tensor-parallel shards) several CTAs then share each kv block and add their dK / dV tiles there. */
+int llmt_attn_bwd_splits(int tokens, int hkv);
 /* dq_order: NULL, or an int scratch of hq * ceil(tokens / 64) entries: the kv blocks then add their dQ contributions
  * in ascending order, which makes the backward bit-reproducible (the reference's `deterministic` flag,
  * src/llm_training/ops/attention_op.py:551,590-592). */

@@ -47,13 +47,16 @@ class _PackedAttentionFn(torch.autograd.Function):
         dq_acc = torch.zeros((tokens, hq * head_dim), dtype=torch.float32, device=qkv.device)
         # deterministic: per (head, 64-query block) turn counters, so the kv blocks add into dq_acc in a fixed order
         order = torch.empty(hq * ((tokens + 63) // 64), dtype=torch.int32, device=qkv.device) if deterministic else None
+        # few kv heads on this GPU (tensor-parallel shard): several CTAs share each kv block and add fp32 dK / dV tiles
+        dkv_acc = None
+        if not deterministic and L.llmt_attn_bwd_splits(_lib.c_int(tokens), _lib.c_int(hkv)) > 1:
+            dkv_acc = torch.empty((tokens, 2 * hkv * head_dim), dtype=torch.float32, device=qkv.device)
         _lib.check(L.llmt_attn_bwd_ex(_lib.ptr(qkv), _lib.ptr(out), _lib.ptr(dout), _lib.ptr(lse), _lib.ptr(delta),
                                       _lib.ptr(dq_acc), _lib.ptr(dqkv), _lib.ptr(seg_start), _lib.ptr(seg_end),
                                       _lib.c_int(tokens), _lib.c_int(hq), _lib.c_int(hkv), _lib.c_int(head_dim),
                                       _lib.c_i64(qkv.stride(0)), _lib.c_f32(scale), _lib.c_int(window),
                                       _lib.c_f32(softcap), _lib.c_int(drop_thr), ctypes.c_uint32(seed),
-                                      _lib.ptr(order) if deterministic else ctypes.c_void_p(0),
-                                      _lib.stream()), 'attn_bwd')
+                                      _lib.ptr(order), _lib.ptr(dkv_acc), _lib.stream()), 'attn_bwd')
         return (dqkv,) + (None,) * 11
 
 

@@ -585,7 +585,7 @@ def test_optimizer_state_cpu_offload_matches_device_update():
         assert float(((a - b).abs() > 1e-6).float().mean()) < 0.05
 
 
-def test_direct_wgrad_accumulation_with_deferred_zeroing_matches_autograd_accumulation():
+def test_direct_wgrad_accumulation_with_deferred_zeroing_matches_autograd_accumulation(monkeypatch):
     """Engine path of the benchmark on one GPU: wgrad GEMMs write straight into the flat gradient buffer, and the
     buffer's weight ranges are NOT cleared between steps (the first wgrad of a step overwrites).  Four steps must
     give the same parameters as the plain path (temporary dW + AccumulateGrad into a zeroed buffer)."""
@@ -595,6 +595,10 @@ def test_direct_wgrad_accumulation_with_deferred_zeroing_matches_autograd_accumu
     from llm_training_b200.parallel import apply_fully_sharded
     cfg = LlamaConfig(vocab_size=1024, hidden_size=256, intermediate_size=512, num_hidden_layers=2,
                       num_attention_heads=4, num_key_value_heads=2)
+    # AdamW moves every element by ~lr per step whatever the gradient's size, so rounding-level differences in
+    # near-zero gradients would show up as 2 * steps * lr in the parameters: keep attention bit-reproducible, the two
+    # runs then differ only in how the weight gradients are accumulated
+    monkeypatch.setenv('FLASH_ATTENTION_DETERMINISTIC', '1')
     runs = []
     for direct in (False, True):
         torch.manual_seed(0)
