@@ -512,7 +512,9 @@ __device__ __forceinline__ float bwd_tanh(float x) {
   return y;
 }
 
-template <bool kExtras>
+// kSplit = false compiles S (BwdParams::splits) to the constant 1, so the usual many-kv-head launch keeps the exact
+// instruction stream it had before kv blocks could be shared.
+template <bool kExtras, bool kSplit>
 __global__ void __launch_bounds__(kBwdThreads, 1)
 attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,1,128}
                    const __grid_constant__ CUtensorMap tmQ,     // qkv, box {64,1,64}
@@ -539,7 +541,7 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 16);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const int S = p.splits;
+  const int S = kSplit ? p.splits : 1;
   const int g = (int)blockIdx.x / S;              // kv head (fast axis: longest jobs of every head start first)
   const int z = (int)blockIdx.x - g * S;          // this CTA's share of the kv block's steps: z, z + S, ...
   const int G = p.hq / p.hkv;
@@ -1179,18 +1181,19 @@ extern "C" int llmt_attn_bwd_ex(const void* qkv, const void* out, const void* do
     attn_bwd_kernel<<<grid, kBwdThreads, BwdCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, p);
   } else {
     grid.x = hkv * p.splits;
-    static bool configured[2][kMaxDevices] = {};
-    if (extras) {
-      rc = ensure_smem_attr(attn_bwd_ts_kernel<true>, BwdTsCfg::kSmemBytes, configured[1], "attn_bwd");
-      if (rc) return rc;
-      attn_bwd_ts_kernel<true><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq,
-                                                                                    tdkvacc, p);
-    } else {
-      rc = ensure_smem_attr(attn_bwd_ts_kernel<false>, BwdTsCfg::kSmemBytes, configured[0], "attn_bwd");
-      if (rc) return rc;
-      attn_bwd_ts_kernel<false><<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq,
-                                                                                     tdkvacc, p);
-    }
+    static bool configured[4][kMaxDevices] = {};
+    auto launch = [&](auto kernel, bool* flags) -> int {
+      int r = ensure_smem_attr(kernel, BwdTsCfg::kSmemBytes, flags, "attn_bwd");
+      if (r) return r;
+      kernel<<<grid, kBwdThreads, BwdTsCfg::kSmemBytes, stream>>>(tkv, tq, tdo, tdkv, tdq, tdkvacc, p);
+      return 0;
+    };
+    const bool split = p.splits > 1;
+    if (extras && split) rc = launch(attn_bwd_ts_kernel<true, true>, configured[3]);
+    else if (extras)     rc = launch(attn_bwd_ts_kernel<true, false>, configured[2]);
+    else if (split)      rc = launch(attn_bwd_ts_kernel<false, true>, configured[1]);
+    else                 rc = launch(attn_bwd_ts_kernel<false, false>, configured[0]);
+    if (rc) return rc;
   }
   rc = check_launch("attn_bwd");
   if (rc) return rc;
