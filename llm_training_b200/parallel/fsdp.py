@@ -235,6 +235,11 @@ class FlatParamEngine:
             u.ready_ids = set()
             u.reduced = False
             u.work = None
+        # Gradient reductions are issued in ONE order on every rank — last unit first, the order backward completes
+        # them in — whatever order the gradients really arrive in: the NVLink collectives pair ranks up by a running
+        # epoch, so a rank whose unit k got no gradient (unused parameters, a branch not taken on its batch) must not
+        # let unit k-1 overtake it.  A unit that is not ready holds back the ones before it until `finish_backward`.
+        self._next_reduce = len(self.units) - 1
 
     def _on_grad_ready(self, param: nn.Parameter) -> None:
         """One notification per parameter and backward pass.  A parameter can report twice — the wgrad GEMM that
@@ -248,7 +253,18 @@ class FlatParamEngine:
         u.ready_ids.add(id(param))
         u.pending_grads -= 1
         if u.pending_grads == 0 and self.require_sync:
-            self._launch_reduce(u)
+            self._launch_ready_reductions()
+
+    def _launch_ready_reductions(self, flush: bool = False) -> None:
+        """Issue the reductions of the longest run of complete units, in the fixed order (see `_reset_pending`);
+        ``flush``: the backward pass is over, issue everything that is left."""
+        while self._next_reduce >= 0:
+            u = self.units[self._next_reduce]
+            if not flush and u.pending_grads > 0:
+                return
+            self._next_reduce -= 1
+            if not u.reduced:
+                self._launch_reduce(u)
 
     def _settle_fresh(self, u: ShardedUnit) -> None:
         """Weights whose zeroing was deferred to their first wgrad GEMM (`zero_grad`) but that received NO gradient
@@ -339,9 +355,7 @@ class FlatParamEngine:
             for u in self.units:       # un-hooked units / units that saw no backward still need gradient storage
                 if not u.reduced:
                     self._alloc_grad(u)
-        for u in self.units:
-            if not u.reduced:          # params that received no grad this step (unused / frozen siblings)
-                self._launch_reduce(u)
+        self._launch_ready_reductions(flush=True)      # params that received no grad this step (unused / frozen siblings)
         if self._comm_stream is not None:
             torch.cuda.current_stream(self.device).wait_stream(self._comm_stream)
         self._replica_flat = None

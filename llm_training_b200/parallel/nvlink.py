@@ -7,8 +7,9 @@ in-tree kernels with plain loads / stores on the mapped peer addresses.
 Protocol notes
   * barrier / one-shot all-reduce use uint32 slots in the signal pads with monotonically increasing epochs
     (``st.release.sys`` by the writer, ``ld.acquire.sys`` spin by the reader);
-  * all ranks issue the same sequence of collectives (same model, same autograd order), so epochs agree
-    without any host-side negotiation;
+  * all ranks issue the same sequence of collectives, so epochs agree without any host-side negotiation: parameter
+    gathers follow the module order, and the sharding engine issues gradient reductions in one fixed order (last unit
+    first) even when a rank's gradients arrive in another order or not at all (``FlatParamEngine._launch_ready_reductions``);
   * kernels run on the caller's current stream; the sharding engine puts them on its communication stream.
 """
 import ctypes

@@ -526,3 +526,35 @@ def test_dpo_reference_model_is_sharded_with_the_policy(tmp_path):
         assert torch.equal(z3[0][1][k], v), k
     ref_keys = [k for k in z3[0][1] if k.startswith('ref_model.')]
     assert ref_keys and all(z3[0][1][k].numel() > 0 for k in ref_keys)
+
+
+def _uneven_worker(rank: int, world: int, reshard: bool):
+    """Rank 1 never uses decoder layer 0 (its parameters get no gradient there); rank 0 uses everything."""
+    from llm_training_b200.optim import ShardedOptimizer
+    from llm_training_b200.parallel import apply_fully_sharded, init_mesh
+    mesh = init_mesh(world, 1)
+    model = _make_model()
+    if rank == 1:
+        model.layers[0].forward = lambda hidden_states, ctx: hidden_states
+    engine = apply_fully_sharded(model, mesh.dp, reshard_after_forward=reshard)
+    opt = ShardedOptimizer(torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.0), [engine],
+                           max_grad_norm=1.0)
+    for step in range(2):
+        opt.zero_grad()
+        _loss(model, _batch(step)[rank::world]).backward()
+        opt.step()
+    with engine.unsharded():
+        params = {n: p.detach().clone() for n, p in model.named_parameters()}
+    return params, float(opt.last_grad_norm)
+
+
+@pytest.mark.parametrize('reshard', [False, True])
+def test_ranks_with_unused_parameters_still_reduce_in_one_order(reshard):
+    """The engine issues gradient reductions in a fixed order on every rank.  Before, a rank whose unit received no
+    gradient reduced it last while its peers reduced it in backward order: the collectives paired up different units
+    (mismatched sizes on gloo / NCCL, silently wrong data on the epoch-paired NVLink kernels)."""
+    results = run_distributed(_uneven_worker, world=2, args=(reshard,))
+    (p0, n0), (p1, n1) = results
+    assert abs(n0 - n1) < 1e-6                      # one global gradient norm
+    for name in p0:
+        assert torch.equal(p0[name], p1[name]), name      # every rank holds the same updated parameters
