@@ -10,12 +10,15 @@
 //
 // One CTA = 128 query rows of one head; KV is streamed in blocks of 64 rows.
 //   warps 0-3 : softmax — thread r owns query row r == TMEM lane r.  S block: tcgen05.ld -> mask ->
-//               online max/sum (exp2, lazy O rescale) -> P (bf16) into SWIZZLE_128B smem
-//   warp  4   : tcgen05.mma issuer (lane 0):  S = Q K^T (SS, both K-major),  O += P V (V is MN-major B)
+//               online max/sum (exp2, lazy O rescale) -> P as packed bf16 pairs written back into TENSOR MEMORY, over
+//               the first 32 columns of the S block it was computed from (tcgen05.st)
+//   warp  4   : tcgen05.mma issuer (one elected lane):  S = Q K^T (SS, both K-major),  O += P V (TS form: A = P from
+//               TMEM, V is the MN-major B operand in smem)
 //   warp  5   : TMA producer (lane 0): Q once, K/V double-buffered
 // S is double-buffered in TMEM (2 x 64 columns) so S(j+1) is computed while softmax works on S(j); O lives in
-// TMEM (DPAD columns).  ~113 KB smem and 256 TMEM columns per CTA -> two CTAs per SM, so one CTA's softmax
-// overlaps the other's MMAs.
+// TMEM (DPAD columns).  P never touches shared memory: no 16 KB tile write + read back per step, no generic->async
+// proxy fence (the tensor pipe executes in issue order: S(j+2), which overwrites P(j), is issued after PV(j)).
+// ~97 KB smem and 256 TMEM columns per CTA -> two CTAs per SM, so one CTA's softmax overlaps the other's MMAs.
 #include <cuda.h>
 
 #include "common.cuh"
@@ -40,8 +43,7 @@ struct FwdCfg {
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kQOff + kQBytes;
   static constexpr int kVOff = kKOff + 2 * kKVBytes;
-  static constexpr int kPOff = kVOff + 2 * kKVBytes;
-  static constexpr int kBarOff = kPOff + kPBytes;
+  static constexpr int kBarOff = kVOff + 2 * kKVBytes;
   static constexpr int kNumBars = 15;   // q_full, k/v full+empty x2, s full+empty x2, p_full, o_done
   static constexpr int kSmemBytes = kBarOff + (kNumBars + 1) * 8 + 16;
   static constexpr int kTmemCols = (128 + DPAD) <= 256 ? 256 : 512;
@@ -180,7 +182,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
     const uint32_t tb = __shfl_sync(0xffffffffu, tmem_base, 0);
     const uint64_t q_a = make_smem_desc(sbase + C::kQOff, 0, 1024);                    // Q as A, K-major
     const uint64_t k_b0 = make_smem_desc(sbase + C::kKOff, 0, 1024);                   // K as B, K-major, stage 0
-    const uint64_t p_a = make_smem_desc(sbase + C::kPOff, 0, 1024);                    // P as A, K-major
     const uint64_t v_b0 = make_smem_desc(sbase + C::kVOff, kBlockKV * 128, 1024);      // V as B, MN-major, stage 0
     constexpr uint64_t kStage = C::kKVBytes >> 4;
     auto kmaj = [](int kk, int rows) -> uint64_t { return (uint64_t)((kk / 4) * (rows * 8) + (kk % 4) * 2); };
@@ -218,8 +219,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
         const uint64_t v_b = v_b0 + (uint64_t)st * kStage;
 #pragma unroll
         for (int kk = 0; kk < kBlockKV / 16; ++kk)
-          // P: 2 descriptor units per k-step; V: MN-major B, [kv rows][64 d] boxes, 16 kv rows per k-step
-          umma_f16<1>(tb + C::kOCol, p_a + (uint64_t)kk * 2, v_b + (uint64_t)kk * 128, idesc_pv, (j | kk) != 0);
+          // P: bf16 pairs in the S block's first columns, 8 columns per k-step; V: MN-major B, [kv rows][64 d]
+          // boxes, 16 kv rows per k-step
+          umma_f16_ts<1>(tb + C::kOCol, tb + (uint32_t)(st * kBlockKV + kk * 8), v_b + (uint64_t)kk * 128, idesc_pv,
+                         (j | kk) != 0);
         umma_commit(v_empty(st));
         umma_commit(o_done);
       }
@@ -233,7 +236,6 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
     const int lo_row = row_ok ? lower_bound(q_idx) : q_idx;
     const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
     float m = -INFINITY, l = 0.f;
-    uint8_t* p_row = smem + C::kPOff + row * 128;
 
     for (int j = 0; j < nb; ++j) {
       const int sb = j & 1;
@@ -264,8 +266,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
           mx = fmaxf(mx, s);
         }
       } else {
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four short max chains
 #pragma unroll
-        for (int c = 0; c < 64; ++c) mx = fmaxf(mx, __uint_as_float(sv[c]));
+        for (int c = 0; c < 64; ++c) mx4[c & 3] = fmaxf(mx4[c & 3], __uint_as_float(sv[c]));
+        mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       }
       if constexpr (kExtras) {
         // soft-capping (cap * tanh(s * scale / cap)) turns the scores into their final log2-domain values here;
@@ -292,13 +296,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
         m = m_new;
       }
       const float m_use = (m == -INFINITY) ? 0.f : m;
-      float sum = 0.f;
+      float sum4[4] = {0.f, 0.f, 0.f, 0.f};               // four short add chains instead of one of 64
       uint32_t pk[32];
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
         float e0 = fast_exp2(fmaf(__uint_as_float(sv[c]), sc, -m_use));
         float e1 = fast_exp2(fmaf(__uint_as_float(sv[c + 1]), sc, -m_use));
-        sum += e0 + e1;                                     // the normaliser is the UNdropped sum
+        sum4[(c >> 1) & 3] += e0 + e1;                      // the normaliser is the UNdropped sum
         if constexpr (kExtras) {
           if (p.drop_thr != 0) {
             const uint32_t rnd = dropout_bits(p.seed, head, q_idx, (kv0 + c) >> 2);   // c is even: same 4-group
@@ -309,10 +313,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
         __nv_bfloat162 h = __floats2bfloat162_rn(e0, e1);
         pk[c >> 1] = *reinterpret_cast<uint32_t*>(&h);
       }
-      l = l * alpha + sum;
+      l = l * alpha + ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
 
       if (j > 0) {
-        mbar_wait(o_done, (j - 1) & 1);   // PV(j-1) finished: P smem is free, O is stable
+        // Every phase of o_done is waited for, in order (a parity wait is only meaningful one phase behind).  PV(j-1)
+        // was issued a whole softmax step ago, so this rarely blocks; only a changed row max needs it (O rescale).
+        mbar_wait(o_done, (j - 1) & 1);
         tc_fence_after();
         if (__any_sync(0xffffffffu, alpha != 1.f)) {
 #pragma unroll
@@ -327,13 +333,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
           tmem_st_wait();
         }
       }
-      // P row -> smem, K-major SWIZZLE_128B ([128 rows][64 cols] box)
-#pragma unroll
-      for (int ch = 0; ch < 8; ++ch) {
-        *reinterpret_cast<uint4*>(p_row + ((ch ^ (row & 7)) << 4)) =
-            make_uint4(pk[ch * 4 + 0], pk[ch * 4 + 1], pk[ch * 4 + 2], pk[ch * 4 + 3]);
-      }
-      fence_proxy_async_smem();
+      // P row -> tensor memory, over the S block it came from (bf16 pairs: column c holds keys 2c, 2c+1)
+      tmem_st_32x32b_x32(t_lane + (uint32_t)(sb * kBlockKV), pk);
+      tmem_st_wait();
       tc_fence_before();
       mbar_arrive(p_full);
     }
