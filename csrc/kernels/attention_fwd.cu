@@ -100,10 +100,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV_q,   // box {64, 1, 12
   volatile uint32_t* tmem_ptr_gen = reinterpret_cast<volatile uint32_t*>(smem + C::kBarOff + 8 * 15);
 
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  // heavy (late) query tiles first: they have the most KV blocks
+  // Heavy (late) query tiles first ACROSS heads: the head index is the fast grid axis, so the 128-step tiles of every
+  // head are dispatched before any light tile (head-major order would start the last head's heaviest tile near the end
+  // of the kernel: +13% makespan for a causal 8192-token launch).  The four query heads of a kv group run together.
   const int num_q_tiles = (p.tokens + kBlockQ - 1) / kBlockQ;
-  const int qt = num_q_tiles - 1 - (int)blockIdx.x;
-  const int head = blockIdx.y;
+  const int qt = num_q_tiles - 1 - (int)blockIdx.y;
+  const int head = blockIdx.x;
   const int kv_head = head / (p.hq / p.hkv);
   const int q0 = qt * kBlockQ;
   const int q_last = min(q0 + kBlockQ, p.tokens) - 1;
@@ -447,7 +449,7 @@ int launch_fwd(const CUtensorMap& tq, const CUtensorMap& tkv, const CUtensorMap&
   auto kern = attn_fwd_kernel<DPAD, kExtras>;
   static bool configured[kMaxDevices] = {};
   if (int rc = ensure_smem_attr(kern, C::kSmemBytes, configured, "attn_fwd")) return rc;
-  dim3 grid((p.tokens + kBlockQ - 1) / kBlockQ, p.hq);
+  dim3 grid(p.hq, (p.tokens + kBlockQ - 1) / kBlockQ);
   kern<<<grid, kFwdThreads, C::kSmemBytes, stream>>>(tq, tkv, to, p);
   return check_launch("attn_fwd");
 }
