@@ -23,7 +23,10 @@ def _worker(rank: int, world: int, port: int, comm_kind: str, queue) -> None:
         comm_kind = comm_kind.split('+')[0]
         os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR='127.0.0.1',
                           MASTER_PORT=str(port), LLMT_COMM=comm_kind,
-                          LLMT_MULTIMEM_RS='0' if 'pullrs' in flags else '1')
+                          LLMT_MULTIMEM_RS='0' if 'pullrs' in flags else '1',
+                          # the bit-for-bit comparisons below are about engine schedules: keep the attention backward's
+                          # fp32 adds in a fixed order (kv blocks are otherwise shared between CTAs on this tiny model)
+                          FLASH_ATTENTION_DETERMINISTIC='1')
         import torch.distributed as dist
         torch.cuda.set_device(rank)
         dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
