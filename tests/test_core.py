@@ -647,3 +647,51 @@ def test_hf_causal_lm_packed_attention_hook_matches_dense_mask_path():
     (b[keep].float().pow(2).mean()).backward()
     for (n, p), (_, q) in zip(dense.named_parameters(), hooked.named_parameters()):
         assert torch.allclose(p.grad, q.grad, atol=1e-5), n
+
+
+def test_deterministic_switches_reach_the_attention_op(monkeypatch):
+    """`Trainer(deterministic=True)` sets torch's global switch (Lightning semantics); the attention op reads it, and
+    the reference's own `FLASH_ATTENTION_DETERMINISTIC=1` (ops/attention_op.py:590-591), when the caller passes
+    `deterministic=None`."""
+    from llm_training_b200.lightning import Trainer
+    from llm_training_b200.ops import attention_op
+    monkeypatch.delenv('FLASH_ATTENTION_DETERMINISTIC', raising=False)
+    assert attention_op.deterministic_default() is False
+    monkeypatch.setenv('FLASH_ATTENTION_DETERMINISTIC', '1')
+    assert attention_op.deterministic_default() is True
+    monkeypatch.delenv('FLASH_ATTENTION_DETERMINISTIC')
+    try:
+        Trainer(deterministic=True, logger=False, enable_progress_bar=False, enable_checkpointing=False)
+        assert torch.are_deterministic_algorithms_enabled()
+        assert attention_op.deterministic_default() is True
+    finally:
+        torch.use_deterministic_algorithms(False)
+    try:
+        Trainer(deterministic='warn', logger=False, enable_progress_bar=False, enable_checkpointing=False)
+        assert torch.are_deterministic_algorithms_enabled() and torch.is_deterministic_algorithms_warn_only_enabled()
+    finally:
+        torch.use_deterministic_algorithms(False)
+    # the flag is part of the reference-compatible dispatcher's signature
+    q = torch.randn(1, 8, 2, 16)
+    out = attention_op.flash_attention_forward(q, q, q, None, 8, deterministic=True)
+    assert out.shape == q.shape
+
+
+def test_norm_multi_linear_residual_passthrough_keeps_values_and_gradients():
+    """`return_residual=True` hands `x` back for the residual connection; on the PyTorch path it is `x` itself, and the
+    result and every gradient equal the plain formulation."""
+    from llm_training_b200.ops import norm_multi_linear
+    torch.manual_seed(0)
+    x = torch.randn(6, 32, requires_grad=True)
+    nw = torch.rand(32, requires_grad=True)
+    w1, w2 = torch.randn(16, 32, requires_grad=True), torch.randn(8, 32, requires_grad=True)
+    y, x_res = norm_multi_linear(x, nw, 1e-5, [w1, w2], return_residual=True)
+    (y.sum() + (x_res * 2).sum()).backward()
+    got = [t.grad.clone() for t in (x, nw, w1, w2)]
+    for t in (x, nw, w1, w2):
+        t.grad = None
+    y2 = norm_multi_linear(x, nw, 1e-5, [w1, w2])
+    (y2.sum() + (x * 2).sum()).backward()
+    assert torch.equal(y, y2)
+    for a, t in zip(got, (x, nw, w1, w2)):
+        assert torch.allclose(a, t.grad)
