@@ -928,7 +928,11 @@ attn_bwd_ts_kernel(const __grid_constant__ CUtensorMap tmKV,    // qkv, box {64,
               if (p.dq_order != nullptr) {
                 int* ctr = p.dq_order + (size_t)d_h * p.n_qblk + (i_lo + d_qi);
                 if (i_lo + d_qi <= prev_hi_blk) {
-                  while (ld_acquire_gpu_s32(ctr) != (int)blockIdx.y) __nanosleep(64);
+                  unsigned spins = 0;
+                  while (ld_acquire_gpu_s32(ctr) != (int)blockIdx.y) {
+                    __nanosleep(64);
+                    if (++spins > (1u << 26)) __trap();     // > 4 s: the predecessor never came; fail, do not hang
+                  }
                   fence_proxy_async_all();                  // the earlier blocks' adds precede this async-proxy add
                 }
                 pend_order = ctr;
