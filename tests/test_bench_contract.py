@@ -58,3 +58,13 @@ def test_bench_reference_arm_runs_the_reference_modules():
     assert out['n_gpus'] == 1 and out['value'] > 0 and out['ours_loaded'] is False
     assert out['e2e']['h2d_bytes_per_step'] > 0 and out['e2e']['d2h_bytes_per_step'] > 0
     assert out['reference_class'] == 'reference modules, bare loop'
+
+
+def test_bench_host_profile_is_written_next_to_the_one_json_line(tmp_path):
+    """`--host-profile` (development aid) writes rank 0's enqueue-path profile to a file and leaves stdout alone."""
+    target = tmp_path / 'prof' / 'host.txt'
+    out = _run('--model', 'llama-tiny', '--steps', '1', '--warmup', '3', '--seq-len', '64', '--phases',
+               '--host-profile', str(target))
+    assert out['steps'] == 1
+    text = target.read_text()
+    assert text.startswith('host wall') and 'tottime' in text
